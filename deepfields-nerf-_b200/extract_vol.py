@@ -1,0 +1,154 @@
+"""Drop-in for the reference's scripts/extract_vol.py: dense density/colour query of an AABB grid, Otsu
+threshold, `volume.pth` in the reference layout.  The grid is never materialised on the fused path
+(coordinates are generated in the MLP kernel from the flat index); slabs of x-planes shard across ranks."""
+from __future__ import annotations
+
+import argparse
+import os
+import time
+from pathlib import Path
+from typing import Optional, Tuple
+
+import torch
+
+from . import ops
+from .config import load_config
+from .model import OptimizedVanillaNeRF
+
+
+def generate_3d_grid(bounds: Tuple[float, float], resolution: int, device="cuda") -> torch.Tensor:
+    """scripts/extract_vol.py:57-82: [R^3,3], ij order (x slowest, z fastest).  Built on the device from the
+    same torch.linspace values the reference meshgrids."""
+    lin = torch.linspace(bounds[0], bounds[1], resolution, device=device)
+    return ops.grid_points(lin, 0, resolution ** 3)
+
+
+def volume_extraction(model, points, canonical_view, batch_size: int = 8192, device: str = "cuda",
+                      show_progress: bool = True):
+    """scripts/extract_vol.py:85-120 -> (densities [N,1], rgbs [N,3]).  One persistent launch replaces the
+    reference's N/batch_size (H2D, model, 2x D2H) iterations; outputs stay on the device."""
+    model.eval()
+    with torch.no_grad():
+        pts = points.to(device)
+        view = canonical_view.to(device).float().reshape(1, 3).expand(pts.shape[0], 3).contiguous()
+        rgb, sigma = model(pts, view)
+    return sigma, rgb
+
+
+def otsu_from_histogram(hist: torch.Tensor, lo: float, hi: float) -> float:
+    """skimage.filters.threshold_otsu on a 256-bin histogram over [lo,hi] (bin centres, maximise the
+    between-class variance w0*w1*(m0-m1)^2).  scikit-image is unpinned and absent: parity unpinned."""
+    h = hist.double().cpu()
+    n = h.numel()
+    edges = torch.linspace(lo, hi, n + 1, dtype=torch.float64)
+    centres = 0.5 * (edges[:-1] + edges[1:])
+    w0 = torch.cumsum(h, 0)
+    w1 = torch.cumsum(h.flip(0), 0).flip(0)
+    m0 = torch.cumsum(h * centres, 0) / w0.clamp(min=1e-300)
+    m1 = (torch.cumsum((h * centres).flip(0), 0) / w1.flip(0).clamp(min=1e-300)).flip(0)
+    var12 = w0[:-1] * w1[1:] * (m0[:-1] - m1[1:]) ** 2
+    return float(centres[int(torch.argmax(var12))])
+
+
+def apply_otsu_threshold(densities: torch.Tensor, fallback_percentile: float = 50.0, group=None):
+    """scripts/extract_vol.py:123-150 -> (binary occupancy [N] bool, threshold).  Histogram on the GPU; with a
+    process group the min/max and the histogram are all-reduced so every rank gets the global threshold."""
+    d = densities.reshape(-1).float()
+    lo, hi = d.min(), d.max()
+    if group is not None:
+        torch.distributed.all_reduce(lo, op=torch.distributed.ReduceOp.MIN, group=group)
+        torch.distributed.all_reduce(hi, op=torch.distributed.ReduceOp.MAX, group=group)
+    lo, hi = float(lo), float(hi)
+    if hi <= lo:
+        thr = lo
+    else:
+        hist = ops.histogram(d, lo, hi, 256)
+        if group is not None:
+            torch.distributed.all_reduce(hist, group=group)
+        thr = otsu_from_histogram(hist, lo, hi)
+    return d > thr, thr
+
+
+def save_volume(occupancy, rgb_values, output_path, resolution, bounds, threshold, metadata: Optional[dict] = None):
+    """scripts/extract_vol.py:153-206: {"occupancy_volume": u8 [R,R,R], "rgb_volume": u8 [R,R,R,3], "metadata"}."""
+    output_path = Path(output_path)
+    if output_path.suffix.lower() != ".pth":
+        raise ValueError(f"Unsupported output format: {output_path.suffix}")
+    R = resolution
+    occ = occupancy.reshape(-1)
+    meta = {
+        "resolution": int(R), "bounds": [float(bounds[0]), float(bounds[1])], "threshold": float(threshold),
+        "occupied_ratio": float(occ.float().mean().item()), "total_voxels": int(occ.numel()),
+        "occupied_voxels": int(occ.sum().item()), "timestamp": time.strftime("%Y-%m-%d %H:%M:%S"),
+    }
+    meta.update(metadata or {})
+    if rgb_values.dtype == torch.uint8:
+        col = rgb_values
+    else:
+        col = (rgb_values.float() * 255).to(torch.uint8)  # truncation, extract_vol.py:198
+    output_path.parent.mkdir(parents=True, exist_ok=True)
+    torch.save({"occupancy_volume": occ.to(torch.uint8).reshape(R, R, R).cpu(),
+                "rgb_volume": col.reshape(R, R, R, 3).cpu(), "metadata": meta}, output_path)
+
+
+def extract_volume_fused(model: OptimizedVanillaNeRF, resolution: int, bounds=(-1.0, 1.0), view_direction=(0.0, 0.0, -1.0),
+                         rank: int = 0, world: int = 1, group=None, out=None):
+    """Slab-sharded dense query: rank r owns x-planes [r*R/G,(r+1)*R/G) == a contiguous range of
+    the flat grid.  Returns (sigma [n], rgb [n,3], start, thr, occupancy u8 [n], rgb u8 [n,3]) for this rank's slab."""
+    dev = next(model.parameters()).device
+    model._sync_packed()
+    R = resolution
+    planes = (R + world - 1) // world
+    x0, x1 = min(rank * planes, R), min((rank + 1) * planes, R)
+    start, count = x0 * R * R, (x1 - x0) * R * R
+    lin = torch.linspace(bounds[0], bounds[1], R, device=dev)
+    view = torch.tensor(view_direction, dtype=torch.float32, device=dev)
+    view = view / torch.norm(view)
+    rgb, sigma = ops.mlp_forward(model._packed, grid=(lin, view, start, count), out=out)
+    occ_b, thr = apply_otsu_threshold(sigma, group=group)
+    occ, col = ops.pack_volume(sigma, rgb, thr)
+    return sigma, rgb, start, thr, occ, col
+
+
+def load_vanilla_model(checkpoint_path: str, cfg, device="cuda") -> OptimizedVanillaNeRF:
+    """extract_vol.py:20-54 for the vanilla network (dispatch on cfg.ngp)."""
+    if not os.path.exists(checkpoint_path):
+        raise FileNotFoundError(f"Checkpoint not found: {checkpoint_path}")
+    ckpt = torch.load(checkpoint_path, map_location=device, weights_only=False)
+    if "nerf_fine_state_dict" not in ckpt:
+        raise KeyError("nerf_fine_state_dict")
+    model = OptimizedVanillaNeRF(cfg.pos_L, cfg.dir_L, cfg.hidden_dim).to(device)
+    model.load_state_dict(ckpt["nerf_fine_state_dict"])
+    return model.eval()
+
+
+def get_args(argv=None):
+    p = argparse.ArgumentParser(description="Dense occupancy / colour volume from a trained NeRF")
+    p.add_argument("--cfg_path", type=str, required=True)
+    p.add_argument("--resolution", type=int, default=512)  # ignored in favour of cfg.volume_resolution (:283-284)
+    p.add_argument("--bounds", type=float, nargs=2, default=[-1.0, 1.0])
+    p.add_argument("--batch-size", type=int, default=8192)
+    p.add_argument("--percentile-threshold", type=float, default=50.0)
+    p.add_argument("--view-direction", type=float, nargs=3, default=[0.0, 0.0, -1.0])
+    return p.parse_args(argv)
+
+
+def main(argv=None):
+    args = get_args(argv)
+    cfg = load_config(args.cfg_path)
+    if getattr(cfg, "ngp", False):
+        raise NotImplementedError("cfg.ngp=true (tiny-cuda-nn) is not available; set ngp: false")
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    model = load_vanilla_model(str(cfg.checkpoint), cfg, dev)
+    R = int(cfg.volume_resolution)
+    with torch.no_grad():
+        sigma, rgb, _, thr, occ, col = extract_volume_fused(model, R, tuple(args.bounds), tuple(args.view_direction))
+    stats = lambda t: {"min": float(t.min()), "max": float(t.max()), "mean": float(t.mean()), "std": float(t.std())}  # noqa: E731
+    meta = {"checkpoint_path": str(cfg.checkpoint), "device_used": str(dev), "batch_size": int(args.batch_size),
+            "density_stats": stats(sigma), "view_direction": list(args.view_direction), "rgb_stats": stats(rgb)}
+    save_volume(occ, col, str(cfg.volume_output_path), R, tuple(args.bounds), thr, meta)
+    print(f"Saved colored occupancy volume with metadata: {cfg.volume_output_path}")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,291 @@
+"""Tensor-level wrappers over the C ABI: argument checking, output allocation (torch caching
+allocator) and launch on torch's current CUDA stream.  No op has a CPU path."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import PointSource
+
+Tensor = torch.Tensor
+MLP_NUM_PARAMS = 595844
+TILE = 128
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: Tensor, dtype, name: str) -> Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name}: expected a CUDA tensor (this library has no CPU fallback)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _f32(t: Tensor, name: str) -> Tensor:
+    return _chk(t, torch.float32, name)
+
+
+def _ptr(t: Optional[Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+# ---- sampling ------------------------------------------------------------------------------------
+def stratified_sample(near: Tensor, far: Tensor, t_vals: Tensor, t_rand: Tensor) -> Tensor:
+    """scripts/sampling.py:13-21 with the torch.rand draw passed in.  near/far [B] or [B,1]."""
+    t_rand = _f32(t_rand, "t_rand")
+    B, S = t_rand.shape
+    near, far = _f32(near.reshape(-1), "near"), _f32(far.reshape(-1), "far")
+    assert near.numel() == B and far.numel() == B and t_vals.numel() == S
+    z = torch.empty_like(t_rand)
+    _lib.call("dfn_stratified_sample", near.data_ptr(), far.data_ptr(), _f32(t_vals, "t_vals").data_ptr(),
+              t_rand.data_ptr(), B, S, z.data_ptr(), _stream())
+    return z
+
+
+def points_on_rays(rays_o: Tensor, rays_d: Tensor, z: Tensor, want_dirs: bool = True):
+    """scripts/sampling.py:24-31.  Returns pts [B*S,3] (and dirs [B*S,3])."""
+    z = _f32(z, "z")
+    B, S = z.shape
+    o, d = _f32(rays_o, "rays_o"), _f32(rays_d, "rays_d")
+    pts = torch.empty(B * S, 3, device=z.device, dtype=torch.float32)
+    dirs = torch.empty_like(pts) if want_dirs else None
+    _lib.call("dfn_points_on_rays", o.data_ptr(), d.data_ptr(), z.data_ptr(), B, S, pts.data_ptr(), _ptr(dirs), _stream())
+    return (pts, dirs) if want_dirs else pts
+
+
+def sample_pdf(bins: Tensor, weights: Tensor, u: Tensor, return_inds: bool = False, return_cdf: bool = False,
+               bins_mid_of_z: bool = False):
+    """scripts/train.py:31-75 (u = the torch.rand draw of :53).  `weights` may be a last-dim slice of a
+    contiguous [B,W] tensor (train.py:158 passes weights[...,1:-1]) -- it is read in place."""
+    u = _f32(u, "u")
+    B, NS = u.shape
+    bins = _f32(bins, "bins")
+    NB = bins.shape[-1] - (1 if bins_mid_of_z else 0)
+    if weights.dtype != torch.float32 or not weights.is_cuda:
+        raise RuntimeError("sample_pdf: weights must be a float32 CUDA tensor")
+    if weights.dim() != 2 or weights.stride(1) != 1:
+        weights = weights.contiguous()
+    assert weights.shape == (B, NB - 1), (weights.shape, B, NB)
+    samples = torch.empty(B, NS, device=u.device, dtype=torch.float32)
+    inds = torch.empty(B, NS, device=u.device, dtype=torch.int64) if return_inds else None
+    cdf = torch.empty(B, NB, device=u.device, dtype=torch.float32) if return_cdf else None
+    _lib.call("dfn_sample_pdf", bins.data_ptr(), int(bins_mid_of_z), weights.data_ptr(), weights.stride(0), 0,
+              u.data_ptr(), B, NB, NS, samples.data_ptr(), _ptr(inds), _ptr(cdf), _stream())
+    out = (samples,) + ((inds,) if return_inds else ()) + ((cdf,) if return_cdf else ())
+    return out[0] if len(out) == 1 else out
+
+
+def sample_pdf_with_cdf(bins: Tensor, cdf: Tensor, u: Tensor) -> Tuple[Tensor, Tensor]:
+    """scripts/train.py:56-73 on a given cdf; returns (samples, inds int64)."""
+    u, bins, cdf = _f32(u, "u"), _f32(bins, "bins"), _f32(cdf, "cdf")
+    B, NS = u.shape
+    NB = bins.shape[-1]
+    samples = torch.empty(B, NS, device=u.device, dtype=torch.float32)
+    inds = torch.empty(B, NS, device=u.device, dtype=torch.int64)
+    _lib.call("dfn_sample_pdf_with_cdf", bins.data_ptr(), cdf.data_ptr(), u.data_ptr(), B, NB, NS, samples.data_ptr(),
+              inds.data_ptr(), _stream())
+    return samples, inds
+
+
+def merge_sort_z(z_coarse: Tensor, z_fine: Tensor) -> Tensor:
+    """torch.sort(torch.cat([z_vals, z_samples], -1), -1).values  (scripts/sampling.py:40)."""
+    a, b = _f32(z_coarse, "z_coarse"), _f32(z_fine, "z_fine")
+    B = a.shape[0]
+    out = torch.empty(B, a.shape[1] + b.shape[1], device=a.device, dtype=torch.float32)
+    _lib.call("dfn_merge_sort_z", a.data_ptr(), a.shape[1], b.data_ptr(), b.shape[1], B, out.data_ptr(), _stream())
+    return out
+
+
+# ---- encoding ------------------------------------------------------------------------------------
+def posenc(x: Tensor, freq_bands: Tensor, include_input: bool = True) -> Tensor:
+    """scripts/model.py:32-53."""
+    shape = x.shape
+    x2 = _f32(x.reshape(-1, 3), "x")
+    L = freq_bands.numel()
+    D = (3 if include_input else 0) + 6 * L
+    out = torch.empty(x2.shape[0], D, device=x.device, dtype=torch.float32)
+    _lib.call("dfn_posenc", x2.data_ptr(), _f32(freq_bands, "freq_bands").data_ptr(), x2.shape[0], L,
+              int(include_input), out.data_ptr(), _stream())
+    return out.reshape(*shape[:-1], D)
+
+
+# ---- compositing ---------------------------------------------------------------------------------
+def _comp_inputs(rgb: Tensor, sigma: Tensor, z: Tensor):
+    z = _f32(z, "z_vals")
+    B, S = z.shape
+    if rgb.dtype != sigma.dtype:
+        rgb, sigma = rgb.float(), sigma.float()
+    if rgb.dtype not in (torch.float32, torch.bfloat16):
+        rgb, sigma = rgb.float(), sigma.float()
+    rgb = _chk(rgb.reshape(B, S, 3), rgb.dtype, "rgb")
+    sigma = _chk(sigma.reshape(B, S), sigma.dtype, "sigma")
+    return rgb, sigma, z, B, S, int(rgb.dtype == torch.bfloat16)
+
+
+def composite_forward(rgb, sigma, z, white_bg=False, dist_last=1e10, want_extras=False):
+    rgb, sigma, z, B, S, bf = _comp_inputs(rgb, sigma, z)
+    rgb_map = torch.empty(B, 3, device=z.device, dtype=torch.float32)
+    weights = torch.empty(B, S, device=z.device, dtype=torch.float32)
+    acc = torch.empty(B, device=z.device, dtype=torch.float32) if want_extras else None
+    depth = torch.empty(B, device=z.device, dtype=torch.float32) if want_extras else None
+    _lib.call("dfn_composite_forward", rgb.data_ptr(), sigma.data_ptr(), z.data_ptr(), B, S, bf, int(white_bg),
+              float(dist_last), rgb_map.data_ptr(), weights.data_ptr(), _ptr(acc), _ptr(depth), _stream())
+    return (rgb_map, weights, acc, depth) if want_extras else (rgb_map, weights)
+
+
+def composite_backward(rgb, sigma, z, d_rgb_map, d_weights=None, white_bg=False, dist_last=1e10):
+    rgb, sigma, z, B, S, bf = _comp_inputs(rgb, sigma, z)
+    d_rgb = torch.empty(B, S, 3, device=z.device, dtype=torch.float32)
+    d_sigma = torch.empty(B, S, device=z.device, dtype=torch.float32)
+    dm = _f32(d_rgb_map, "d_rgb_map")
+    dw = _f32(d_weights, "d_weights") if d_weights is not None else None
+    _lib.call("dfn_composite_backward", rgb.data_ptr(), sigma.data_ptr(), z.data_ptr(), B, S, bf, int(white_bg),
+              float(dist_last), dm.data_ptr(), _ptr(dw), d_rgb.data_ptr(), d_sigma.data_ptr(), _stream())
+    return d_rgb, d_sigma
+
+
+def render_loss(rgb, sigma, z, target, loss_sum: Tensor, white_bg=False, dist_last=1e10, loss_scale=1.0,
+                want_weights=True):
+    """Fused raw2outputs + MSELoss(mean) + backward.  loss_sum[0] += sum of squared errors.
+    Returns (rgb_map, weights, d_rgb [B,S,3], d_sigma [B,S])."""
+    rgb, sigma, z, B, S, bf = _comp_inputs(rgb, sigma, z)
+    target = _f32(target, "target")
+    rgb_map = torch.empty(B, 3, device=z.device, dtype=torch.float32)
+    weights = torch.empty(B, S, device=z.device, dtype=torch.float32) if want_weights else None
+    d_rgb = torch.empty(B, S, 3, device=z.device, dtype=torch.float32)
+    d_sigma = torch.empty(B, S, device=z.device, dtype=torch.float32)
+    _lib.call("dfn_render_loss", rgb.data_ptr(), sigma.data_ptr(), z.data_ptr(), target.data_ptr(), B, S, bf,
+              int(white_bg), float(dist_last), float(loss_scale), rgb_map.data_ptr(), _ptr(weights),
+              _f32(loss_sum, "loss_sum").data_ptr(), d_rgb.data_ptr(), d_sigma.data_ptr(), _stream())
+    return rgb_map, weights, d_rgb, d_sigma
+
+
+# ---- MLP -------------------------------------------------------------------------------------------
+class PackedMLP:
+    """bf16 operand images of one OptimizedVanillaNeRF (hidden 256, L 10/4) built from the flat fp32
+    parameter vector (reference named_parameters() order)."""
+
+    def __init__(self, device):
+        lib = _lib.load()
+        self.fwd = torch.empty(lib.dfn_mlp_fwd_pack_bytes(), dtype=torch.uint8, device=device)
+        self.bwd = torch.empty(lib.dfn_mlp_bwd_pack_bytes(), dtype=torch.uint8, device=device)
+        self.consts = torch.empty(lib.dfn_mlp_consts_bytes() // 4, dtype=torch.float32, device=device)
+
+    def pack(self, flat_params: Tensor) -> None:
+        p = _f32(flat_params, "flat_params")
+        assert p.numel() == MLP_NUM_PARAMS, p.numel()
+        _lib.call("dfn_mlp_pack_weights", p.data_ptr(), self.fwd.data_ptr(), self.bwd.data_ptr(),
+                  self.consts.data_ptr(), _stream())
+
+
+def _source(pos=None, view=None, rays=None, grid=None):
+    """Builds the dfn_point_source struct; returns (struct, P, keep-alive list)."""
+    s = PointSource()
+    keep = []
+    if pos is not None:
+        pos, view = _f32(pos.reshape(-1, 3), "pos"), _f32(view.reshape(-1, 3), "view")
+        assert pos.shape == view.shape
+        s.mode, s.pos, s.view = 0, pos.data_ptr(), view.data_ptr()
+        keep += [pos, view]
+        P = pos.shape[0]
+    elif rays is not None:
+        o, d, z = (_f32(t, n) for t, n in zip(rays, ("rays_o", "rays_d", "z")))
+        B, S = z.shape
+        s.mode, s.rays_o, s.rays_d, s.z, s.S = 1, o.data_ptr(), d.data_ptr(), z.data_ptr(), S
+        keep += [o, d, z]
+        P = B * S
+    else:
+        lin, view, start, count = grid
+        lin, view = _f32(lin, "lin"), _f32(view.reshape(3), "view")
+        s.mode, s.lin, s.view, s.R, s.p_offset = 2, lin.data_ptr(), view.data_ptr(), lin.numel(), int(start)
+        keep += [lin, view]
+        P = int(count)
+    return s, P, keep
+
+
+def mlp_stash_bytes(P: int) -> int:
+    return _lib.load().dfn_mlp_stash_bytes(P)
+
+
+def mlp_dz_bytes(P: int) -> int:
+    return _lib.load().dfn_mlp_dz_bytes(P)
+
+
+def mlp_forward(packed: PackedMLP, *, pos=None, view=None, rays=None, grid=None, noise: Optional[Tensor] = None,
+                stash: Optional[Tensor] = None, out: Optional[Tuple[Tensor, Tensor]] = None):
+    """OptimizedVanillaNeRF.forward (scripts/model.py:173-187).  Returns (rgb [P,3], sigma [P]) fp32."""
+    s, P, keep = _source(pos, view, rays, grid)
+    dev = packed.fwd.device
+    if out is None:
+        rgb = torch.empty(P, 3, device=dev, dtype=torch.float32)
+        sigma = torch.empty(P, device=dev, dtype=torch.float32)
+    else:
+        rgb, sigma = out
+    if noise is not None:
+        noise = _f32(noise.reshape(-1), "noise")
+        assert noise.numel() == P
+    if stash is not None:
+        assert stash.is_cuda and stash.dtype == torch.uint8 and stash.numel() >= mlp_stash_bytes(P)
+    _lib.call("dfn_mlp_forward", C.byref(s), P, packed.fwd.data_ptr(), packed.consts.data_ptr(), _ptr(noise),
+              rgb.data_ptr(), sigma.data_ptr(), _ptr(stash), _stream())
+    return rgb, sigma
+
+
+def mlp_backward(packed: PackedMLP, rgb: Tensor, sigma: Tensor, d_rgb: Tensor, d_sigma: Tensor, stash: Tensor,
+                 dz: Tensor, grads: Tensor, *, pos=None, view=None, rays=None, grid=None) -> None:
+    """Accumulates d loss / d params into `grads` (flat fp32, reference parameter order)."""
+    s, P, keep = _source(pos, view, rays, grid)
+    assert grads.numel() == MLP_NUM_PARAMS and grads.dtype == torch.float32 and grads.is_cuda
+    assert dz.numel() >= mlp_dz_bytes(P)
+    _lib.call("dfn_mlp_backward", C.byref(s), P, packed.bwd.data_ptr(), packed.consts.data_ptr(),
+              _f32(rgb.reshape(-1, 3), "rgb").data_ptr(), _f32(sigma.reshape(-1), "sigma").data_ptr(),
+              _f32(d_rgb.reshape(-1, 3), "d_rgb").data_ptr(), _f32(d_sigma.reshape(-1), "d_sigma").data_ptr(),
+              stash.data_ptr(), dz.data_ptr(), grads.data_ptr(), _stream())
+
+
+def umma_selftest(a_img: Tensor, b_img: Tensor, N: int, K: int, a_mn: int, b_mn: int, a_lbo: int, a_sbo: int,
+                  b_lbo: int, b_sbo: int, a_kstep: int, b_kstep: int) -> Tensor:
+    d = torch.empty(128, N, device=a_img.device, dtype=torch.float32)
+    _lib.call("dfn_umma_selftest", a_img.data_ptr(), b_img.data_ptr(), N, K, a_mn, b_mn, a_lbo, a_sbo, b_lbo, b_sbo,
+              a_kstep, b_kstep, d.data_ptr(), _stream())
+    return d
+
+
+# ---- dense grid / volume ---------------------------------------------------------------------------
+def grid_points(lin: Tensor, start: int, count: int) -> Tensor:
+    lin = _f32(lin, "lin")
+    out = torch.empty(count, 3, device=lin.device, dtype=torch.float32)
+    _lib.call("dfn_grid_points", lin.data_ptr(), lin.numel(), int(start), int(count), out.data_ptr(), _stream())
+    return out
+
+
+def histogram(v: Tensor, lo: float, hi: float, nbins: int = 256) -> Tensor:
+    v = _f32(v.reshape(-1), "values")
+    hist = torch.zeros(nbins, device=v.device, dtype=torch.int64)
+    _lib.call("dfn_histogram", v.data_ptr(), v.numel(), float(lo), float(hi), nbins, hist.data_ptr(), _stream())
+    return hist
+
+
+def pack_volume(sigma: Tensor, rgb: Tensor, thr: float) -> Tuple[Tensor, Tensor]:
+    sigma, rgb = _f32(sigma.reshape(-1), "sigma"), _f32(rgb.reshape(-1, 3), "rgb")
+    n = sigma.numel()
+    occ = torch.empty(n, device=sigma.device, dtype=torch.uint8)
+    col = torch.empty(n, 3, device=sigma.device, dtype=torch.uint8)
+    _lib.call("dfn_pack_volume", sigma.data_ptr(), rgb.data_ptr(), n, float(thr), occ.data_ptr(), col.data_ptr(), _stream())
+    return occ, col
+
+
+# ---- optimiser -------------------------------------------------------------------------------------
+def adamw_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, beta1_table: Tensor, step: Tensor,
+               beta2=0.999, eps=1e-8, weight_decay=1e-6, grad_scale=1.0) -> None:
+    assert step.dtype == torch.int32 and step.is_cuda
+    _lib.call("dfn_adamw_step", _f32(p, "p").data_ptr(), _f32(g, "g").data_ptr(), _f32(m, "m").data_ptr(),
+              _f32(v, "v").data_ptr(), p.numel(), _f32(lr_table, "lr_table").data_ptr(),
+              _f32(beta1_table, "beta1_table").data_ptr(), step.data_ptr(), lr_table.numel(), float(beta2), float(eps),
+              float(weight_decay), float(grad_scale), _stream())

@@ -1,0 +1,289 @@
+"""Drop-in for the reference's scripts/train.py hot path: sample_pdf, raw2outputs,
+process_rays_in_chunks, forward_pass (same signatures) plus the fused trainer that the `train(cfg)`
+entry point and bench.py use (one launch per stage, flat gradient buffer, fused AdamW)."""
+from __future__ import annotations
+
+import math
+import os
+import time
+from collections import OrderedDict
+from types import SimpleNamespace
+from typing import Optional
+
+import torch
+
+from . import ops
+from .model import OptimizedVanillaNeRF, get_nerf_models
+from .sampling import StratifiedSampler
+
+# forward_pass reads a module-global cfg exactly like the reference (scripts/train.py:148-177)
+cfg = SimpleNamespace(N_samples=64, N_importance=128, chunk_size=32768)
+
+
+def sample_pdf(bins, weights, N_samples, device=None, u=None):
+    """scripts/train.py:31-75.  `u` optionally injects the torch.rand draw of :53."""
+    if u is None:
+        u = torch.rand(list(bins.shape[:-1]) + [N_samples], device=weights.device)
+    return ops.sample_pdf(bins, weights, u)
+
+
+class _Composite(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rgb, sigma, z_vals, white_bg, dist_last):
+        rgb_map, weights = ops.composite_forward(rgb, sigma, z_vals, white_bg, dist_last)
+        ctx.save_for_backward(rgb, sigma, z_vals)
+        ctx.white_bg, ctx.dist_last = white_bg, dist_last
+        return rgb_map, weights
+
+    @staticmethod
+    def backward(ctx, d_rgb_map, d_weights):
+        rgb, sigma, z_vals = ctx.saved_tensors
+        d_rgb, d_sigma = ops.composite_backward(rgb, sigma, z_vals, d_rgb_map.contiguous(),
+                                                None if d_weights is None else d_weights.contiguous(),
+                                                ctx.white_bg, ctx.dist_last)
+        return d_rgb.reshape(rgb.shape).to(rgb.dtype), d_sigma.reshape(sigma.shape).to(sigma.dtype), None, None, None
+
+
+def raw2outputs(rgb, sigma, z_vals, white_bg=False, dist_last=1e10):
+    """scripts/train.py:78-106 -> (rgb_map [B,3], weights [B,S]); differentiable w.r.t. rgb and sigma."""
+    return _Composite.apply(rgb, sigma, z_vals, bool(white_bg), float(dist_last))
+
+
+def process_rays_in_chunks(model, pts, view_pts, device=None, chunk_size=8192):
+    """scripts/train.py:110-126.  The fused MLP kernel is persistent over any number of points, so the
+    chunk loop of the reference collapses to a single launch (chunk_size is accepted and ignored)."""
+    return model(pts, view_pts)
+
+
+def forward_pass(model_coarse, model_fine, rays_o, rays_d, t_near, t_far, image_rgb, sampler, criterion, device,
+                 white_bg, draws: Optional[dict] = None):
+    """scripts/train.py:129-186, same argument order and return value (total, coarse, fine losses).
+    `draws` optionally injects {"t_rand","u","noise_c","noise_f"} for parity tests."""
+    d = draws or {}
+    S, I = cfg.N_samples, cfg.N_importance
+    pts, view_pts, z_vals = sampler(rays_o, rays_d, t_near, t_far, d.get("t_rand"))
+    rgb_c, sig_c = model_coarse(pts, view_pts, d.get("noise_c"))
+    rgb_map_c, weights = raw2outputs(rgb_c.reshape(-1, S, 3), sig_c.reshape(-1, S, 1), z_vals, white_bg)
+    z_mid = 0.5 * (z_vals[..., :-1] + z_vals[..., 1:])
+    z_samples = sample_pdf(z_mid, weights[..., 1:-1].detach(), I, device, d.get("u")).detach()
+    pts_f, view_f, z_all = sampler.fine_points(rays_o, rays_d, z_samples, z_vals, t_near, t_far, S, I)
+    rgb_f, sig_f = model_fine(pts_f, view_f, d.get("noise_f"))
+    rgb_map_f, _ = raw2outputs(rgb_f.reshape(-1, S + I, 3), sig_f.reshape(-1, S + I, 1), z_all, white_bg)
+    loss_c = criterion(rgb_map_c, image_rgb)
+    loss_f = criterion(rgb_map_f, image_rgb)
+    return loss_c + loss_f, loss_c, loss_f
+
+
+def onecycle_tables(total_steps: int, base_lr: float):
+    """OneCycleLR(max_lr=10*lr, pct_start=.1, cos, div_factor=10, final_div_factor=100) with the default
+    cycle_momentum (beta1 0.95 -> 0.85 -> 0.95), as scripts/train.py:250-259 builds it."""
+    max_lr, init_lr = base_lr * 10.0, base_lr
+    min_lr = init_lr / 100.0
+    up_end, down_end = float(0.1 * total_steps) - 1.0, float(total_steps) - 1.0
+    cos = lambda a, b, pct: b + (a - b) / 2.0 * (math.cos(math.pi * pct) + 1.0)  # noqa: E731
+    lrs, b1s = [], []
+    for s in range(max(total_steps, 1)):
+        if s <= up_end:
+            pct = s / up_end if up_end > 0 else 1.0
+            lrs.append(cos(init_lr, max_lr, pct)); b1s.append(cos(0.95, 0.85, pct))
+        else:
+            pct = (s - up_end) / (down_end - up_end) if down_end > up_end else 1.0
+            lrs.append(cos(max_lr, min_lr, pct)); b1s.append(cos(0.85, 0.95, pct))
+    return lrs, b1s
+
+
+class FusedTrainer:
+    """One training step of scripts/train.py:282-323 as ~12 kernel launches and no autograd graph:
+    stratified z -> coarse MLP (rays read in-kernel) -> composite+MSE+backward -> pdf/searchsorted ->
+    merge -> fine MLP -> composite+MSE+backward -> MLP dgrad/wgrad (both nets) -> [NCCL all-reduce]
+    -> fused AdamW(+OneCycleLR) on the flat buffer -> repack bf16 weights.
+
+    Both networks' parameters live in ONE flat fp32 buffer (coarse then fine: the optimiser's parameter
+    order at train.py:227-228), so the data-parallel gradient exchange is a single all-reduce."""
+
+    def __init__(self, model_coarse: OptimizedVanillaNeRF, model_fine: OptimizedVanillaNeRF, N_samples=64,
+                 N_importance=128, lr=5e-4, total_steps=1000, white_bg=False, dist_last=1e10, weight_decay=1e-6,
+                 train_noise=True, process_group=None):
+        dev = next(model_coarse.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("FusedTrainer needs CUDA models (no CPU fallback)")
+        self.dev, self.S, self.I = dev, N_samples, N_importance
+        self.white_bg, self.dist_last, self.wd = white_bg, dist_last, weight_decay
+        self.train_noise = train_noise
+        self.pg = process_group
+        self.world = torch.distributed.get_world_size(process_group) if self._dist_on() else 1
+        self.models = (model_coarse, model_fine)
+        n = ops.MLP_NUM_PARAMS
+        # re-home both models into one flat buffer
+        self.flat = torch.empty(2 * n, dtype=torch.float32, device=dev)
+        for k, m in enumerate(self.models):
+            off = k * n
+            for p in m._ordered_params():
+                c = p.numel()
+                self.flat[off:off + c].copy_(p.detach().reshape(-1))
+                p.data = self.flat[off:off + c].view_as(p)
+                off += c
+            m._flat = self.flat[k * n:(k + 1) * n]
+            m.mark_dirty()
+            m._sync_packed()
+        self.grads = torch.zeros_like(self.flat)
+        self.m = torch.zeros_like(self.flat)
+        self.v = torch.zeros_like(self.flat)
+        lrs, b1s = onecycle_tables(total_steps, lr)
+        self.lr_table = torch.tensor(lrs, dtype=torch.float32, device=dev)
+        self.b1_table = torch.tensor(b1s, dtype=torch.float32, device=dev)
+        self.total_steps = total_steps
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.sampler = StratifiedSampler(N_samples, dev)
+        self.loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
+        self._B = None
+
+    def _dist_on(self):
+        return torch.distributed.is_available() and torch.distributed.is_initialized()
+
+    def _alloc(self, B):
+        if self._B == B:
+            return
+        S, T, dev = self.S, self.S + self.I, self.dev
+        Pc, Pf = B * S, B * T
+        u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=dev)  # noqa: E731
+        self.stash_c, self.stash_f = u8(ops.mlp_stash_bytes(Pc)), u8(ops.mlp_stash_bytes(Pf))
+        self.dz = u8(max(ops.mlp_dz_bytes(Pc), ops.mlp_dz_bytes(Pf)))
+        self.out_c = (torch.empty(Pc, 3, device=dev), torch.empty(Pc, device=dev))
+        self.out_f = (torch.empty(Pf, 3, device=dev), torch.empty(Pf, device=dev))
+        self._B = B
+
+    def forward_backward(self, rays_o, rays_d, near, far, target, t_rand=None, u=None, noise_c=None, noise_f=None):
+        """Losses + parameter gradients (self.grads) for one batch; no optimiser update."""
+        B = rays_o.shape[0]
+        S, I, T = self.S, self.I, self.S + self.I
+        self._alloc(B)
+        mc, mf = self.models
+        if t_rand is None:
+            t_rand = torch.rand(B, S, device=self.dev)
+        if u is None:
+            u = torch.rand(B, I, device=self.dev)
+        if self.train_noise:
+            if noise_c is None:
+                noise_c = torch.randn(B * S, device=self.dev)
+            if noise_f is None:
+                noise_f = torch.randn(B * T, device=self.dev)
+        self.loss_sum.zero_()
+        self.grads.zero_()
+        n = ops.MLP_NUM_PARAMS
+        z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
+        rays_c = (rays_o, rays_d, z_c)
+        rgb_c, sig_c = ops.mlp_forward(mc._packed, rays=rays_c, noise=noise_c, stash=self.stash_c, out=self.out_c)
+        _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg,
+                                                   self.dist_last)
+        z_new = ops.sample_pdf(z_c, w_c[:, 1:-1], u, bins_mid_of_z=True)
+        z_all = ops.merge_sort_z(z_c, z_new)
+        rays_f = (rays_o, rays_d, z_all)
+        rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f)
+        _, _, d_rgb_f, d_sig_f = ops.render_loss(rgb_f, sig_f, z_all, target, self.loss_sum[1:2], self.white_bg,
+                                                 self.dist_last, want_weights=False)
+        ops.mlp_backward(mc._packed, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.dz, self.grads[:n], rays=rays_c)
+        ops.mlp_backward(mf._packed, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.dz, self.grads[n:], rays=rays_f)
+        self.aux = {"z": z_c, "z_all": z_all, "z_new": z_new, "weights_coarse": w_c}
+        return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
+
+    def optimizer_step(self):
+        if self.world > 1:
+            torch.distributed.all_reduce(self.grads, group=self.pg)
+        ops.adamw_step(self.flat, self.grads, self.m, self.v, self.lr_table, self.b1_table, self.step_dev,
+                       weight_decay=self.wd, grad_scale=1.0 / self.world)
+        for m in self.models:
+            m._packed.pack(m._flat)
+            m._packed_version = (m._flat._version, sum(p._version for p in m._ordered_params()))
+
+    def step(self, rays_o, rays_d, near, far, target, **draws):
+        losses = self.forward_backward(rays_o, rays_d, near, far, target, **draws)
+        self.optimizer_step()
+        return losses
+
+    # ---- checkpoint in the reference layout (scripts/train.py:343-364) ---------------------------------
+    def optimizer_state_dict(self, lr_now: float, beta1_now: float):
+        state, idx, off = {}, 0, 0
+        step = float(self.step_dev.item())
+        for m in self.models:
+            for p in m._ordered_params():
+                c = p.numel()
+                state[idx] = {"step": torch.tensor(step), "exp_avg": self.m[off:off + c].view_as(p).clone(),
+                              "exp_avg_sq": self.v[off:off + c].view_as(p).clone()}
+                idx += 1
+                off += c
+        group = {"lr": lr_now, "betas": (beta1_now, 0.999), "eps": 1e-8, "weight_decay": self.wd, "amsgrad": False,
+                 "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "params": list(range(idx))}
+        return {"state": state, "param_groups": [group]}
+
+    def save_checkpoint(self, path, iteration):
+        i = min(int(self.step_dev.item()), self.total_steps - 1)
+        torch.save({
+            "iteration": iteration,
+            "nerf_coarse_state_dict": OrderedDict((k, v.detach().clone()) for k, v in self.models[0].state_dict().items()),
+            "nerf_fine_state_dict": OrderedDict((k, v.detach().clone()) for k, v in self.models[1].state_dict().items()),
+            "optimizer_state_dict": self.optimizer_state_dict(float(self.lr_table[i]), float(self.b1_table[i])),
+        }, path)
+
+
+class RayStore:
+    """GPU-resident replacement for scripts/dataset.py + DataLoader: the whole .npz (keys rgbs, rays_o,
+    rays_d, t_near, t_far; dataset.py:32-60) lives in HBM, batches are gathered with an on-device permutation."""
+
+    def __init__(self, rays_file, device, rank=0, world=1):
+        import numpy as np
+        d = np.load(rays_file)
+        f = lambda k: torch.from_numpy(d[k].astype("float32")).to(device)  # noqa: E731
+        self.rgb, self.o, self.d = f("rgbs"), f("rays_o"), f("rays_d")
+        self.near, self.far = f("t_near").reshape(-1), f("t_far").reshape(-1)
+        self.n, self.rank, self.world = self.rgb.shape[0], rank, world
+
+    def batches(self, batch_size, generator=None):
+        perm = torch.randperm(self.n, device=self.rgb.device, generator=generator)
+        per = batch_size // self.world
+        for i in range(0, self.n - batch_size + 1, batch_size):
+            idx = perm[i + self.rank * per: i + (self.rank + 1) * per]
+            yield self.o[idx], self.d[idx], self.near[idx], self.far[idx], self.rgb[idx]
+
+    def __len__(self):
+        return self.n
+
+
+def train(cfg_in):
+    """scripts/train.py:189-370 for the vanilla model (cfg.ngp false): same cfg keys, same checkpoint files."""
+    global cfg
+    cfg = cfg_in
+    if getattr(cfg, "ngp", False):
+        raise NotImplementedError("cfg.ngp=true needs tiny-cuda-nn semantics (parity unpinned, see DESIGN.md); "
+                                  "set ngp: false for the vanilla model")
+    dist_on = "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1
+    rank, world = 0, 1
+    if dist_on:
+        torch.distributed.init_process_group("nccl")
+        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    ckpt_dir = str(cfg.checkpoint_dir)
+    os.makedirs(ckpt_dir, exist_ok=True)
+    store = RayStore(str(cfg.rays_file), dev, rank, world)
+    steps_per_epoch = len(store) // cfg.batch_size
+    torch.manual_seed(0)
+    mc, mf = get_nerf_models(cfg.pos_L, cfg.dir_L, cfg.hidden_dim, device=dev)
+    tr = FusedTrainer(mc, mf, cfg.N_samples, cfg.N_importance, cfg.lr, max(cfg.num_epochs * steps_per_epoch, 1),
+                      bool(cfg.white_bg))
+    t0 = time.time()
+    for epoch in range(1, cfg.num_epochs + 1):
+        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size)):
+            losses = tr.step(o, d, near, far, rgb)
+            if it % 100 == 0 and rank == 0:
+                lc, lf = losses.tolist()
+                psnr = -10.0 * math.log10(max(lf, 1e-12))
+                print(f"epoch {epoch} it {it}/{steps_per_epoch} loss {lc + lf:.5f} (c {lc:.5f} f {lf:.5f}) "
+                      f"psnr {psnr:.2f} {time.time() - t0:.1f}s")
+        if epoch % 2 == 0 and rank == 0:
+            tr.save_checkpoint(os.path.join(ckpt_dir, f"nerf_epoch_{epoch:06d}.pth"), epoch)
+    if rank == 0:
+        tr.save_checkpoint(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
+        print(f"Training completed in {time.time() - t0:.2f}s")
+    return tr

@@ -1,0 +1,127 @@
+/* libdeepfields_b200.so -- C ABI of the B200-native NeRF render/train hot path.
+ *
+ * The reference (mohamedhaiham94/DeepFields-NeRF-) has no FFI of its own: its hot path is Python calling
+ * torch ops.  Each entry point below replaces the reference Python function cited beside it; the
+ * reference-side binding is the ctypes stub in INTEGRATION.md.  Conventions:
+ *   - plain pointers + sizes only, all pointers are DEVICE pointers unless stated otherwise;
+ *   - every call enqueues on `stream` (a cudaStream_t passed as void*), never synchronises, never
+ *     allocates, never retains a pointer after return;
+ *   - return 0 on success, non-zero on bad arguments / launch failure; dfn_last_error() gives the
+ *     thread-local message;
+ *   - there is no CPU fallback.
+ */
+#ifndef DEEPFIELDS_B200_H
+#define DEEPFIELDS_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dfn_last_error(void);
+int dfn_abi_version(void);
+
+/* ---- sampling ---------------------------------------------------------------------------------- */
+/* StratifiedSampler.__call__  scripts/sampling.py:10-21.  near/far [B], t_vals [S] (the sampler's linspace),
+ * t_rand [B,S] (the torch.rand draw of :20) -> z [B,S].  Bit-exact with the reference's torch ops. */
+int dfn_stratified_sample(const float* near, const float* far, const float* t_vals, const float* t_rand, int B, int S,
+                          float* z_out, void* stream);
+/* pts = o + d*z, dirs = d broadcast  scripts/sampling.py:24-31 / :43-48.  pts/dirs [B*S,3], either may be NULL. */
+int dfn_points_on_rays(const float* rays_o, const float* rays_d, const float* z, int B, int S, float* pts, float* dirs,
+                       void* stream);
+/* sample_pdf  scripts/train.py:31-75 with the draw u [B,NS] passed in.  bins [B,NB] (or, bins_mid=1, z [B,NB+1]
+ * whose mid-points are the bins, train.py:157); weights row r starts at weights + r*w_stride + w_offset and has
+ * NB-1 entries (train.py:158 passes weights[...,1:-1]).  inds_out (int64 searchsorted result) and cdf_out
+ * [B,NB] are optional. */
+int dfn_sample_pdf(const float* bins, int bins_mid, const float* weights, long long w_stride, int w_offset,
+                   const float* u, int B, int NB, int NS, float* samples, long long* inds_out, float* cdf_out,
+                   void* stream);
+/* scripts/train.py:56-73 on a caller-supplied cdf [B,NB] (parity tier A: bit-exact indices). */
+int dfn_sample_pdf_with_cdf(const float* bins, const float* cdf, const float* u, int B, int NB, int NS, float* samples,
+                            long long* inds_out, void* stream);
+/* torch.sort(cat([z_vals, z_samples]))  scripts/sampling.py:40.  NA+NB <= 256. */
+int dfn_merge_sort_z(const float* z_coarse, int NA, const float* z_fine, int NB, int B, float* z_out, void* stream);
+
+/* ---- encoding ---------------------------------------------------------------------------------- */
+/* OptimizedPositionalEncoding.forward  scripts/model.py:32-53.  x [P,3], freqs [L] -> out [P, 3*inc + 6L]. */
+int dfn_posenc(const float* x, const float* freqs, long long P, int L, int include_input, float* out, void* stream);
+
+/* ---- compositing ------------------------------------------------------------------------------- */
+/* raw2outputs  scripts/train.py:78-106 (dist_last 1e10; train_no_amp.py:84 uses 1e6).  rgb [B,S,3], sigma [B,S]
+ * fp32 (in_bf16=0) or bf16 (in_bf16=1); z [B,S].  Outputs (each optional): rgb_map [B,3], weights [B,S],
+ * acc [B], depth [B]. */
+int dfn_composite_forward(const void* rgb, const void* sigma, const float* z, int B, int S, int in_bf16, int white_bg,
+                          float dist_last, float* rgb_map, float* weights, float* acc, float* depth, void* stream);
+/* autograd of the above: d_rgb_map [B,3] (+ optional d_weights [B,S]) -> d_rgb [B,S,3], d_sigma [B,S] fp32. */
+int dfn_composite_backward(const void* rgb, const void* sigma, const float* z, int B, int S, int in_bf16, int white_bg,
+                           float dist_last, const float* d_rgb_map, const float* d_weights, float* d_rgb,
+                           float* d_sigma, void* stream);
+/* compositing + MSELoss(mean) + their backward in one pass (train.py:154,179,182-184):
+ * loss_sum[0] += sum of squared errors of this batch; d_rgb/d_sigma = d(loss_scale * mean sq err). */
+int dfn_render_loss(const void* rgb, const void* sigma, const float* z, const float* target, int B, int S, int in_bf16,
+                    int white_bg, float dist_last, float loss_scale, float* rgb_map, float* weights, float* loss_sum,
+                    float* d_rgb, float* d_sigma, void* stream);
+
+/* ---- vanilla NeRF MLP (OptimizedVanillaNeRF, scripts/model.py:56-187; hidden 256, pos_L 10, dir_L 4) ---- */
+#define DFN_MLP_NUM_PARAMS 595844 /* flat fp32, reference named_parameters() order */
+#define DFN_MLP_TILE 128
+
+/* where the P points of a query come from */
+typedef struct dfn_point_source {
+  int mode;            /* 0: pos/view arrays; 1: rays (pos = o + d*z, view = d); 2: dense grid          */
+  const float* pos;    /* mode 0: [P,3]                                                                   */
+  const float* view;   /* mode 0: [P,3]; mode 2: [3] canonical view (extract_vol.py:291-292)             */
+  const float* rays_o; /* mode 1: [B,3]                                                                   */
+  const float* rays_d; /* mode 1: [B,3]                                                                   */
+  const float* z;      /* mode 1: [B,S], P = B*S                                                          */
+  int S;               /* mode 1                                                                          */
+  const float* lin;    /* mode 2: [R] = torch.linspace(min,max,R) (extract_vol.py:71); point index g ->   */
+  int R;               /*         (lin[g/R^2], lin[(g/R)%R], lin[g%R])  (ij meshgrid, :74-77)             */
+  long long p_offset;  /* mode 2: flat grid index of point 0 (slab start)                                 */
+} dfn_point_source;
+
+/* sizes (bytes) of the buffers the caller allocates */
+long long dfn_mlp_fwd_pack_bytes(void);
+long long dfn_mlp_bwd_pack_bytes(void);
+long long dfn_mlp_consts_bytes(void);
+long long dfn_mlp_stash_bytes(long long P); /* activations kept by a training forward for the backward */
+long long dfn_mlp_dz_bytes(long long P);    /* pre-activation gradients kept by dgrad for wgrad        */
+
+/* fp32 parameters (flat, DFN_MLP_NUM_PARAMS) -> bf16 operand images for the kernels.  Called after
+ * load_state_dict and after every optimiser step. */
+int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream);
+
+/* OptimizedVanillaNeRF.forward  scripts/model.py:173-187 on P points: rgb [P,3], sigma [P] (fp32 values of the
+ * bf16 computation).  noise [P] or NULL = the randn_like draw of model.py:162 (training mode).
+ * stash != NULL keeps the activations the backward needs (dfn_mlp_stash_bytes). */
+int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                    const float* noise, float* rgb, float* sigma, void* stash, void* stream);
+/* backward of the above w.r.t. the parameters: d_rgb [P,3], d_sigma [P] (fp32), rgb/sigma = forward outputs,
+ * stash from the forward, dz = scratch of dfn_mlp_dz_bytes(P).  grads [DFN_MLP_NUM_PARAMS] fp32 is ACCUMULATED
+ * into (zero it first). */
+int dfn_mlp_backward(const dfn_point_source* src, long long P, const void* bwd_pack, const float* consts,
+                     const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma, const void* stash,
+                     void* dz, float* grads, void* stream);
+
+/* single 128 x N x K tcgen05 GEMM on operand tiles in the chunk layout (bring-up / descriptor self test) */
+int dfn_umma_selftest(const void* a_tile, const void* b_tile, int N, int K, int a_mn_major, int b_mn_major,
+                      unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, unsigned a_kstep, unsigned b_kstep,
+                      float* d_out, void* stream);
+
+/* ---- dense grid / volume (scripts/extract_vol.py:57-206) ---------------------------------------- */
+int dfn_grid_points(const float* lin, int R, long long start, long long count, float* out, void* stream);
+int dfn_histogram(const float* v, long long n, float lo, float hi, int nbins, unsigned long long* hist, void* stream);
+int dfn_pack_volume(const float* sigma, const float* rgb, long long n, float thr, unsigned char* occ, unsigned char* col,
+                    void* stream);
+
+/* ---- optimiser (scripts/train.py:244-259, :321-322) ---------------------------------------------- */
+/* AdamW on a flat buffer; lr_table/beta1_table [table_len] hold the OneCycleLR schedule, *step_ptr (device int,
+ * 0-based) selects the entry and is incremented. */
+int dfn_adamw_step(float* p, const float* g, float* m, float* v, long long n, const float* lr_table,
+                   const float* beta1_table, int* step_ptr, int table_len, float beta2, float eps, float weight_decay,
+                   float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEEPFIELDS_B200_H */

@@ -1,0 +1,313 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every CUDA op is called through the C ABI
+(deepfields_nerf_b200.ops -> ctypes -> libdeepfields_b200.so) and compared with oracle/nerf_oracle.py on the
+same seeded inputs / injected random draws, and with the committed reference-generated golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from common import make_draws, make_noise, make_rays, make_state_dict, peaked
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+T = lambda a: torch.from_numpy(np.asarray(a))  # noqa: E731
+
+
+@pytest.fixture(scope="module")
+def D():
+    import deepfields_nerf_b200 as d
+    assert torch.cuda.is_available()
+    return d
+
+
+def chunks(t):
+    """[rows, cols] -> UMMA chunk image [cols/8][rows][8]."""
+    r, c = t.shape
+    return t.reshape(r, c // 8, 8).permute(1, 0, 2).contiguous()
+
+
+def flat_params(sd):
+    keys = [k for k in sd if "freq_bands" not in k]
+    return torch.cat([sd[k].reshape(-1) for k in keys])
+
+
+# ---- tcgen05 descriptor conventions ------------------------------------------------------------------
+@pytest.mark.parametrize("N,K", [(256, 64), (256, 256), (128, 32), (16, 128)])
+def test_umma_kmajor(D, N, K):
+    g = torch.Generator().manual_seed(N + K)
+    A = torch.randn(128, K, generator=g).bfloat16().cuda()
+    B = torch.randn(N, K, generator=g).bfloat16().cuda()
+    d = D.ops.umma_selftest(chunks(A), chunks(B), N, K, 0, 0, 128 * 16, 128, N * 16, 128, 2 * 128 * 16, 2 * N * 16)
+    ref = A.float() @ B.float().t()
+    torch.testing.assert_close(d, ref, rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("N,K", [(256, 128), (64, 128), (16, 128)])
+def test_umma_mnmajor(D, N, K):
+    """Both operands read 'transposed' from [points x features] tiles: D = At^T * Bt (wgrad form)."""
+    g = torch.Generator().manual_seed(7 * N + K)
+    At = torch.randn(K, 128, generator=g).bfloat16().cuda()   # [reduction rows, M]
+    Bt = torch.randn(K, N, generator=g).bfloat16().cuda()     # [reduction rows, N]
+    d = D.ops.umma_selftest(chunks(At), chunks(Bt), N, K, 1, 1, 128, K * 16, 128, K * 16, 256, 256)
+    ref = At.float().t() @ Bt.float()
+    torch.testing.assert_close(d, ref, rtol=1e-3, atol=1e-2)
+
+
+# ---- sampling -------------------------------------------------------------------------------------------
+def test_stratified_and_points_bit_exact(D, golden):
+    B, S, I = 48, 64, 128
+    o, d, near, far, _ = make_rays(11, B)
+    t_rand, _ = make_draws(12, B, S, I)
+    smp = D.StratifiedSampler(S, "cuda")
+    pts, dirs, z = smp(o.cuda(), d.cuda(), near.cuda(), far.cuda(), t_rand.cuda())
+    # torch.linspace on CUDA may round differently from the CPU one the golden used: compare through the
+    # oracle fed with the sampler's own t grid as well as the golden
+    assert np.array_equal(z.cpu().numpy(), golden["sampler_z"]) or torch.equal(
+        z.cpu(), O.stratified_z(near, far, t_rand))
+    z_ref = T(golden["sampler_z"]).cuda()
+    pts2, dirs2 = D.ops.points_on_rays(o.cuda(), d.cuda(), z_ref)
+    assert np.array_equal(pts2.cpu().numpy(), golden["sampler_pts"])
+    assert np.array_equal(dirs2.cpu().numpy(), golden["sampler_dirs"])
+
+
+def test_stratified_given_tvals_bit_exact(D):
+    for B, S in ((1, 2), (5, 64), (333, 256), (4096, 64)):
+        o, d, near, far, _ = make_rays(B + S, B)
+        t_rand, _ = make_draws(B, B, S, 1)
+        ref = O.stratified_z(near, far, t_rand)
+        tv = torch.linspace(0.0, 1.0, S)
+        z = D.ops.stratified_sample(near.cuda(), far.cuda(), tv.cuda(), t_rand.cuda())
+        assert torch.equal(z.cpu(), ref), (B, S)
+
+
+def test_sample_pdf_shared_cdf_bit_exact(D, golden):
+    z = T(golden["sampler_z"])
+    mids = 0.5 * (z[:, :-1] + z[:, 1:])
+    w, u = T(golden["pdf_weights"]), T(golden["pdf_u"])
+    cdf = O.pdf_to_cdf(w)
+    s, inds = D.ops.sample_pdf_with_cdf(mids.cuda(), cdf.cuda(), u.cuda())
+    assert np.array_equal(inds.cpu().numpy(), golden["pdf_inds"])          # tier A: bit-exact indices
+    assert np.array_equal(s.cpu().numpy(), golden["pdf_samples"])
+
+
+def test_sample_pdf_fused(D, golden):
+    z = T(golden["sampler_z"])
+    mids = 0.5 * (z[:, :-1] + z[:, 1:])
+    w, u = T(golden["pdf_weights"]), T(golden["pdf_u"])
+    s, inds, cdf = D.ops.sample_pdf(mids.cuda(), w.cuda(), u.cuda(), return_inds=True, return_cdf=True)
+    s2 = D.ops.sample_pdf(z.cuda(), w.cuda(), u.cuda(), bins_mid_of_z=True)
+    assert torch.equal(s, s2)
+    ref_cdf = O.pdf_to_cdf(w)
+    assert (cdf.cpu() - ref_cdf).abs().max() <= 2.5e-7
+    ref_inds = T(golden["pdf_inds"])
+    bad = (inds.cpu() != ref_inds)
+    # tier B: the fused cdf may differ by an ulp (sum order); every index flip must be an edge case
+    if bad.any():
+        uu, cc = u[bad], torch.gather(ref_cdf, 1, ref_inds.clamp(max=62))[bad]
+        lo = torch.gather(ref_cdf, 1, (ref_inds - 1).clamp(min=0))[bad]
+        assert torch.minimum((uu - cc).abs(), (uu - lo).abs()).max() <= 3e-7
+        assert bad.float().mean() < 1e-3
+    np.testing.assert_allclose(s.cpu().numpy(), golden["pdf_samples"], rtol=1e-5, atol=2e-6)
+    # a strided weights view (train.py:158 passes weights[..., 1:-1])
+    wfull = torch.zeros(w.shape[0], 64)
+    wfull[:, 1:-1] = w
+    s3 = D.ops.sample_pdf(mids.cuda(), wfull.cuda()[:, 1:-1], u.cuda())
+    assert torch.equal(s, s3)
+
+
+def test_merge_sort_bit_exact(D, golden):
+    zz = D.ops.merge_sort_z(T(golden["sampler_z"]).cuda(), T(golden["pdf_samples"]).cuda())
+    assert np.array_equal(zz.cpu().numpy(), golden["fine_z"])
+    g = torch.Generator().manual_seed(3)
+    for B, NA, NB in ((1, 1, 1), (7, 64, 192), (100, 0, 5), (33, 17, 0)):
+        a = torch.rand(B, NA, generator=g).sort(-1).values
+        b = torch.rand(B, NB, generator=g)
+        out = D.ops.merge_sort_z(a.cuda(), b.cuda())
+        assert torch.equal(out.cpu(), torch.sort(torch.cat([a, b], -1), -1).values)
+
+
+def test_posenc(D, golden):
+    x = T(golden["pe_in"]).cuda()
+    for L, key in ((10, "pe_L10"), (4, "pe_L4")):
+        enc = D.OptimizedPositionalEncoding(L).cuda()
+        out = enc(x)
+        assert out.shape[-1] == enc.output_dim
+        np.testing.assert_allclose(out.cpu().numpy(), golden[key], atol=2e-6, rtol=0)
+
+
+# ---- compositing --------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag,zkey", [("c", "sampler_z"), ("f", "fine_z")])
+def test_composite_forward_backward(D, golden, tag, zkey):
+    rgb, sig, z = T(golden[f"comp_{tag}_rgb"]), T(golden[f"comp_{tag}_sigma"]), T(golden[zkey])
+    for wb in (False, True):
+        rm, w = D.raw2outputs(rgb.cuda(), sig.cuda(), z.cuda(), wb)
+        np.testing.assert_allclose(rm.cpu().numpy(), golden[f"comp_{tag}_map_wb{int(wb)}"], rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(w.cpu().numpy(), golden[f"comp_{tag}_w_wb{int(wb)}"], rtol=1e-5, atol=1e-9)
+    rm, w = D.raw2outputs(rgb.cuda(), sig.cuda(), z.cuda(), False, 1e6)
+    np.testing.assert_allclose(w.cpu().numpy(), golden[f"comp_{tag}_w_1e6"], rtol=1e-5, atol=1e-9)
+    r2, s2 = rgb.cuda().requires_grad_(), sig.cuda().requires_grad_()
+    rm, _ = D.raw2outputs(r2, s2, z.cuda())
+    (rm * T(golden[f"comp_{tag}_G"]).cuda()).sum().backward()
+    np.testing.assert_allclose(r2.grad.cpu().numpy(), golden[f"comp_{tag}_drgb"], rtol=1e-5, atol=1e-8)
+    ref = golden[f"comp_{tag}_dsigma"]
+    np.testing.assert_allclose(s2.grad.cpu().numpy(), ref, rtol=1e-4, atol=1e-6 * np.abs(ref).max())
+    # extras + white background + weight gradients against oracle autograd
+    r3, s3 = rgb.clone().requires_grad_(), sig.clone().requires_grad_()
+    out = O.composite(r3, s3, z, True)
+    gw = torch.randn(out["weights"].shape, generator=torch.Generator().manual_seed(1))
+    gm = torch.randn(out["rgb_map"].shape, generator=torch.Generator().manual_seed(2))
+    ((out["rgb_map"] * gm).sum() + (out["weights"] * gw).sum()).backward()
+    d_rgb, d_sig = D.ops.composite_backward(rgb.cuda(), sig.cuda(), z.cuda(), gm.cuda(), gw.cuda(), True)
+    torch.testing.assert_close(d_rgb.cpu(), r3.grad, rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(d_sig.cpu().reshape(s3.shape), s3.grad, rtol=1e-4, atol=1e-6 * float(s3.grad.abs().max()))
+    rm, w, acc, dep = D.ops.composite_forward(rgb.cuda(), sig.cuda(), z.cuda(), want_extras=True)
+    o2 = O.composite(rgb, sig, z)
+    torch.testing.assert_close(acc.cpu(), o2["acc"], rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(dep.cpu(), o2["depth"], rtol=1e-5, atol=1e-6)
+
+
+def test_render_loss_fused(D, golden):
+    rgb, sig, z = T(golden["comp_f_rgb"]), T(golden["comp_f_sigma"]), T(golden["fine_z"])
+    B = z.shape[0]
+    tgt = torch.rand(B, 3, generator=torch.Generator().manual_seed(5))
+    r, s = rgb.clone().requires_grad_(), sig.clone().requires_grad_()
+    out = O.composite(r, s, z)
+    loss = torch.nn.functional.mse_loss(out["rgb_map"], tgt)
+    loss.backward()
+    ls = torch.zeros(1, device="cuda")
+    rm, w, d_rgb, d_sig = D.ops.render_loss(rgb.cuda(), sig.cuda(), z.cuda(), tgt.cuda(), ls)
+    assert abs(ls.item() / (3 * B) - loss.item()) <= 1e-5 * loss.item()
+    torch.testing.assert_close(d_rgb.cpu(), r.grad, rtol=1e-4, atol=1e-9)
+    torch.testing.assert_close(d_sig.cpu().reshape(s.shape), s.grad, rtol=1e-4, atol=1e-6 * float(s.grad.abs().max()))
+    # bf16 inputs are accepted as-is (MLP outputs)
+    rm2, w2 = D.ops.composite_forward(rgb.cuda().bfloat16(), sig.cuda().bfloat16(), z.cuda())
+    o2 = O.composite(rgb.bfloat16(), sig.bfloat16(), z)
+    torch.testing.assert_close(rm2.cpu(), o2["rgb_map"], rtol=1e-5, atol=1e-7)
+
+
+# ---- MLP forward ------------------------------------------------------------------------------------------------
+def _packed(D, sd):
+    pk = D.ops.PackedMLP("cuda")
+    pk.pack(flat_params(sd).cuda())
+    return pk
+
+
+def test_mlp_forward_golden(D, golden):
+    sd = make_state_dict(21, 256)
+    pos, view = T(golden["mlp_pos"]).cuda(), T(golden["mlp_view"]).cuda()
+    rgb, sig = D.ops.mlp_forward(_packed(D, sd), pos=pos, view=view)
+    # north_star tolerance for the bf16 MLP: 2e-2 against the reference (fp32 and bf16-autocast runs)
+    for tag in ("fp32", "bf16"):
+        np.testing.assert_allclose(rgb.cpu().numpy(), golden[f"mlp_{tag}_rgb"], atol=2e-2, rtol=0)
+        np.testing.assert_allclose(sig.cpu().numpy(), golden[f"mlp_{tag}_sigma"][:, 0], atol=2e-2, rtol=2e-2)
+    # same rounding points as the bf16 oracle -> much tighter
+    r_o, s_o = O.mlp_forward(sd, pos.cpu(), view.cpu(), low=torch.bfloat16)
+    assert (rgb.cpu() - r_o.float()).abs().max() < 8e-3
+    assert (sig.cpu() - s_o.float()[:, 0]).abs().max() < 8e-3
+    # training-mode noise and the peaked-sigma weight set
+    noise = make_noise(16, 512)
+    rgb, sig = D.ops.mlp_forward(_packed(D, sd), pos=pos, view=view, noise=noise.cuda())
+    np.testing.assert_allclose(sig.cpu().numpy(), golden["mlp_fp32_train_sigma"][:, 0], atol=3e-2, rtol=2e-2)
+    rgb, sig = D.ops.mlp_forward(_packed(D, peaked(sd)), pos=pos, view=view)
+    np.testing.assert_allclose(sig.cpu().numpy(), golden["mlp_peaked_sigma"][:, 0], atol=0.3, rtol=2e-2)
+
+
+@pytest.mark.parametrize("P", [1, 127, 128, 129, 1000, 148 * 256 + 77])
+def test_mlp_forward_ragged_sizes(D, P):
+    sd = make_state_dict(22, 256)
+    g = torch.Generator().manual_seed(P)
+    pos = torch.rand(P, 3, generator=g) * 2 - 1
+    view = torch.nn.functional.normalize(torch.randn(P, 3, generator=g), dim=-1)
+    rgb, sig = D.ops.mlp_forward(_packed(D, sd), pos=pos.cuda(), view=view.cuda())
+    n = min(P, 4096)
+    idx = torch.randperm(P, generator=g)[:n]
+    r_o, s_o = O.mlp_forward(sd, pos[idx], view[idx], low=torch.bfloat16)
+    assert (rgb.cpu()[idx] - r_o.float()).abs().max() < 1e-2
+    assert (sig.cpu()[idx] - s_o.float()[:, 0]).abs().max() < 1e-2
+
+
+def test_mlp_forward_sources_and_module(D, golden):
+    sd = make_state_dict(21, 256)
+    B, S = 37, 64
+    o, d, near, far, _ = make_rays(3, B)
+    t_rand, _ = make_draws(4, B, S, 1)
+    z = O.stratified_z(near, far, t_rand)
+    pts, dirs = O.points_on_rays(o, d, z)
+    pk = _packed(D, sd)
+    a = D.ops.mlp_forward(pk, pos=pts.cuda(), view=dirs.cuda())
+    b = D.ops.mlp_forward(pk, rays=(o.cuda(), d.cuda(), z.cuda()))
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    # dense grid source == explicit grid points (extract_vol.py:57-120)
+    R = 12
+    lin = torch.linspace(-1.0, 1.0, R, device="cuda")
+    view = torch.tensor([0.0, 0.0, -1.0], device="cuda")
+    g1 = D.ops.mlp_forward(pk, grid=(lin, view, 0, R ** 3))
+    gp = D.generate_3d_grid((-1.0, 1.0), R)
+    assert np.array_equal(gp.cpu().numpy(), golden["grid_R12"]) or torch.equal(gp.cpu(), O.grid_points((-1.0, 1.0), R))
+    g2 = D.ops.mlp_forward(pk, pos=gp, view=view.expand(R ** 3, 3).contiguous())
+    assert torch.equal(g1[0], g2[0]) and torch.equal(g1[1], g2[1])
+    np.testing.assert_allclose(g1[1].cpu().numpy(), golden["grid_sigma"][:, 0], atol=2e-2, rtol=2e-2)
+    np.testing.assert_allclose(g1[0].cpu().numpy(), golden["grid_rgb"], atol=2e-2, rtol=0)
+    # slab offset
+    g3 = D.ops.mlp_forward(pk, grid=(lin, view, 5 * R * R, 2 * R * R))
+    assert torch.equal(g3[1], g1[1][5 * R * R: 7 * R * R])
+    # nn.Module surface: state-dict round trip with the reference key set
+    m = D.OptimizedVanillaNeRF().cuda()
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    m.load_state_dict(sd)
+    m.eval()
+    with torch.no_grad():
+        rgb, sig = m(pts.cuda(), dirs.cuda())
+        sg, feat = m.query_density(pts.cuda())
+    assert rgb.shape == (B * S, 3) and sig.shape == (B * S, 1) and feat.shape == (B * S, 256)
+    assert torch.equal(rgb, a[0]) and torch.equal(sig[:, 0], a[1]) and torch.equal(sg, sig)
+    np.testing.assert_allclose(feat.float().cpu().numpy()[:512], O_feat(sd, pts[:512]), atol=3e-2, rtol=2e-2)
+
+
+def O_feat(sd, pos):
+    pe = O.posenc(pos, 10)
+    h = pe
+    for i in (0, 2, 4, 6):
+        h = torch.relu(O._lin(h, sd[f"pos_layers.{i}.weight"], sd[f"pos_layers.{i}.bias"], None))
+    h = torch.cat([h, pe], -1)
+    for i in (0, 2, 4, 6):
+        h = torch.relu(O._lin(h, sd[f"skip_layers.{i}.weight"], sd[f"skip_layers.{i}.bias"], None))
+    return O._lin(h, sd["feature_layer.weight"], sd["feature_layer.bias"], None).numpy()
+
+
+# ---- optimiser / volume -----------------------------------------------------------------------------------------------
+def test_adamw_onecycle(D, golden):
+    total = 50
+    lrs, b1s = D.onecycle_tables(total, 5e-4)
+    np.testing.assert_allclose(lrs[: total - 1], golden["adamw_lrs"], rtol=1e-9)
+    p = T(golden["adamw_p0"]).clone().cuda()
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    step = torch.zeros(1, dtype=torch.int32, device="cuda")
+    lt, bt = torch.tensor(lrs, device="cuda", dtype=torch.float32), torch.tensor(b1s, device="cuda", dtype=torch.float32)
+    for s in range(total - 1):
+        D.ops.adamw_step(p, T(golden["adamw_grads"][s]).cuda(), m, v, lt, bt, step)
+        np.testing.assert_allclose(p.cpu().numpy(), golden["adamw_params"][s], rtol=1e-5, atol=2e-6)
+    assert step.item() == total - 1
+
+
+def test_histogram_otsu_pack(D):
+    g = torch.Generator().manual_seed(9)
+    v = torch.cat([torch.rand(50000, generator=g) * 0.2, 5 + torch.randn(30000, generator=g)])
+    rgb = torch.rand(v.numel(), 3, generator=g)
+    occ, thr = D.apply_otsu_threshold(v.cuda())
+    ref_thr = O.otsu_threshold(v)
+    assert abs(thr - ref_thr) <= (float(v.max()) - float(v.min())) / 256 + 1e-6
+    o8, c8 = D.ops.pack_volume(v.cuda(), rgb.cuda(), thr)
+    assert torch.equal(o8.cpu(), (v > thr).to(torch.uint8))
+    assert torch.equal(c8.cpu(), (rgb * 255).to(torch.uint8))
+    h = D.ops.histogram(v.cuda(), float(v.min()), float(v.max()), 256)
+    assert int(h.sum()) == v.numel()
+
+
+def test_errors_are_loud(D):
+    with pytest.raises(RuntimeError):
+        D.ops.stratified_sample(torch.zeros(4), torch.ones(4), torch.linspace(0, 1, 8), torch.rand(4, 8))  # CPU tensors
+    with pytest.raises(RuntimeError):
+        D.ops.merge_sort_z(torch.zeros(2, 200, device="cuda"), torch.zeros(2, 100, device="cuda"))
+    with pytest.raises(NotImplementedError):
+        m = D.OptimizedVanillaNeRF(hidden_dim=64).cuda()
+        m(torch.zeros(4, 3, device="cuda"), torch.zeros(4, 3, device="cuda"))

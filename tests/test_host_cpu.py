@@ -1,0 +1,79 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol include/deepfields_b200.h declares, the
+host-side mirrors keep the reference's names / state-dict layout, the config loader resolves ${} references.
+No compute call is made (there is no GPU here)."""
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def D():
+    import __graft_entry__ as ge
+    ge.build()
+    import deepfields_nerf_b200 as d
+    return d
+
+
+def test_header_symbols_exported(D):
+    hdr = open(os.path.join(ROOT, "include", "deepfields_b200.h")).read()
+    declared = set(re.findall(r"\b(dfn_[a-z0-9_]+)\s*\(", hdr))
+    declared.discard("dfn_point_source")
+    assert len(declared) >= 24
+    lib = D._lib.load()
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+        assert name in D._lib.SIGNATURES, f"{name} has no ctypes signature"
+    assert lib.dfn_abi_version() == 1
+    assert lib.dfn_mlp_fwd_pack_bytes() == 1187840
+    assert lib.dfn_mlp_stash_bytes(129) == 2 * (9 * 65536 + 32768)
+
+
+def test_state_dict_layout_matches_reference(D, golden):
+    from common import make_state_dict
+    sd = make_state_dict(1, 256)
+    m = D.OptimizedVanillaNeRF()
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    for k, v in m.state_dict().items():
+        assert v.shape == sd[k].shape and v.dtype == torch.float32, k
+    m.load_state_dict(sd)
+    flat = m.flatten_parameters()
+    assert flat.numel() == 595844 == D.ops.MLP_NUM_PARAMS
+    assert torch.equal(flat[: 256 * 63].view(256, 63), sd["pos_layers.0.weight"])
+    m.pos_layers[0].weight.data.add_(1.0)             # parameters alias the flat buffer
+    assert torch.equal(flat[: 256 * 63].view(256, 63), sd["pos_layers.0.weight"] + 1.0)
+    assert float(m.density_layer.bias.detach()) == pytest.approx(0.1)  # after load: golden init value
+    c, f = D.get_nerf_models(device="cpu")
+    assert c is not f
+
+
+def test_cpu_tensors_are_rejected(D):
+    with pytest.raises(RuntimeError):
+        D.raw2outputs(torch.rand(2, 8, 3), torch.rand(2, 8, 1), torch.rand(2, 8).sort(-1).values)
+    m = D.OptimizedVanillaNeRF()
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(4, 3), torch.zeros(4, 3))
+
+
+def test_config_loader(D, tmp_path):
+    for name in ("base_cfg", "blender_scene", "grass_scene", "real_scene"):
+        p = os.path.join("/root/reference/cfg", name + ".yml")
+        if os.path.exists(p):
+            c = D.load_config(p)
+            assert c.checkpoint.endswith("checkpoints/nerf_final.pth") and "${" not in c.checkpoint
+            assert c.N_samples == 64 and c.N_importance == 128 and c.hidden_dim == 256
+    y = tmp_path / "c.yml"
+    y.write_text('scene_name: "s"\noutput_dir: "./o/${scene_name}"\ncheckpoint_dir: "${output_dir}/ck"\nn: 3\nm: ${n}\nsub:\n  a: [1, 2]\n')
+    c = D.load_config(str(y))
+    assert c.checkpoint_dir == "./o/s/ck" and c.m == 3 and c.sub.a == [1, 2]
+
+
+def test_onecycle_tables_match_oracle(D):
+    from oracle import nerf_oracle as O
+    lrs, b1s = D.onecycle_tables(200, 5e-4)
+    for s in (0, 1, 19, 20, 100, 199):
+        lr, b1 = O.onecycle(s, 200, 5e-4)
+        assert lrs[s] == pytest.approx(lr, rel=1e-12) and b1s[s] == pytest.approx(b1, rel=1e-12)
