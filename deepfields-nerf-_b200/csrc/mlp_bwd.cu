@@ -1,11 +1,296 @@
-// placeholder until the dgrad/wgrad kernels land
+// Backward of the fused vanilla-NeRF MLP, part 1: the data-gradient chain (autograd of reference
+// scripts/model.py:139-187 w.r.t. the hidden activations), same persistent two-slot tcgen05 pipeline as
+// the forward kernel.  Per 128-point tile:
+//   prologue : dZ_c2 = d_rgb * rgb(1-rgb)            (sigmoid', 3 columns, fp32 -> global)
+//              dZ_c0 = (dZ_c2 * color_layer.2.weight) masked by c > 0   (CUDA cores, K = 3)
+//   b0       : d feat = dZ_c0 * color_layer.0.weight[:, :256]           (tcgen05, K = 128)
+//   b1       : d h8   = dZ_f * feature_layer.weight + d sigma_pre * density_layer.weight, masked by h8 > 0
+//   b2..b8   : d h7 .. d h1 through skip_layers / pos_layers (skip_layers.0 uses its first 256 columns)
+// Every dZ is rounded to bf16 (what bf16 autocast autograd does), written back to shared memory as the next
+// job's A operand and stored to the dz scratch (chunk layout) for the weight-gradient kernel.  ReLU masks come
+// from the forward's activation stash (h > 0), read straight from global memory by the epilogue threads.
 #include "mlp_common.cuh"
-extern "C" long long dfn_mlp_dz_bytes(long long P) {
-  const long long nt = (P + mlp::kTile - 1) / mlp::kTile;
-  return nt * (10LL * 65536);
+
+namespace mlp {
+// dz scratch layout (per n_tiles): [8][nt][64K] dZ_1..dZ_8 | [nt][64K] dZ_f | [nt][32K] dZ_c0 | [nt][128][4] f32
+// (dZ_c2[0..2], d sigma_pre)
+__host__ __device__ inline size_t dz_off_h(int l, int nt, int tile) { return (static_cast<size_t>(l) * nt + tile) << 16; }
+__host__ __device__ inline size_t dz_off_f(int nt, int tile) { return (static_cast<size_t>(8) * nt + tile) << 16; }
+__host__ __device__ inline size_t dz_off_c0(int nt, int tile) { return (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(tile) << 15); }
+__host__ __device__ inline size_t dz_off_small(int nt, int tile) {
+  return (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(nt) << 15) + static_cast<size_t>(tile) * 2048;
 }
-extern "C" int dfn_mlp_backward(const dfn_point_source*, long long, const void*, const float*, const float*,
-                                const float*, const float*, const float*, const void*, void*, float*, void*) {
-  dfn_set_error("mlp_backward: not built yet");
-  return DFN_ERR_ARG;
+}  // namespace mlp
+
+namespace {
+using namespace mlp;
+using namespace umma;
+
+constexpr int kStages = 4;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;
+
+constexpr uint32_t kOffAct = 0;
+constexpr uint32_t kOffRing = kOffAct + 2 * kActBytes;
+constexpr uint32_t kOffConst = kOffRing + kStages * kStageBytes;
+constexpr uint32_t kOffBars = kOffConst + kConstBytes;
+constexpr uint32_t kNumBars = 2 * kStages + 4;
+constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
+constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
+static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
+
+struct DgradArgs {
+  long long P;
+  int n_tiles;
+  const uint8_t* wpack;  // packed W^T images
+  const float* consts;
+  const float* rgb;      // [P,3] forward output
+  const float* sigma;    // [P]
+  const float* d_rgb;    // [P,3]
+  const float* d_sigma;  // [P]
+  const uint8_t* stash;  // forward stash
+  uint8_t* dz;
+};
+
+__device__ __forceinline__ int tile_of(int it, int t) { return (it * 2 + t) * gridDim.x + blockIdx.x; }
+
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t h2) {
+  // 0xFFFF per bf16 half that is > 0 (post-ReLU activations are >= +0)
+  return ((h2 & 0x0000FFFFu) ? 0x0000FFFFu : 0u) | ((h2 & 0xFFFF0000u) ? 0xFFFF0000u : 0u);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t bar0 = sbase + kOffBars;
+  auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
+  auto bar_wempty = [&](int s) { return bar0 + 8u * (kStages + s); };
+  auto bar_accfull = [&](int t) { return bar0 + 8u * (2 * kStages + t); };
+  auto bar_aready = [&](int t) { return bar0 + 8u * (2 * kStages + 2 + t); };
+  float* consts = reinterpret_cast<float*>(smem + kOffConst);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(bar_wfull(s), 1); mbar_init(bar_wempty(s), 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiThreads); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
+  for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
+  const int n_it = (a.n_tiles + 2 * gridDim.x - 1) / (2 * gridDim.x);
+  const int nt = a.n_tiles;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ---- weight producer
+      int stage = 0; uint32_t ph = 0;
+      for (int it = 0; it < n_it; ++it)
+        for (int b = 0; b < kNumBwdJobs; ++b) {
+          const uint32_t jbytes = bjob_bytes(b);
+          const uint8_t* src = a.wpack + bjob_off(b);
+          for (int t = 0; t < 2; ++t) {
+            if (tile_of(it, t) >= nt) continue;
+            for (uint32_t off = 0; off < jbytes; off += kStageBytes) {
+              mbar_wait(bar_wempty(stage), ph ^ 1);
+              mbar_arrive_expect_tx(bar_wfull(stage), kStageBytes);
+              bulk_g2s(sbase + kOffRing + stage * kStageBytes, src + off, kStageBytes, bar_wfull(stage));
+              if (++stage == kStages) { stage = 0; ph ^= 1; }
+            }
+          }
+        }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ---- MMA issuer
+      int stage = 0; uint32_t ph = 0;
+      uint32_t pa[2] = {0, 0};
+      const uint32_t idesc = instr_desc_bf16(128, 256, 0, 0);
+      for (int it = 0; it < n_it; ++it)
+        for (int b = 0; b < kNumBwdJobs; ++b) {
+          const int kc_total = bjob_kc(b);
+          for (int t = 0; t < 2; ++t) {
+            if (tile_of(it, t) >= nt) continue;
+            mbar_wait(bar_aready(t), pa[t]); pa[t] ^= 1;
+            tc_fence_after();
+            const uint32_t act = sbase + kOffAct + t * kActBytes;
+            const uint32_t tacc = tmem_base + t * 256;
+            for (int kc0 = 0; kc0 < kc_total; kc0 += 4) {
+              mbar_wait(bar_wfull(stage), ph);
+              tc_fence_after();
+              const uint32_t wst = sbase + kOffRing + stage * kStageBytes;
+#pragma unroll
+              for (int c = 0; c < 4; c += 2) {
+                const int kc = kc0 + c;
+                mma_bf16(tacc, smem_desc(act + kc * kChunkBytes, kChunkBytes, 128), smem_desc(wst + c * 4096, 4096, 128),
+                         idesc, kc > 0 ? 1u : 0u);
+              }
+              mma_commit(bar_wempty(stage));
+              if (++stage == kStages) { stage = 0; ph ^= 1; }
+            }
+            mma_commit(bar_accfull(t));
+          }
+        }
+    }
+  } else {
+    // ---- epilogue warps
+    const int ew = warp - 2, q = warp & 3, hh = ew >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
+    uint32_t pf[2] = {0, 0};
+
+    // prologue of a tile: dZ_c0 -> act chunks 0..15 (+ dz scratch), small fp32 grads
+    auto prologue = [&](int t, int tile) {
+      uint8_t* act = smem + kOffAct + t * kActBytes;
+      const long long p = static_cast<long long>(tile) * kTile + row;
+      const bool valid = p < a.P;
+      float g[3] = {0.f, 0.f, 0.f};
+      float ds = 0.f;
+      if (valid) {
+#pragma unroll
+        for (int o = 0; o < 3; ++o) {
+          const float r = a.rgb[p * 3 + o];
+          g[o] = a.d_rgb[p * 3 + o] * r * (1.0f - r);
+        }
+        ds = a.sigma[p] > 0.f ? a.d_sigma[p] : 0.f;
+      }
+      if (hh == 0) {
+        float4* sm = reinterpret_cast<float4*>(a.dz + dz_off_small(nt, tile)) + row;
+        *sm = make_float4(g[0], g[1], g[2], ds);
+      }
+      const uint8_t* cst = a.stash + (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(tile) << 15);
+      uint8_t* dzc0 = a.dz + dz_off_c0(nt, tile);
+      const float* w2 = consts + kConstWc2;
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        const int chunk = hh * 8 + ch;
+        const uint32_t off = chunk * kChunkBytes + row * 16;
+        const uint4 cv = *reinterpret_cast<const uint4*>(cst + off);
+        const uint32_t cw[4] = {cv.x, cv.y, cv.z, cv.w};
+        uint32_t o4[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int k = chunk * 8 + 2 * i;
+          const float d0 = g[0] * w2[k] + g[1] * w2[128 + k] + g[2] * w2[256 + k];
+          const float d1 = g[0] * w2[k + 1] + g[1] * w2[128 + k + 1] + g[2] * w2[256 + k + 1];
+          o4[i] = pack_bf16x2(d0, d1) & relu_mask2(cw[i]);
+        }
+        const uint4 q4 = make_uint4(o4[0], o4[1], o4[2], o4[3]);
+        *reinterpret_cast<uint4*>(act + off) = q4;
+        *reinterpret_cast<uint4*>(dzc0 + off) = q4;
+      }
+    };
+
+    for (int t = 0; t < 2; ++t) {
+      const int tile = tile_of(0, t);
+      if (tile < nt) prologue(t, tile);
+      fence_proxy_async();
+      mbar_arrive(bar_aready(t));
+    }
+
+    for (int it = 0; it < n_it; ++it)
+      for (int b = 0; b < kNumBwdJobs; ++b)
+        for (int t = 0; t < 2; ++t) {
+          const int tile = tile_of(it, t);
+          if (tile >= nt) continue;
+          uint8_t* act = smem + kOffAct + t * kActBytes;
+          const uint32_t tacc = tmem_base + t * 256 + lane_sel;
+          const int c0 = hh * 128;
+          // mask source (h_{l+1} of the forward stash) and dz destination
+          const int l = 8 - b;  // b >= 1
+          const uint8_t* hsrc = b >= 1 ? a.stash + ((static_cast<size_t>(l) * nt + tile) << 16) : nullptr;
+          uint8_t* dst = b == 0 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(l, nt, tile);
+          float dsig = 0.f;
+          if (b == 1) dsig = reinterpret_cast<const float4*>(a.dz + dz_off_small(nt, tile))[row].w;
+          uint4 hb[2][4];
+          if (b >= 1) {
+#pragma unroll
+            for (int g4 = 0; g4 < 4; ++g4)
+              hb[0][g4] = *reinterpret_cast<const uint4*>(hsrc + (c0 / 8 + g4) * kChunkBytes + row * 16);
+          }
+          mbar_wait(bar_accfull(t), pf[t]); pf[t] ^= 1;
+          tc_fence_after();
+          uint32_t v0[32], v1[32];
+          tmem_ld32(tacc + c0, v0);
+          tmem_ld_wait();
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc) {
+            uint32_t (&cur)[32] = (cc & 1) ? v1 : v0;
+            uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
+            const int col0 = c0 + cc * 32;
+            if (cc < 3) {
+              tmem_ld32(tacc + col0 + 32, nxt);
+              if (b >= 1) {
+#pragma unroll
+                for (int g4 = 0; g4 < 4; ++g4)
+                  hb[(cc + 1) & 1][g4] = *reinterpret_cast<const uint4*>(hsrc + ((col0 + 32) / 8 + g4) * kChunkBytes + row * 16);
+              }
+            }
+#pragma unroll
+            for (int g4 = 0; g4 < 4; ++g4) {
+              float x[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(cur[g4 * 8 + i]);
+              if (b == 1) {
+                const float* ws = consts + kConstWsig + col0 + g4 * 8;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) x[i] += dsig * ws[i];
+              }
+              uint4 o;
+              o.x = pack_bf16x2(x[0], x[1]); o.y = pack_bf16x2(x[2], x[3]);
+              o.z = pack_bf16x2(x[4], x[5]); o.w = pack_bf16x2(x[6], x[7]);
+              if (b >= 1) {
+                const uint4 h = hb[cc & 1][g4];
+                o.x &= relu_mask2(h.x); o.y &= relu_mask2(h.y); o.z &= relu_mask2(h.z); o.w &= relu_mask2(h.w);
+              }
+              const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
+              if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;
+              *reinterpret_cast<uint4*>(dst + off) = o;
+            }
+            if (cc < 3) tmem_ld_wait();
+          }
+          if (b == kNumBwdJobs - 1) {
+            const int ntile = tile_of(it + 1, t);
+            if (ntile < nt) prologue(t, ntile);
+          }
+          tc_fence_before();
+          fence_proxy_async();
+          mbar_arrive(bar_aready(t));
+        }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace
+
+int dfn_launch_wgrad(const dfn_point_source* src, long long P, int n_tiles, const uint8_t* stash, const uint8_t* dz,
+                     float* grads, cudaStream_t st);
+
+extern "C" long long dfn_mlp_dz_bytes(long long P) {
+  const long long nt = (P + kTile - 1) / kTile;
+  return nt * (9LL * 65536 + 32768 + 2048);
+}
+
+extern "C" int dfn_mlp_backward(const dfn_point_source* src, long long P, const void* bwd_pack, const float* consts,
+                                const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma,
+                                const void* stash, void* dz, float* grads, void* stream) {
+  DFN_CHECK_ARG(src && bwd_pack && consts && rgb && sigma && d_rgb && d_sigma && stash && dz && grads,
+                "mlp_backward: null pointer");
+  DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward: P out of range");
+  if (P == 0) return DFN_OK;
+  DgradArgs a{};
+  a.P = P; a.n_tiles = static_cast<int>((P + kTile - 1) / kTile);
+  a.wpack = static_cast<const uint8_t*>(bwd_pack); a.consts = consts; a.rgb = rgb; a.sigma = sigma;
+  a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.stash = static_cast<const uint8_t*>(stash); a.dz = static_cast<uint8_t*>(dz);
+  const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DFN_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward");
+  mlp_dgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
+  DFN_CHECK_LAUNCH("mlp_backward(dgrad)");
+  return dfn_launch_wgrad(src, P, a.n_tiles, a.stash, a.dz, grads, st);
 }

@@ -206,7 +206,7 @@ extern "C" int dfn_sample_pdf_with_cdf(const float* bins, const float* cdf, cons
 
 extern "C" int dfn_merge_sort_z(const float* z_coarse, int NA, const float* z_fine, int NBn, int B, float* z_out,
                                 void* stream) {
-  DFN_CHECK_ARG(z_coarse && z_fine && z_out, "merge_sort_z: null pointer");
+  DFN_CHECK_ARG((z_coarse || NA == 0) && (z_fine || NBn == 0) && z_out, "merge_sort_z: null pointer");
   DFN_CHECK_ARG(NA >= 0 && NBn >= 0 && NA + NBn <= kSortN, "merge_sort_z: %d+%d keys exceed %d", NA, NBn, kSortN);
   if (B == 0) return DFN_OK;
   merge_sort_kernel<<<grid_for(B, kSortWarps), kSortWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
