@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""Benchmark of the NeRF render/train hot path (BASELINE.json config 2: vanilla NeRF train step, 4096 rays per
+GPU x (64 stratified + 128 hierarchical) samples, bf16 MLP, data-parallel rays).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+One "step" = one full training iteration of scripts/train.py:282-323 on one 4096-ray batch per GPU: jittered
+sampling, coarse MLP, compositing + loss, inverse-CDF resampling, merge, fine MLP, compositing + loss, backward of
+both networks, gradient all-reduce (N > 1), AdamW + OneCycleLR, bf16 weight repack.  Synthetic rays, random-init
+weights.  Rank 0 prints ONE JSON line.
+
+`value`   rays/s over all ranks with the ray batches already resident in HBM.
+`e2e`     the same step driven from pinned HOST buffers through FusedTrainer.step_from_host: H2D copy of the
+          batch and D2H read of the losses inside the timed region.
+`roofline` the dominant kernel (tensor-bound MLP kernel) timed live with CUDA events inside the timed region.
+`cpu_baseline` the oracle port of the reference path timed on this box's host cores (bounded sample).
+`--impl reference` times that CPU port alone (the reference is pure Python on torch; /root/reference does not
+exist on the GPU box, so the port in oracle/ stands in for it -- kind "port").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests", "golden")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+B_RAYS, S_COARSE, N_IMPORTANCE = 4096, 64, 128
+T_FINE = S_COARSE + N_IMPORTANCE
+# algorithmic FLOP per MLP evaluation (unpadded layer dims, SURVEY 8d / DESIGN.md)
+FLOP_FWD = 2 * 593408
+FLOP_DGRAD = 2 * 557696
+FLOP_WGRAD = 2 * 593408
+FLOP_PER_RAY_TRAIN = (S_COARSE + T_FINE) * (FLOP_FWD + FLOP_DGRAD + FLOP_WGRAD)
+STAGE_FLOP = {"mlp_fwd": FLOP_FWD, "dgrad": FLOP_DGRAD, "wgrad": FLOP_WGRAD}
+METRIC, UNIT = "train_rays_per_s", "rays/s"
+WORKLOAD = ("vanilla NeRF train step (model.py, PE L=10/4, hidden 256), 4096 rays/GPU x (64 stratified + 128 "
+            "hierarchical) samples, coarse+fine nets, bf16 MLP, fp32 sampling/compositing/AdamW")
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return {"hbm": d["hbm_gbs"], "tensor_burst": d["bf16_tflops"], "tensor_sustained": d["bf16_tflops_sustained"],
+                "src": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.thr.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's train step (fp32, as scripts/train_no_amp.py computes on CPU)
+# ------------------------------------------------------------------------------------------------------------
+class CpuStep:
+    def __init__(self, n_rays: int):
+        import torch
+        from common import make_state_dict
+        from oracle import nerf_oracle as O
+        self.torch, self.O, self.n = torch, O, n_rays
+        self.sd = [make_state_dict(31, 256), make_state_dict(32, 256)]
+        self.leaves = []
+        for sd in self.sd:
+            for k in sd:
+                if "freq_bands" not in k:
+                    sd[k] = sd[k].clone().requires_grad_(True)
+                    self.leaves.append(sd[k])
+        self.opt = torch.optim.AdamW(self.leaves, lr=5e-4, weight_decay=1e-6)  # scripts/train.py:244-248
+
+    def __call__(self, seed: int, n_rays=None):
+        from common import make_rays
+        torch, O = self.torch, self.O
+        n = n_rays or self.n
+        o, d, near, far, tgt = make_rays(seed, n)
+        t_rand, u = torch.rand(n, S_COARSE), torch.rand(n, N_IMPORTANCE)
+        nc, nf = torch.randn(n * S_COARSE, 1), torch.randn(n * T_FINE, 1)
+        t0 = time.perf_counter()
+        self.opt.zero_grad(set_to_none=True)
+        out = O.render_losses(self.sd[0], self.sd[1], o, d, near, far, tgt, t_rand, u, nc, nf)
+        out["loss"].backward()
+        self.opt.step()
+        return time.perf_counter() - t0
+
+
+def cpu_rate(budget_s: float):
+    """rays/s of the CPU port on a bounded sample sized for ~budget_s seconds; returns (rays/s, sample text, cores)."""
+    import torch
+    step = CpuStep(64)
+    step(0, 64)                      # warm-up (first-call allocator / thread-pool effects)
+    t = step(1, 64)
+    n = int(max(64, min(1024, (budget_s / max(t / 64, 1e-9)) // 64 * 64)))
+    t = step(2, n)
+    return n / t, f"1 step of {n} rays x (64+192) samples, fp32 torch CPU, after a 64-ray warm-up", torch.get_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    cores = torch.get_num_threads()
+    probe = CpuStep(64)
+    probe(0, 64)
+    t64 = probe(1, 64)
+    # size the per-step sample so that steps+warmup finish in ~150 s
+    total = max(args.steps + args.warmup, 1)
+    n = int(max(32, min(1024, (150.0 / total) / max(t64 / 64, 1e-9) // 32 * 32)))
+    step = probe
+    for i in range(args.warmup):
+        step(10 + i, n)
+    times = [step(100 + i, n) for i in range(args.steps)]
+    elapsed = sum(times)
+    value = n * args.steps / elapsed
+    sample = f"{args.steps} steps of {n} rays x (64+192) samples (bounded sample of the 4096-ray batch), fp32 torch CPU"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "rays_per_step": n, "note": "CPU port of the reference path (oracle/nerf_oracle.py); "
+                   "the reference itself is Python on torch and /root/reference is absent on the GPU box"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from common import make_rays, make_state_dict
+    import deepfields_nerf_b200 as D
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pk = peaks()
+
+    K, W = args.steps, max(args.warmup, 3)
+    mc, mf = D.get_nerf_models(device=dev)
+    mc.load_state_dict(make_state_dict(31, 256))
+    mf.load_state_dict(make_state_dict(32, 256))
+    tr = D.FusedTrainer(mc, mf, S_COARSE, N_IMPORTANCE, lr=5e-4, total_steps=10 * (K + W) + 64, train_noise=True)
+
+    n_batches = 8
+    host, resident = [], []   # pinned flat batches (the .npz columns of dataset.py:32-60) and their HBM copies
+    for i in range(n_batches):
+        o, d, near, far, rgb = make_rays(1000 + 17 * rank + i, B_RAYS)
+        host.append(D.FusedTrainer.pack_host_batch(o, d, near, far, rgb))
+        resident.append(tuple(t.reshape(-1).to(dev) if t.shape[-1] == 1 else t.to(dev) for t in (o, d, near, far, rgb)))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_max(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timed region -------------------------------------------------------------------
+    for i in range(W):
+        tr.step(*resident[i % n_batches])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tr.profile = True
+    with ClockSampler(local) as clk:
+        barrier()
+        e0.record()
+        for i in range(K):
+            tr.step(*resident[(W + i) % n_batches])
+        e1.record()
+        barrier()
+    tr.profile = False
+    ms_total = reduce_max(e0.elapsed_time(e1))
+    stages = tr.stage_times_ms()
+    launches = tr.launches_per_step * K
+    value = world * B_RAYS * K / (ms_total * 1e-3)
+
+    # ---- end-to-end timed region: pinned host batches in, losses out --------------------------------------
+    for i in range(2):
+        tr.step_from_host(host[i % n_batches])
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(K):
+        losses_host = tr.step_from_host(host[(2 + i) % n_batches])
+    e3.record()
+    barrier()
+    ms_e2e = reduce_max(e2.elapsed_time(e3))
+    e2e_value = world * B_RAYS * K / (ms_e2e * 1e-3)
+    assert all(map(lambda v: v == v, losses_host.tolist())), "non-finite loss"
+
+    # ---- roofline of the dominant kernel ------------------------------------------------------------------
+    pts = {"coarse": B_RAYS * S_COARSE, "fine": B_RAYS * T_FINE}
+    mean = {k: sum(v) / len(v) for k, v in stages.items()}
+    tot = sum(sum(v) for v in stages.values())
+    mlp = {k: v for k, v in mean.items() if k.split("_")[-1] in pts and k.rsplit("_", 1)[0] in STAGE_FLOP}
+    dom = max(mlp, key=lambda k: mlp[k] * len(stages[k]))
+    kind, net = dom.rsplit("_", 1)
+    flop = STAGE_FLOP[kind] * pts[net]
+    achieved = flop / (mlp[dom] * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            traffic = json.load(fh).get(dom)
+    roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tensor_sustained"], "unit": "TFLOP/s",
+                "frac": achieved / pk["tensor_sustained"], "traffic": traffic, "peak_source": pk["src"] + ", sustained bf16",
+                "flop_per_launch": flop, "ms_per_launch": mlp[dom]}
+    step_tflops = world * FLOP_PER_RAY_TRAIN * B_RAYS * K / (ms_total * 1e-3) / 1e12
+    stage_report = {k: {"ms": round(mean[k], 4), "share": round(sum(stages[k]) / tot, 4)} for k in stages}
+    for k in mlp:
+        kk, nn = k.rsplit("_", 1)
+        stage_report[k]["tflops"] = round(STAGE_FLOP[kk] * pts[nn] / (mean[k] * 1e-3) / 1e12, 1)
+
+    # ---- extract_vol 512^3 (BASELINE.json config 4), slab-sharded, reported beside the headline ---------------
+    extract = None
+    if not args.no_extract:
+        R = args.extract_res
+        mf.eval()
+        planes = (R + world - 1) // world
+        n_pts = max(min((rank + 1) * planes, R) - min(rank * planes, R), 0) * R * R
+        out = (torch.empty(n_pts, 3, device=dev), torch.empty(n_pts, device=dev))
+        with torch.no_grad():
+            D.extract_volume_fused(mf, R, rank=rank, world=world, out=out)
+            barrier()
+            x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            x0.record()
+            D.extract_volume_fused(mf, R, rank=rank, world=world, out=out)
+            x1.record()
+            barrier()
+        ms_x = reduce_max(x0.elapsed_time(x1))
+        tf = R ** 3 * FLOP_FWD / (ms_x * 1e-3) / 1e12
+        extract = {"metric": "extract_vol_points_per_s", "value": R ** 3 / (ms_x * 1e-3), "unit": "points/s", "resolution": R,
+                   "ms": ms_x, "includes": "MLP query + min/max + histogram + Otsu + u8 pack (outputs stay in HBM)",
+                   "tflops": tf, "frac_of_sustained_tensor_peak": tf / (pk["tensor_sustained"] * world)}
+        del out
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, sample, cores = cpu_rate(args.cpu_budget)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        stash_gb = (D.ops.mlp_stash_bytes(pts["coarse"]) + D.ops.mlp_stash_bytes(pts["fine"]) + D.ops.mlp_dz_bytes(pts["fine"])) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "rays_per_gpu": B_RAYS, "global_rays": B_RAYS * world, "N_samples": S_COARSE,
+                       "N_importance": N_IMPORTANCE, "parallelism": f"dp{world} (rays sharded, one NCCL all-reduce of the flat gradient)",
+                       "l2": f"no explicit flush: each step streams {stash_gb:.2f} GB of activation/gradient scratch through HBM "
+                             "(>> 126 MB L2) and rotates over 8 distinct ray batches"},
+            "roofline": roofline,
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host[0].numel() * 4 * world,
+                    "d2h_bytes_per_step": 8 * world, "ms_per_step": ms_e2e / K},
+            "gpu_launches": launches,
+            "clocks": clk.summary(),
+            "step_tflops": step_tflops, "step_frac_of_sustained_tensor_peak": step_tflops / (pk["tensor_sustained"] * world),
+            "stages": stage_report,
+            "extract_vol": extract,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extract", action="store_true", help="skip the extract_vol measurement")
+    ap.add_argument("--extract-res", type=int, default=512)
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -276,12 +276,11 @@ extern "C" long long dfn_mlp_dz_bytes(long long P) {
   return nt * (9LL * 65536 + 32768 + 2048);
 }
 
-extern "C" int dfn_mlp_backward(const dfn_point_source* src, long long P, const void* bwd_pack, const float* consts,
-                                const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma,
-                                const void* stash, void* dz, float* grads, void* stream) {
-  DFN_CHECK_ARG(src && bwd_pack && consts && rgb && sigma && d_rgb && d_sigma && stash && dz && grads,
-                "mlp_backward: null pointer");
-  DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward: P out of range");
+extern "C" int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const float* consts, const float* rgb,
+                                     const float* sigma, const float* d_rgb, const float* d_sigma, const void* stash,
+                                     void* dz, void* stream) {
+  DFN_CHECK_ARG(bwd_pack && consts && rgb && sigma && d_rgb && d_sigma && stash && dz, "mlp_backward_dgrad: null pointer");
+  DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward_dgrad: P out of range");
   if (P == 0) return DFN_OK;
   DgradArgs a{};
   a.P = P; a.n_tiles = static_cast<int>((P + kTile - 1) / kTile);
@@ -289,8 +288,25 @@ extern "C" int dfn_mlp_backward(const dfn_point_source* src, long long P, const 
   a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.stash = static_cast<const uint8_t*>(stash); a.dz = static_cast<uint8_t*>(dz);
   const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  DFN_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward");
+  DFN_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward_dgrad");
   mlp_dgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
-  DFN_CHECK_LAUNCH("mlp_backward(dgrad)");
-  return dfn_launch_wgrad(src, P, a.n_tiles, a.stash, a.dz, grads, st);
+  DFN_CHECK_LAUNCH("mlp_backward_dgrad");
+  return DFN_OK;
+}
+
+extern "C" int dfn_mlp_backward_wgrad(const dfn_point_source* src, long long P, const void* stash, const void* dz,
+                                     float* grads, void* stream) {
+  DFN_CHECK_ARG(src && stash && dz && grads, "mlp_backward_wgrad: null pointer");
+  DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward_wgrad: P out of range");
+  if (P == 0) return DFN_OK;
+  return dfn_launch_wgrad(src, P, static_cast<int>((P + kTile - 1) / kTile), static_cast<const uint8_t*>(stash),
+                          static_cast<const uint8_t*>(dz), grads, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dfn_mlp_backward(const dfn_point_source* src, long long P, const void* bwd_pack, const float* consts,
+                                const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma,
+                                const void* stash, void* dz, float* grads, void* stream) {
+  DFN_CHECK_ARG(src && grads, "mlp_backward: null pointer");
+  if (int rc = dfn_mlp_backward_dgrad(P, bwd_pack, consts, rgb, sigma, d_rgb, d_sigma, stash, dz, stream)) return rc;
+  return dfn_mlp_backward_wgrad(src, P, stash, dz, grads, stream);
 }

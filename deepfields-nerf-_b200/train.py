@@ -137,6 +137,31 @@ class FusedTrainer:
         self.sampler = StratifiedSampler(N_samples, dev)
         self.loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
         self._B = None
+        # optional per-stage CUDA-event timing (bench.py): list of (stage name, event) per recorded step
+        self.profile = False
+        self._marks = []
+        self.launches_per_step = 0
+
+    # ---- stage timing -----------------------------------------------------------------------------------
+    def _mark(self, name, launches=1):
+        """Called after every stage of the step (`launches` = kernels of this library the stage launched).  With
+        self.profile an event is recorded on the launching (current) stream, so consecutive marks bracket one stage."""
+        self._n_launch += launches
+        if self.profile:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._marks.append((name, ev))
+
+    def stage_times_ms(self):
+        """{stage: [ms per recorded launch]} from the recorded events (call after a synchronize); clears them."""
+        out = {}
+        prev = None
+        for name, ev in self._marks:
+            if name != "begin" and prev is not None:
+                out.setdefault(name, []).append(prev.elapsed_time(ev))
+            prev = ev
+        self._marks = []
+        return out
 
     def _dist_on(self):
         return torch.distributed.is_available() and torch.distributed.is_initialized()
@@ -168,22 +193,36 @@ class FusedTrainer:
                 noise_c = torch.randn(B * S, device=self.dev)
             if noise_f is None:
                 noise_f = torch.randn(B * T, device=self.dev)
+        self._n_launch = 0
+        self._mark("begin", 0)
         self.loss_sum.zero_()
         self.grads.zero_()
+        self._mark("zero", 0)  # torch memsets, not kernels of this library
         n = ops.MLP_NUM_PARAMS
         z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
+        self._mark("stratified")
         rays_c = (rays_o, rays_d, z_c)
         rgb_c, sig_c = ops.mlp_forward(mc._packed, rays=rays_c, noise=noise_c, stash=self.stash_c, out=self.out_c)
+        self._mark("mlp_fwd_coarse")
         _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg,
                                                    self.dist_last)
+        self._mark("render_loss_coarse")
         z_new = ops.sample_pdf(z_c, w_c[:, 1:-1], u, bins_mid_of_z=True)
+        self._mark("sample_pdf")
         z_all = ops.merge_sort_z(z_c, z_new)
+        self._mark("merge_sort")
         rays_f = (rays_o, rays_d, z_all)
         rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f)
+        self._mark("mlp_fwd_fine")
         _, _, d_rgb_f, d_sig_f = ops.render_loss(rgb_f, sig_f, z_all, target, self.loss_sum[1:2], self.white_bg,
                                                  self.dist_last, want_weights=False)
-        ops.mlp_backward(mc._packed, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.dz, self.grads[:n], rays=rays_c)
-        ops.mlp_backward(mf._packed, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.dz, self.grads[n:], rays=rays_f)
+        self._mark("render_loss_fine")
+        mk_c = lambda nm: self._mark(nm + "_coarse")  # noqa: E731
+        mk_f = lambda nm: self._mark(nm + "_fine")  # noqa: E731
+        ops.mlp_backward(mc._packed, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.dz, self.grads[:n], rays=rays_c,
+                         mark=mk_c)
+        ops.mlp_backward(mf._packed, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.dz, self.grads[n:], rays=rays_f,
+                         mark=mk_f)
         self.aux = {"z": z_c, "z_all": z_all, "z_new": z_new, "weights_coarse": w_c}
         return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
 
@@ -192,14 +231,41 @@ class FusedTrainer:
             torch.distributed.all_reduce(self.grads, group=self.pg)
         ops.adamw_step(self.flat, self.grads, self.m, self.v, self.lr_table, self.b1_table, self.step_dev,
                        weight_decay=self.wd, grad_scale=1.0 / self.world)
+        self._mark("adamw")
         for m in self.models:
             m._packed.pack(m._flat)
             m._packed_version = (m._flat._version, sum(p._version for p in m._ordered_params()))
+        self._mark("pack_weights", 2)
+        self.launches_per_step = self._n_launch
 
     def step(self, rays_o, rays_d, near, far, target, **draws):
         losses = self.forward_backward(rays_o, rays_d, near, far, target, **draws)
         self.optimizer_step()
         return losses
+
+    # ---- host-driven step (what scripts/train.py:285-289 does per iteration: H2D of the batch, then the step) ----
+    @staticmethod
+    def pack_host_batch(rays_o, rays_d, near, far, rgb):
+        """One pinned flat fp32 buffer [o(3B) | d(3B) | near(B) | far(B) | rgb(3B)] -> a single H2D copy per step."""
+        flat = torch.cat([rays_o.reshape(-1), rays_d.reshape(-1), near.reshape(-1), far.reshape(-1), rgb.reshape(-1)]).float()
+        return flat.contiguous().pin_memory()
+
+    def step_from_host(self, host_batch, **draws):
+        """Copies a pack_host_batch() buffer to the device, runs one training step and returns the two losses as a
+        host tensor (a blocking 8-byte D2H read, the `.item()` of train.py:325-331)."""
+        n = host_batch.numel()
+        B = n // 11
+        if getattr(self, "_hb", None) is None or self._hb.numel() != n:
+            self._hb = torch.empty(n, dtype=torch.float32, device=self.dev)
+            self._loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+        self._hb.copy_(host_batch, non_blocking=True)
+        b = self._hb
+        o, d = b[0:3 * B].view(B, 3), b[3 * B:6 * B].view(B, 3)
+        near, far, rgb = b[6 * B:7 * B], b[7 * B:8 * B], b[8 * B:11 * B].view(B, 3)
+        losses = self.step(o, d, near, far, rgb, **draws)
+        self._loss_host.copy_(losses, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self._loss_host
 
     # ---- checkpoint in the reference layout (scripts/train.py:343-364) ---------------------------------
     def optimizer_state_dict(self, lr_now: float, beta1_now: float):

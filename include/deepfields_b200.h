@@ -103,6 +103,13 @@ int dfn_mlp_backward(const dfn_point_source* src, long long P, const void* bwd_p
                      const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma, const void* stash,
                      void* dz, float* grads, void* stream);
 
+/* the two halves of dfn_mlp_backward as separate launches (stage timing; same buffers): the data-gradient chain
+ * (writes dz) and the weight/bias-gradient reduction (reads stash + dz, accumulates into grads). */
+int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const float* consts, const float* rgb, const float* sigma,
+                           const float* d_rgb, const float* d_sigma, const void* stash, void* dz, void* stream);
+int dfn_mlp_backward_wgrad(const dfn_point_source* src, long long P, const void* stash, const void* dz, float* grads,
+                           void* stream);
+
 /* single 128 x N x K tcgen05 GEMM on operand tiles in the chunk layout (bring-up / descriptor self test) */
 int dfn_umma_selftest(const void* a_tile, const void* b_tile, int N, int K, int a_mn_major, int b_mn_major,
                       unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, unsigned a_kstep, unsigned b_kstep,

@@ -98,16 +98,22 @@ def test_sample_pdf_fused(D, golden):
     assert torch.equal(s, s2)
     ref_cdf = O.pdf_to_cdf(w)
     assert (cdf.cpu() - ref_cdf).abs().max() <= 6e-7   # a few ulp(1): fp32 sum order differs from torch's
+    # tier A on the kernel's own cdf: searchsorted indices and samples are BIT-EXACT with torch (train.py:56-73)
+    s_chk, i_chk = O.invert_cdf(mids, cdf.cpu(), u)
+    assert torch.equal(inds.cpu(), i_chk)
+    assert torch.equal(s.cpu(), s_chk)
     ref_inds = T(golden["pdf_inds"])
     bad = (inds.cpu() != ref_inds)
-    # tier B: the fused cdf may differ by an ulp (sum order); every index flip must be an edge case
+    # tier B: the fused cdf may differ from torch's CPU cdf by an ulp (sum order); every index flip against the
+    # reference-generated golden must be an edge case (u within an ulp of a cdf edge)
     if bad.any():
         uu, cc = u[bad], torch.gather(ref_cdf, 1, ref_inds.clamp(max=62))[bad]
         lo = torch.gather(ref_cdf, 1, (ref_inds - 1).clamp(min=0))[bad]
         assert torch.minimum((uu - cc).abs(), (uu - lo).abs()).max() <= 7e-7
         # the golden puts u = 1 - 2^-24 on the top edge of EVERY row (cdf[-1] = 1 +- 1 ulp), hence up to B flips
         assert bad.sum() <= 2 * u.shape[0]
-    np.testing.assert_allclose(s.cpu().numpy(), golden["pdf_samples"], rtol=1e-5, atol=2e-6)
+    ok = ~bad.numpy()
+    np.testing.assert_allclose(s.cpu().numpy()[ok], golden["pdf_samples"][ok], rtol=1e-5, atol=2e-6)
     # a strided weights view (train.py:158 passes weights[..., 1:-1])
     wfull = torch.zeros(w.shape[0], 64)
     wfull[:, 1:-1] = w

@@ -53,7 +53,9 @@ def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35):
     for k in param_keys(ref32):
         g32, g16 = ref32[k].grad, ref16[k].grad
         e, e16 = rel_err(got[k], g32), rel_err(g16, g32)
-        tol = min(slack * e16 + floor, cap)
+        # a tensor whose bf16-autocast gradient is itself further than `cap` from fp32 is ill-conditioned in bf16
+        # (a sum of cancelling terms, e.g. density_layer in eval mode): there the kernel must be no worse than it
+        tol = min(slack * e16 + floor, cap) if e16 <= cap else e16
         rows.append(f"{k:26s} cuda-vs-fp32 {e:.4f}  bf16oracle-vs-fp32 {e16:.4f}  tol {tol:.4f}")
         ok = ok and e <= tol
         worst = max(worst, e)
