@@ -31,17 +31,21 @@ constexpr uint32_t kActBytes = 32 * kChunkBytes;    // 128 x 256 bf16 = 64 KB
 constexpr uint32_t kAuxBytes = 8 * kChunkBytes;     // 128 x 64 bf16  = 16 KB
 constexpr uint32_t kStageBytes = 16384;
 
-// forward job table
+// forward job table.  Every job's weight block ends with one extra K=16 slice that carries the layer bias
+// (column k=0 = bf16(bias), the rest zero); its A operand is a constant "ones" tile (column 0 = 1), so the bias
+// is added by the tensor core exactly as bf16 autocast does it (F.linear casts the bias to bf16) and the
+// epilogue has no per-column loads.
 __host__ __device__ constexpr int job_N(int j) { return j == 9 ? 128 : 256; }
-__host__ __device__ constexpr int job_kc(int j) { return j == 0 ? 8 : (j == 4 ? 40 : (j == 9 ? 36 : 32)); }
+__host__ __device__ constexpr int job_kc(int j) { return j == 0 ? 8 : (j == 4 ? 40 : (j == 9 ? 36 : 32)); }  // data chunks
+__host__ __device__ constexpr int job_kcb(int j) { return job_kc(j) + 2; }                                   // + bias slice
 __host__ __device__ constexpr int job_kc_act(int j) { return j == 0 ? 0 : 32; }  // chunks read from the act tile
-__host__ __device__ constexpr uint32_t job_bytes(int j) { return static_cast<uint32_t>(job_kc(j)) * job_N(j) * 16u; }
+__host__ __device__ constexpr uint32_t job_bytes(int j) { return static_cast<uint32_t>(job_kcb(j)) * job_N(j) * 16u; }
 __host__ __device__ constexpr uint32_t job_off(int j) {
   uint32_t o = 0;
   for (int i = 0; i < j; ++i) o += job_bytes(i);
   return o;
 }
-constexpr uint32_t kFwdPackBytes = job_off(kNumJobs);  // 1,187,840 B
+constexpr uint32_t kFwdPackBytes = job_off(kNumJobs);
 
 // dgrad job table (backward chain; B operand = W^T, reduction over the layer's outputs)
 //   b0: d feat = dZ_c0 [128x128] * color_layer.0[:, :256]      K=128 N=256
@@ -59,14 +63,12 @@ __host__ __device__ constexpr uint32_t bjob_off(int b) {
 }
 constexpr uint32_t kBwdPackBytes = bjob_off(kNumBwdJobs);
 
-// fp32 consts block (floats)
-constexpr int kConstBias = 0;                       // 9 x 256 (j0..j8)
-constexpr int kConstBias9 = 9 * 256;                // 128
-constexpr int kConstWsig = kConstBias9 + 128;       // 256, bf16-rounded density_layer.weight
+// fp32 consts block (floats): the two small heads that run on the CUDA cores
+constexpr int kConstWsig = 0;                       // 256, bf16-rounded density_layer.weight
 constexpr int kConstWc2 = kConstWsig + 256;         // 3 x 128, bf16-rounded color_layer.2.weight
-constexpr int kConstBsig = kConstWc2 + 384;         // 1
-constexpr int kConstBc2 = kConstBsig + 1;           // 3
-constexpr int kConstFloats = ((kConstBc2 + 3 + 3) / 4) * 4;  // 3080
+constexpr int kConstBsig = kConstWc2 + 384;         // 1, bf16-rounded density_layer.bias
+constexpr int kConstBc2 = kConstBsig + 1;           // 3, bf16-rounded color_layer.2.bias
+constexpr int kConstFloats = ((kConstBc2 + 3 + 3) / 4) * 4;
 constexpr uint32_t kConstBytes = kConstFloats * 4;
 
 // flat fp32 parameter order == reference state_dict / named_parameters order (model.py:99-137)

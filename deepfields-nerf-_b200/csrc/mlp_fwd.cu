@@ -1,18 +1,24 @@
 // Fused vanilla-NeRF MLP forward (reference scripts/model.py:139-187) for sm_100a.
 //
 // Persistent kernel, one CTA per SM, two 128-point tiles (slots X/Y) in flight per CTA:
-//   warp 0      : weight producer - streams packed bf16 weight blocks (16 KB) from L2 into a shared
+//   warp 0      : weight producer - streams packed bf16 weight blocks (16 KB stages) from L2 into a shared
 //                 memory ring with 1-D bulk async copies (TMA engine, mbarrier complete_tx)
-//   warp 1      : MMA issuer - one thread issues tcgen05.mma (M=128, N=256/128, K=16, bf16 -> fp32 in
-//                 TMEM); slot X accumulates in TMEM columns [0,256), slot Y in [256,512)
-//   warps 2..9  : epilogue - tcgen05.ld the accumulator, bias + ReLU, round to bf16, write the next
-//                 layer's A operand back to shared memory in the UMMA chunk layout (activations never
-//                 leave the SM); positional encodings are computed here too.
+//   warp 1      : MMA issuer - the warp runs converged and one elected lane issues tcgen05.mma (M=128,
+//                 N=256/128, K=16, bf16 -> fp32 in TMEM); slot X accumulates in TMEM columns [0,256), slot Y in
+//                 [256,512).  One ring stage (wait, MMAs, commit) is a single asm block with the election
+//                 inside: ~60 issue cycles per MMA against 128 of execution (tools/umma_bench.py, mode 9).
+//   warps 2..9  : epilogue - tcgen05.ld the accumulator, ReLU, round to bf16, write the next layer's A
+//                 operand back to shared memory in the UMMA chunk layout (activations never leave the SM);
+//                 positional encodings are computed here too.
 // While the tensor core runs layer L of slot X the epilogue warps drain layer L-1 of slot Y.
+// Biases ride along as one extra K=16 MMA per layer against a constant "ones" tile (mlp_common.cuh).
 // The sigma head (N=1) and color_layer.2 (N=3) are CUDA-core dot products inside the epilogues.
-// TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout)
-// for the backward kernels.
+// TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
+// backward kernels: the issuer of a slot bulk-copies the finished activation tile shared -> global.
 #include "mlp_common.cuh"
+#include <stdlib.h>
+#include <string.h>
+#include <utility>
 
 namespace {
 using namespace mlp;
@@ -21,18 +27,26 @@ using namespace umma;
 constexpr int kStages = 3;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;
+constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
 
 // shared memory map (bytes)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;            // 2 x 16 KB
 constexpr uint32_t kOffRing = kOffAux + 2 * kAuxBytes;           // kStages x 16 KB
-constexpr uint32_t kOffConst = kOffRing + kStages * kStageBytes;
+constexpr uint32_t kOffOnes = kOffRing + kStages * kStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
+constexpr uint32_t kOnesBytes = 2 * kChunkBytes;
+constexpr uint32_t kOffConst = kOffOnes + kOnesBytes;
 // partial head dot products of the upper column half, [2 slots][128 rows][3] f32 (sigma uses [..][0];
 // reuse across j7 / j9 of a slot is ordered by the other slot's named barrier in between)
 constexpr uint32_t kOffPart = kOffConst + kConstBytes;
 constexpr uint32_t kOffBars = kOffPart + 2 * 128 * 3 * 4;
-constexpr uint32_t kNumBars = 2 * kStages + 4;
+// barriers: full[slot][stage], empty[slot][stage] (one set per issuer: a parity wait can only tell adjacent phases
+// apart, so the two issuers must never wait on the same barrier), accfull[slot], aready[slot]
+constexpr uint32_t kNumBars = 4 * kStages + 4;
+__host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
+__host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }
+__host__ __device__ constexpr uint32_t bar_accfull_i(int t) { return 4 * kStages + t; }
+__host__ __device__ constexpr uint32_t bar_aready_i(int t) { return 4 * kStages + 2 + t; }
 constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
@@ -49,23 +63,22 @@ struct FwdArgs {
   uint8_t* stash_h;       // TRAIN: [8][n_tiles][64 KB]
   uint8_t* stash_f;       // TRAIN: [n_tiles][64 KB]
   uint8_t* stash_c;       // TRAIN: [n_tiles][32 KB]
+  long long* stats;       // bring-up only: wait-time counters of block 0 (DFN_FWD_STATS)
+  int debug;              // bring-up only (DFN_FWD_DEBUG): 1 = no weight copies, 2 = no epilogue math, 8 = wait statistics
 };
 
 __device__ __forceinline__ int tile_of(int it, int t) { return (it * 2 + t) * gridDim.x + blockIdx.x; }
 
 // ---- epilogue helpers ------------------------------------------------------------------------------
-// 32 accumulator columns -> bias, optional ReLU, bf16 -> 4 x 16 B into the act tile (+ stash)
+// 32 accumulator columns -> optional ReLU, bf16 -> 4 x 16 B into the act tile
 template <bool RELU>
-__device__ __forceinline__ void emit32(const uint32_t (&v)[32], const float* bias, uint8_t* act, uint8_t* stash,
-                                       int col0, int row, uint32_t (&packed)[16]) {
+__device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, int col0, int row, uint32_t (&packed)[16]) {
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
-    const float4 b0 = *reinterpret_cast<const float4*>(bias + col0 + g * 8);
-    const float4 b1 = *reinterpret_cast<const float4*>(bias + col0 + g * 8 + 4);
-    const float x0 = __uint_as_float(v[g * 8 + 0]) + b0.x, x1 = __uint_as_float(v[g * 8 + 1]) + b0.y;
-    const float x2 = __uint_as_float(v[g * 8 + 2]) + b0.z, x3 = __uint_as_float(v[g * 8 + 3]) + b0.w;
-    const float x4 = __uint_as_float(v[g * 8 + 4]) + b1.x, x5 = __uint_as_float(v[g * 8 + 5]) + b1.y;
-    const float x6 = __uint_as_float(v[g * 8 + 6]) + b1.z, x7 = __uint_as_float(v[g * 8 + 7]) + b1.w;
+    const float x0 = __uint_as_float(v[g * 8 + 0]), x1 = __uint_as_float(v[g * 8 + 1]);
+    const float x2 = __uint_as_float(v[g * 8 + 2]), x3 = __uint_as_float(v[g * 8 + 3]);
+    const float x4 = __uint_as_float(v[g * 8 + 4]), x5 = __uint_as_float(v[g * 8 + 5]);
+    const float x6 = __uint_as_float(v[g * 8 + 6]), x7 = __uint_as_float(v[g * 8 + 7]);
     uint4 q;
     if (RELU) {
       q.x = pack_bf16x2_relu(x0, x1); q.y = pack_bf16x2_relu(x2, x3);
@@ -77,8 +90,243 @@ __device__ __forceinline__ void emit32(const uint32_t (&v)[32], const float* bia
     packed[g * 4 + 0] = q.x; packed[g * 4 + 1] = q.y; packed[g * 4 + 2] = q.z; packed[g * 4 + 3] = q.w;
     const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
     if (act) *reinterpret_cast<uint4*>(act + off) = q;
-    if (stash) *reinterpret_cast<uint4*>(stash + off) = q;
   }
+}
+
+// ---- weight ring + MMA issue, one instantiation per job so every shape is a compile-time constant -----
+// A generic issue loop with run-time shapes costs ~300 cycles per tcgen05.mma in address arithmetic alone
+// (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
+// whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
+constexpr int job_stages(int j) { return (job_bytes(j) + kStageBytes - 1) / kStageBytes; }
+constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
+  int n = 0;
+  for (int i = 0; i < j; ++i) n += 2 * job_stages(i);
+  return n + t * job_stages(j);
+}
+
+// mbar_wait that also accumulates the cycles spent waiting (bring-up statistics)
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, long long& acc) {
+  const long long t0 = clock64();
+  mbar_wait(bar, parity);
+  acc += clock64() - t0;
+}
+
+struct ProdState {
+  uint32_t use[2][kStages];   // parity of the number of fills so far per (slot, stage)
+  int last[kStages];          // slot that used the stage last (-1: never)
+};
+
+template <int J>
+__device__ __forceinline__ void produce_job(const uint8_t* wpack, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2], int debug) {
+  constexpr uint32_t jbytes = job_bytes(J);
+  const uint8_t* src = wpack + job_off(J);
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    if (!has[t]) continue;
+#pragma unroll
+    for (int k = 0; k < job_stages(J); ++k) {
+      constexpr uint32_t kFull = kStageBytes;
+      const uint32_t off = k * kFull;
+      const uint32_t nb = (jbytes - off) < kFull ? (jbytes - off) : kFull;
+      const int stage = (stage_prefix(J, t) + k) % kStages;
+      // the previous user of this stage (either slot) must have released it
+      if (ps.last[stage] == 0) mbar_wait(bar0 + 8u * bar_empty_i(0, stage), ps.use[0][stage] ^ 1);
+      else if (ps.last[stage] == 1) mbar_wait(bar0 + 8u * bar_empty_i(1, stage), ps.use[1][stage] ^ 1);
+      ps.use[t][stage] ^= 1;
+      ps.last[stage] = t;
+      const uint32_t full = bar0 + 8u * bar_full_i(t, stage);
+      if (debug & 1) mbar_arrive(full);
+      else {
+        mbar_arrive_expect_tx(full, nb);
+        bulk_g2s(ring + stage * kStageBytes, src + off, nb, full);
+      }
+    }
+  }
+}
+template <int... Js>
+__device__ __forceinline__ void produce_all(const uint8_t* wpack, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2], int debug, std::integer_sequence<int, Js...>) {
+  (produce_job<Js>(wpack, ring, bar0, ps, has, debug), ...);
+}
+
+// One ring stage as a single asm block: bounded wait for the weights (a protocol bug traps instead of hanging),
+// NMMA x tcgen05.mma (K = 16 each) and the commit that releases the stage.  MMA i < NMMA-1 reads A at
+// a_lo + i*256 (two chunks further), the last one at a_last; B advances by B_STEP descriptor units per MMA.
+#define DFN_STAGE_HEAD                                          \
+  "{\n\t"                                                       \
+  ".reg .pred q, p, pe;\n\t"                                    \
+  ".reg .b32 cnt, al, bl;\n\t"                                  \
+  ".reg .b64 da, db;\n\t"                                       \
+  "mov.u32 cnt, 0;\n\t"                                         \
+  "SW_WAIT:\n\t"                                                \
+  "mbarrier.try_wait.parity.shared::cta.b64 q, [%0], %1;\n\t"   \
+  "@q bra SW_GO;\n\t"                                           \
+  "add.u32 cnt, cnt, 1;\n\t"                                    \
+  "setp.lt.u32 p, cnt, 8000000;\n\t"                            \
+  "@p bra SW_WAIT;\n\t"                                         \
+  "trap;\n\t"                                                   \
+  "SW_GO:\n\t"                                                  \
+  "tcgen05.fence::after_thread_sync;\n\t"                       \
+  "elect.sync _|pe, 0xffffffff;\n\t"                            \
+  "setp.ne.b32 p, %7, 0;\n\t"
+#define DFN_STAGE_FIRST                                         \
+  "mov.b64 da, {%3, %5};\n\t"                                   \
+  "mov.b64 db, {%4, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, p;\n\t"
+#define DFN_STAGE_NEXT(i)                                       \
+  "add.u32 al, %3, " #i "*256;\n\t"                             \
+  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
+  "mov.b64 da, {al, %5};\n\t"                                   \
+  "mov.b64 db, {bl, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, 1;\n\t"
+#define DFN_STAGE_LAST(i)                                       \
+  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
+  "mov.b64 da, {%9, %5};\n\t"                                   \
+  "mov.b64 db, {bl, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, 1;\n\t"
+#define DFN_STAGE_ONLY                                          \
+  "mov.b64 da, {%9, %5};\n\t"                                   \
+  "mov.b64 db, {%4, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, p;\n\t"
+#define DFN_STAGE_TAIL                                                                       \
+  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t"       \
+  "}"
+// last stage of a job: the second commit tells the epilogue that the accumulator is complete
+#define DFN_STAGE_TAIL_ACC                                                                   \
+  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t"       \
+  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%11];\n\t"      \
+  "}"
+#define DFN_STAGE_OPERANDS                                                                                     \
+  ::"r"(full_bar), "r"(parity), "r"(tacc), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc_first), "r"(empty_bar), \
+      "r"(a_last), "n"(B_STEP), "r"(acc_bar)                                                                      \
+      : "memory"
+
+// Executed by the whole (converged) issuer warp.
+template <int NMMA, int B_STEP, bool ACC>
+__device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, uint32_t tacc, uint32_t a_lo, uint32_t a_last,
+                                          uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc_first, uint32_t empty_bar,
+                                          uint32_t acc_bar) {
+  static_assert(NMMA >= 1 && NMMA <= 4, "1..4 MMAs per stage");
+  if constexpr (ACC) {
+    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 3)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL_ACC
+                       DFN_STAGE_OPERANDS);
+  } else {
+    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 3)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL
+                       DFN_STAGE_OPERANDS);
+  }
+}
+
+struct SlotCtx {
+  uint32_t ph0, ph1, ph2;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
+  uint32_t pa;              // phase of this slot's aready barrier
+  bool has;                 // the slot has a tile in the current iteration
+  int tile, prev_tile;      // the slot's tile in the current / previous iteration (-1: none)
+};
+struct IssueCtx {
+  uint32_t sbase, bar0, tmem_base;
+  SlotCtx s0, s1;
+  int n_tiles, lane;
+  uint8_t *stash_h, *stash_f, *stash_c;
+  int debug;
+  long long w_aready;
+};
+template <int T>
+__device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
+  if constexpr (T == 0) return c.s0; else return c.s1;
+}
+template <int S>
+__device__ __forceinline__ uint32_t& ph_of(SlotCtx& c) {
+  if constexpr (S == 0) return c.ph0;
+  else if constexpr (S == 1) return c.ph1;
+  else return c.ph2;
+}
+
+// where chunk kc of job J's A operand lives (descriptor address units relative to the three bases)
+template <int J>
+__device__ __forceinline__ uint32_t a_chunk_lo(int kc, uint32_t a_act, uint32_t a_aux, uint32_t a_ones) {
+  constexpr int KC = job_kc(J), KC_ACT = job_kc_act(J);
+  if (kc >= KC) return a_ones + (kc - KC) * (kChunkBytes >> 4);
+  if (kc < KC_ACT) return a_act + kc * (kChunkBytes >> 4);
+  return a_aux + (kc - KC_ACT) * (kChunkBytes >> 4);
+}
+
+template <int J, int T, int K>
+__device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc) {
+  constexpr int N = job_N(J), KCB = job_kcb(J);
+  constexpr uint32_t idesc = instr_desc_bf16(128, N, 0, 0);
+  constexpr uint32_t b_chunk = N * 16;                    // bytes per K chunk of the weight block
+  constexpr int CPS = kStageBytes / b_chunk;              // chunks per stage: 4 (N=256) or 8 (N=128)
+  constexpr uint32_t hi = desc_hi(128);
+  constexpr int B_STEP = 2 * (b_chunk >> 4);              // descriptor address units per MMA (two K chunks)
+  constexpr int kc0 = K * CPS;
+  constexpr int stage = (stage_prefix(J, T) + K) % kStages;
+  constexpr int nchunk = (KCB - kc0) < CPS ? (KCB - kc0) : CPS;
+  constexpr bool last = K == job_stages(J) - 1;
+  const uint32_t full = c.bar0 + 8u * bar_full_i(T, stage), empty = c.bar0 + 8u * bar_empty_i(T, stage);
+  const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
+  const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kStageBytes, b_chunk);
+  const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
+  const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
+  constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
+  uint32_t& ph = ph_of<stage>(slot_of<T>(c));
+  stage_mma<nchunk / 2, B_STEP, last>(full, ph, tacc, a_lo, a_last, b_lo, hi, idesc, accf, empty, accfull);
+  ph ^= 1;
+}
+template <int J, int T, int... Ks>
+__device__ __forceinline__ void issue_stages(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc,
+                                             std::integer_sequence<int, Ks...>) {
+  (issue_stage<J, T, Ks>(c, a_act, a_aux, a_ones, tacc), ...);
+}
+
+// Runs on the whole issuer warp (converged); single-lane work (bulk copies) is done by lane 0.
+template <int J, int T, bool TRAIN>
+__device__ __forceinline__ void issue_job(IssueCtx& c) {
+  SlotCtx& sc = slot_of<T>(c);
+  if (!sc.has) return;
+  const uint32_t aready = c.bar0 + 8u * bar_aready_i(T);
+  if (c.debug & 8) mbar_wait_t(aready, sc.pa, c.w_aready); else mbar_wait(aready, sc.pa);
+  sc.pa ^= 1;
+  tc_fence_after();
+  const uint32_t act_addr = c.sbase + kOffAct + T * kActBytes;
+  if (TRAIN && c.lane == 0) {  // the finished activation tile of the previous layer -> stash (bulk copy shared -> global)
+    // the previous bulk copy of this slot read the tile that the epilogue has just overwritten; it finished long ago
+    // (checked before that epilogue could start, see below), so only this slot's newest copy is ever in flight
+    if (J == 0) {
+      if (sc.prev_tile >= 0) bulk_s2g(c.stash_c + (static_cast<size_t>(sc.prev_tile) << 15), act_addr, 32768);
+    } else if (J <= 8) {
+      bulk_s2g(c.stash_h + ((static_cast<size_t>(J - 1) * c.n_tiles + sc.tile) << 16), act_addr, 65536);
+    } else {
+      bulk_s2g(c.stash_f + (static_cast<size_t>(sc.tile) << 16), act_addr, 65536);
+    }
+    bulk_commit();
+  }
+  const uint32_t a_act = desc_lo(act_addr, kChunkBytes);
+  const uint32_t a_aux = desc_lo(c.sbase + kOffAux + T * kAuxBytes, kChunkBytes);
+  const uint32_t a_ones = desc_lo(c.sbase + kOffOnes, kChunkBytes);
+  const uint32_t tacc = c.tmem_base + T * 256;
+  // all stages but the last; the last one also commits accfull, and the epilogue it releases overwrites the tile
+  // the bulk copy reads -> wait for the copy's reads in between
+  issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J) - 1>{});
+  if (TRAIN) {
+    if (c.lane == 0) bulk_wait_read_all();
+    __syncwarp();
+  }
+  issue_stage<J, T, job_stages(J) - 1>(c, a_act, a_aux, a_ones, tacc);
+}
+template <bool TRAIN, int... Js>
+__device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
+  ((issue_job<Js, 0, TRAIN>(c), issue_job<Js, 1, TRAIN>(c)), ...);
 }
 
 template <bool TRAIN>
@@ -87,19 +335,21 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar0 = sbase + kOffBars;
-  auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
-  auto bar_wempty = [&](int s) { return bar0 + 8u * (kStages + s); };
-  auto bar_accfull = [&](int t) { return bar0 + 8u * (2 * kStages + t); };
-  auto bar_aready = [&](int t) { return bar0 + 8u * (2 * kStages + 2 + t); };
+  auto bar_accfull = [&](int t) { return bar0 + 8u * bar_accfull_i(t); };
+  auto bar_aready = [&](int t) { return bar0 + 8u * bar_aready_i(t); };
   float* consts = reinterpret_cast<float*>(smem + kOffConst);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(bar_wfull(s), 1); mbar_init(bar_wempty(s), 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiThreads); }
+    for (int i = 0; i < 4 * kStages; ++i) mbar_init(bar0 + 8u * i, 1);
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
   for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
+  // ones tile: [2 chunks][128 rows][8 bf16], column 0 of every row = 1.0
+  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += kThreads)
+    *reinterpret_cast<uint4*>(smem + kOffOnes + i * 16) = make_uint4(i < 128 ? 0x3F80u : 0u, 0u, 0u, 0u);
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -110,62 +360,43 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
   if (warp == 0) {
     // ================= weight producer =================
     if (lane == 0) {
-      int stage = 0; uint32_t ph = 0;
+      ProdState ps;
+#pragma unroll
+      for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
       for (int it = 0; it < n_it; ++it) {
-        for (int j = 0; j < kNumJobs; ++j) {
-          const uint32_t jbytes = job_bytes(j);
-          const uint8_t* src = a.wpack + job_off(j);
-          for (int t = 0; t < 2; ++t) {
-            if (tile_of(it, t) >= a.n_tiles) continue;
-            for (uint32_t off = 0; off < jbytes; off += kStageBytes) {
-              const uint32_t nb = (jbytes - off) < kStageBytes ? (jbytes - off) : kStageBytes;
-              mbar_wait(bar_wempty(stage), ph ^ 1);
-              mbar_arrive_expect_tx(bar_wfull(stage), nb);
-              bulk_g2s(sbase + kOffRing + stage * kStageBytes, src + off, nb, bar_wfull(stage));
-              if (++stage == kStages) { stage = 0; ph ^= 1; }
-            }
-          }
-        }
+        const bool has[2] = {tile_of(it, 0) < a.n_tiles, tile_of(it, 1) < a.n_tiles};
+        produce_all(a.wpack, sbase + kOffRing, bar0, ps, has, a.debug, std::make_integer_sequence<int, kNumJobs>{});
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      int stage = 0; uint32_t ph = 0;
-      uint32_t pa[2] = {0, 0};
-      for (int it = 0; it < n_it; ++it) {
-        for (int j = 0; j < kNumJobs; ++j) {
-          const int N = job_N(j), kc_total = job_kc(j), kc_act = job_kc_act(j);
-          const uint32_t idesc = instr_desc_bf16(128, N, 0, 0);
-          const uint32_t b_chunk = N * 16;                    // bytes per K chunk of the weight block
-          const int chunks_per_stage = kStageBytes / b_chunk;  // 4 (N=256) or 8 (N=128)
-          for (int t = 0; t < 2; ++t) {
-            if (tile_of(it, t) >= a.n_tiles) continue;
-            mbar_wait(bar_aready(t), pa[t]); pa[t] ^= 1;
-            tc_fence_after();
-            const uint32_t act = sbase + kOffAct + t * kActBytes;
-            const uint32_t aux = sbase + kOffAux + t * kAuxBytes;
-            const uint32_t tacc = tmem_base + t * 256;
-            for (int kc0 = 0; kc0 < kc_total; kc0 += chunks_per_stage) {
-              mbar_wait(bar_wfull(stage), ph);
-              tc_fence_after();
-              const uint32_t wst = sbase + kOffRing + stage * kStageBytes;
-              const int nchunk = (kc_total - kc0) < chunks_per_stage ? (kc_total - kc0) : chunks_per_stage;
-              for (int c = 0; c < nchunk; c += 2) {
-                const int kc = kc0 + c;
-                const uint32_t a_addr = kc < kc_act ? act + kc * kChunkBytes : aux + (kc - kc_act) * kChunkBytes;
-                const uint64_t ad = smem_desc(a_addr, kChunkBytes, 128);
-                const uint64_t bd = smem_desc(wst + c * b_chunk, b_chunk, 128);
-                mma_bf16(tacc, ad, bd, idesc, kc > 0 ? 1u : 0u);
-              }
-              mma_commit(bar_wempty(stage));
-              if (++stage == kStages) { stage = 0; ph ^= 1; }
-            }
-            mma_commit(bar_accfull(t));
-          }
-        }
-      }
+    // ================= MMA issuer (whole warp, converged; one elected lane issues) =================
+    IssueCtx c{};
+    c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.debug = a.debug; c.lane = lane;
+    c.n_tiles = a.n_tiles; c.stash_h = a.stash_h; c.stash_f = a.stash_f; c.stash_c = a.stash_c;
+    c.s0 = SlotCtx{0, 0, 0, 0, false, -1, -1};
+    c.s1 = c.s0;
+    c.w_aready = 0;
+    const long long t0 = clock64();
+    for (int it = 0; it < n_it; ++it) {
+      c.s0.tile = tile_of(it, 0); c.s0.has = c.s0.tile < a.n_tiles;
+      c.s1.tile = tile_of(it, 1); c.s1.has = c.s1.tile < a.n_tiles;
+      issue_all<TRAIN>(c, std::make_integer_sequence<int, kNumJobs>{});
+      c.s0.prev_tile = c.s0.has ? c.s0.tile : -1;
+      c.s1.prev_tile = c.s1.has ? c.s1.tile : -1;
     }
+    if (TRAIN) {  // colour hidden layer of the last tile of each slot
+      if (c.s0.prev_tile >= 0) {
+        mbar_wait(bar_aready(0), c.s0.pa);
+        if (lane == 0) { bulk_s2g(c.stash_c + (static_cast<size_t>(c.s0.prev_tile) << 15), sbase + kOffAct, 32768); bulk_commit(); }
+      }
+      if (c.s1.prev_tile >= 0) {
+        mbar_wait(bar_aready(1), c.s1.pa);
+        if (lane == 0) { bulk_s2g(c.stash_c + (static_cast<size_t>(c.s1.prev_tile) << 15), sbase + kOffAct + kActBytes, 32768); bulk_commit(); }
+      }
+      if (lane == 0) bulk_wait_all();
+      __syncwarp();
+    }
+    if (a.stats && blockIdx.x == 0 && lane == 0) { a.stats[2] = clock64() - t0; a.stats[3] = c.w_aready; }
   } else {
     // ================= epilogue / PE warps =================
     const int ew = warp - 2;
@@ -175,10 +406,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     float* part = reinterpret_cast<float*>(smem + kOffPart);
     uint32_t pf[2] = {0, 0};
+    long long w_acc = 0;
+    const long long t_epi0 = clock64();
 
     auto point_of = [&](int tile) {
       long long p = static_cast<long long>(tile) * kTile + row;
       return p < a.P ? p : a.P - 1;
+    };
+    // activations / encodings written -> visible to the async proxy -> one arrive per warp
+    auto publish = [&](int t) {
+      tc_fence_before();
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_aready(t));
     };
     // initial PE for both slots
     for (int t = 0; t < 2; ++t) {
@@ -188,8 +428,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
         load_point(a.src, point_of(tile), x, d);
         write_pe_row(smem + kOffAux + t * kAuxBytes, nullptr, row, hh, x, d);
       }
-      fence_proxy_async();
-      mbar_arrive(bar_aready(t));
+      publish(t);
     }
 
     for (int it = 0; it < n_it; ++it) {
@@ -201,16 +440,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
           uint8_t* aux = smem + kOffAux + t * kAuxBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
           const long long p = static_cast<long long>(tile) * kTile + row;
-          mbar_wait(bar_accfull(t), pf[t]); pf[t] ^= 1;
+          if (a.debug & 8) mbar_wait_t(bar_accfull(t), pf[t], w_acc); else mbar_wait(bar_accfull(t), pf[t]);
+          pf[t] ^= 1;
           tc_fence_after();
 
-          if (j < 9) {
-            const float* bias = consts + kConstBias + j * 256;
-            uint8_t* stash = nullptr;
-            if (TRAIN) {
-              stash = (j < 8) ? a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16)
-                              : a.stash_f + (static_cast<size_t>(tile) << 16);
-            }
+          if (a.debug & 2) {
+            publish(t);
+          } else if (j < 9) {
             float sdot = 0.f;
             const int c0 = hh * 128;
             uint32_t v0[32], v1[32], pk[16];
@@ -222,8 +458,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
               uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
               if (cc < 3) tmem_ld32(tacc + c0 + (cc + 1) * 32, nxt);
               const int col0 = c0 + cc * 32;
-              if (j == 8) emit32<false>(cur, bias, act, stash, col0, row, pk);
-              else emit32<true>(cur, bias, act, stash, col0, row, pk);
+              if (j == 8) emit32<false>(cur, act, col0, row, pk);
+              else emit32<true>(cur, act, col0, row, pk);
               if (j == 7) {
                 const float* ws = consts + kConstWsig + col0;
 #pragma unroll
@@ -239,9 +475,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
               load_point(a.src, p < a.P ? p : a.P - 1, x, d);
               write_pe_row(nullptr, aux, row, hh, x, d);
             }
-            tc_fence_before();
-            fence_proxy_async();
-            mbar_arrive(bar_aready(t));
+            publish(t);
             if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
               if (hh == 1) part[(t * 128 + row) * 3] = sdot;
               named_bar_sync(1, kEpiThreads);
@@ -254,8 +488,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
             }
           } else {
             // j == 9: colour hidden layer (N=128) + color_layer.2 + sigmoid
-            const float* bias = consts + kConstBias9;
-            uint8_t* stash = TRAIN ? a.stash_c + (static_cast<size_t>(tile) << 15) : nullptr;
             float r0 = 0.f, r1 = 0.f, r2 = 0.f;
             const int c0 = hh * 64;
             uint32_t v0[32], v1[32], pk[16];
@@ -266,7 +498,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
             for (int cc = 0; cc < 2; ++cc) {
               uint32_t (&cur)[32] = cc ? v1 : v0;
               const int col0 = c0 + cc * 32;
-              emit32<true>(cur, bias, nullptr, stash, col0, row, pk);
+              emit32<true>(cur, TRAIN ? act : nullptr, col0, row, pk);   // TRAIN: the issuer stashes it from act
               const float* w0 = consts + kConstWc2 + col0;
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
@@ -283,9 +515,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
               load_point(a.src, point_of(ntile), x, d);
               write_pe_row(aux, nullptr, row, hh, x, d);
             }
-            tc_fence_before();
-            fence_proxy_async();
-            mbar_arrive(bar_aready(t));
+            publish(t);
             float* pr = part + (t * 128 + row) * 3;
             if (hh == 1) { pr[0] = r0; pr[1] = r1; pr[2] = r2; }
             named_bar_sync(1, kEpiThreads);
@@ -301,6 +531,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
         }
       }
     }
+    if (a.stats && blockIdx.x == 0 && threadIdx.x == 64) { a.stats[5] = clock64() - t_epi0; a.stats[6] = w_acc; }
   }
 
   tc_fence_before();
@@ -332,13 +563,15 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
       const int e = idx - job_off(j) / 2;
       const int N = job_N(j);
       const int kc = e / (N * 8), n = (e / 8) % N, k = kc * 8 + (e & 7);
+      const int layer = j < 8 ? j : (j == 8 ? 9 : 10);   // reference layer index of job j
+      const int kdata = job_kc(j) * 8;
       float v = 0.f;
-      if (j == 0) { if (k < 63) v = param_w(params, 0, n, k); }
-      else if (j <= 3) v = param_w(params, j, n, k);
-      else if (j == 4) { if (k < 256) v = param_w(params, 4, n, k); else if (k - 256 < 63) v = param_w(params, 4, n, k); }
-      else if (j <= 7) v = param_w(params, j, n, k);
-      else if (j == 8) v = param_w(params, 9, n, k);
-      else { if (k < 256) v = param_w(params, 10, n, k); else if (k - 256 < 27) v = param_w(params, 10, n, k); }
+      if (k >= kdata) {  // bias slice: column 0 carries the bias, the other 15 are zero
+        if (k == kdata) v = params[po.b[layer] + n];
+      } else if (j == 0) { if (k < 63) v = param_w(params, 0, n, k); }
+      else if (j == 4) { if (k < 256 + 63) v = param_w(params, 4, n, k); }
+      else if (j == 9) { if (k < 256 + 27) v = param_w(params, 10, n, k); }
+      else v = param_w(params, layer, n, k);
       fwd[idx] = __float2bfloat16_rn(v);
     } else if (idx < nf + nb) {
       const int bi = idx - nf;
@@ -351,15 +584,10 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
     } else {
       const int c = idx - nf - nb;
       float v = 0.f;
-      if (c < kConstBias9) {
-        const int j = c / 256, n = c % 256;
-        const int layer = j < 8 ? j : 9;
-        v = params[po.b[layer] + n];
-      } else if (c < kConstWsig) v = params[po.b[10] + (c - kConstBias9)];
-      else if (c < kConstWc2) v = round_bf16(params[po.w[8] + (c - kConstWsig)]);
+      if (c < kConstWc2) v = round_bf16(params[po.w[8] + (c - kConstWsig)]);
       else if (c < kConstBsig) v = round_bf16(params[po.w[11] + (c - kConstWc2)]);
-      else if (c == kConstBsig) v = params[po.b[8]];
-      else if (c < kConstBc2 + 3) v = params[po.b[11] + (c - kConstBc2)];
+      else if (c == kConstBsig) v = round_bf16(params[po.b[8]]);
+      else if (c < kConstBc2 + 3) v = round_bf16(params[po.b[11] + (c - kConstBc2)]);
       consts[c] = v;
     }
   }
@@ -409,6 +637,12 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   }
   const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (const char* e = getenv("DFN_FWD_DEBUG")) a.debug = atoi(e);
+  static long long* d_stats = nullptr;
+  if (getenv("DFN_FWD_STATS")) {
+    if (!d_stats) cudaMalloc(&d_stats, 64);
+    a.stats = d_stats;
+  }
   if (stash) {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
     mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
@@ -417,5 +651,11 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
     mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
   }
   DFN_CHECK_LAUNCH("mlp_forward");
+  if (a.stats) {
+    long long h[8];
+    cudaMemcpy(h, a.stats, 64, cudaMemcpyDeviceToHost);
+    fprintf(stderr, "fwd stats (block 0, cycles): mma total %lld wait_aready %lld | epi total %lld wait_accfull %lld\n", h[2], h[3],
+            h[5], h[6]);
+  }
   return DFN_OK;
 }

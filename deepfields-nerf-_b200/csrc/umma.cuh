@@ -128,6 +128,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= static_cast<uint64_t>(1) << 46;
   return d;
 }
+// The same descriptor split into its two 32-bit words, so an issue loop can keep the constant parts in
+// registers and only add to the 14-bit address field:  lo = addr>>4 | (LBO>>4)<<16,  hi = SBO>>4 | version.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFFu) | ((lbo_bytes >> 4) << 16);
+}
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+
 // instruction descriptor for kind::f16, bf16 x bf16 -> fp32, dense
 __host__ __device__ constexpr uint32_t instr_desc_bf16(uint32_t M, uint32_t N, uint32_t a_mn_major, uint32_t b_mn_major) {
   return (1u << 4)                 // D format  : f32

@@ -112,8 +112,18 @@ def test_sample_pdf_fused(D, golden):
         assert torch.minimum((uu - cc).abs(), (uu - lo).abs()).max() <= 7e-7
         # the golden puts u = 1 - 2^-24 on the top edge of EVERY row (cdf[-1] = 1 +- 1 ulp), hence up to B flips
         assert bad.sum() <= 2 * u.shape[0]
-    ok = ~bad.numpy()
-    np.testing.assert_allclose(s.cpu().numpy()[ok], golden["pdf_samples"][ok], rtol=1e-5, atol=2e-6)
+    # where the index agrees, the sample may still move with the cdf's last bit: t = (u - c0) / (c1 - c0) amplifies an
+    # ulp of the cdf by 1 / (c1 - c0) (>= 1e-5 by train.py:71), so the bound is per sample
+    ok = ~bad
+    c1 = torch.gather(ref_cdf, 1, ref_inds.clamp(max=62))
+    c0 = torch.gather(ref_cdf, 1, (ref_inds - 1).clamp(min=0))
+    b1 = torch.gather(mids, 1, ref_inds.clamp(max=62))
+    b0 = torch.gather(mids, 1, (ref_inds - 1).clamp(min=0))
+    denom = (c1 - c0)
+    denom = torch.where(denom < 1e-5, torch.ones_like(denom), denom)
+    ref_s = T(golden["pdf_samples"])
+    tol = 1e-5 * ref_s.abs() + 2e-6 + 2.5e-7 * (b1 - b0).abs() / denom
+    assert bool(((s.cpu() - ref_s).abs() <= tol)[ok].all())
     # a strided weights view (train.py:158 passes weights[..., 1:-1])
     wfull = torch.zeros(w.shape[0], 64)
     wfull[:, 1:-1] = w
