@@ -28,7 +28,7 @@ def test_header_symbols_exported(D):
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
         assert name in D._lib.SIGNATURES, f"{name} has no ctypes signature"
     assert lib.dfn_abi_version() == 1
-    assert lib.dfn_mlp_fwd_pack_bytes() == 1187840
+    assert lib.dfn_mlp_fwd_pack_bytes() == 1265664
     assert lib.dfn_mlp_stash_bytes(129) == 2 * (9 * 65536 + 32768)
 
 
