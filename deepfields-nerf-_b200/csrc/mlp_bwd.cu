@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
         }
         const uint4 q4 = make_uint4(o4[0], o4[1], o4[2], o4[3]);
         *reinterpret_cast<uint4*>(act + off) = q4;
-        *reinterpret_cast<uint4*>(dzc0 + off) = q4;
+        st_global_v4(dzc0 + off, o4[0], o4[1], o4[2], o4[3]);
       }
     };
 
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
               }
               const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
               if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;
-              *reinterpret_cast<uint4*>(dst + off) = o;
+              st_global_v4(dst + off, o.x, o.y, o.z, o.w);
             }
             if (cc < 3) tmem_ld_wait();
           }

@@ -14,7 +14,7 @@
 // Biases ride along as one extra K=16 MMA per layer against a constant "ones" tile (mlp_common.cuh).
 // The sigma head (N=1) and color_layer.2 (N=3) are CUDA-core dot products inside the epilogues.
 // TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
-// backward kernels: the issuer of a slot bulk-copies the finished activation tile shared -> global.
+// backward kernels; that is done by 8 extra "stash" warps which read the accumulator a second time (see below).
 #include "mlp_common.cuh"
 #include <stdlib.h>
 #include <string.h>
@@ -27,7 +27,9 @@ using namespace umma;
 constexpr int kStages = 3;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
+constexpr int kStashWarps = 8;               // TRAIN only
+constexpr int kThreadsInfer = 64 + kEpiThreads;                    // producer, issuer, 8 epilogue warps
+constexpr int kThreadsTrain = kThreadsInfer + kStashWarps * 32;    // + 8 stash warps
 
 // shared memory map (bytes)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
@@ -70,9 +72,19 @@ struct FwdArgs {
 __device__ __forceinline__ int tile_of(int it, int t) { return (it * 2 + t) * gridDim.x + blockIdx.x; }
 
 // ---- epilogue helpers ------------------------------------------------------------------------------
+// the first NC packed 32-column groups of one row -> stash (global); a warp covers 512 contiguous bytes per chunk
+template <int NC>
+__device__ __forceinline__ void stash_row(uint8_t* stash, int col0, int row, const uint32_t (&keep)[64]) {
+#pragma unroll
+  for (int g = 0; g < NC * 4; ++g) {
+    const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
+    st_global_v4(stash + off, keep[g * 4], keep[g * 4 + 1], keep[g * 4 + 2], keep[g * 4 + 3]);
+  }
+}
+
 // 32 accumulator columns -> optional ReLU, bf16 -> 4 x 16 B into the act tile
 template <bool RELU>
-__device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, int col0, int row, uint32_t (&packed)[16]) {
+__device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, int col0, int row, uint32_t* packed /* 16 */) {
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
     const float x0 = __uint_as_float(v[g * 8 + 0]), x1 = __uint_as_float(v[g * 8 + 1]);
@@ -299,30 +311,12 @@ __device__ __forceinline__ void issue_job(IssueCtx& c) {
   sc.pa ^= 1;
   tc_fence_after();
   const uint32_t act_addr = c.sbase + kOffAct + T * kActBytes;
-  if (TRAIN && c.lane == 0) {  // the finished activation tile of the previous layer -> stash (bulk copy shared -> global)
-    // the previous bulk copy of this slot read the tile that the epilogue has just overwritten; it finished long ago
-    // (checked before that epilogue could start, see below), so only this slot's newest copy is ever in flight
-    if (J == 0) {
-      if (sc.prev_tile >= 0) bulk_s2g(c.stash_c + (static_cast<size_t>(sc.prev_tile) << 15), act_addr, 32768);
-    } else if (J <= 8) {
-      bulk_s2g(c.stash_h + ((static_cast<size_t>(J - 1) * c.n_tiles + sc.tile) << 16), act_addr, 65536);
-    } else {
-      bulk_s2g(c.stash_f + (static_cast<size_t>(sc.tile) << 16), act_addr, 65536);
-    }
-    bulk_commit();
-  }
   const uint32_t a_act = desc_lo(act_addr, kChunkBytes);
   const uint32_t a_aux = desc_lo(c.sbase + kOffAux + T * kAuxBytes, kChunkBytes);
   const uint32_t a_ones = desc_lo(c.sbase + kOffOnes, kChunkBytes);
   const uint32_t tacc = c.tmem_base + T * 256;
-  // all stages but the last; the last one also commits accfull, and the epilogue it releases overwrites the tile
-  // the bulk copy reads -> wait for the copy's reads in between
-  issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J) - 1>{});
-  if (TRAIN) {
-    if (c.lane == 0) bulk_wait_read_all();
-    __syncwarp();
-  }
-  issue_stage<J, T, job_stages(J) - 1>(c, a_act, a_aux, a_ones, tacc);
+  // the last stage also commits accfull
+  issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J)>{});
 }
 template <bool TRAIN, int... Js>
 __device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
@@ -330,7 +324,7 @@ __device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int
 }
 
 template <bool TRAIN>
-__global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
+__global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_fwd_kernel(const FwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t sbase = smem_u32(smem);
@@ -341,13 +335,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < 4 * kStages; ++i) mbar_init(bar0 + 8u * i, 1);
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps); }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (TRAIN ? kStashWarps : 0)); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
-  for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
+  for (int i = threadIdx.x; i < kConstFloats; i += blockDim.x) consts[i] = a.consts[i];
   // ones tile: [2 chunks][128 rows][8 bf16], column 0 of every row = 1.0
-  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += kThreads)
+  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += blockDim.x)
     *reinterpret_cast<uint4*>(smem + kOffOnes + i * 16) = make_uint4(i < 128 ? 0x3F80u : 0u, 0u, 0u, 0u);
   fence_proxy_async();
   tc_fence_before();
@@ -384,19 +378,59 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
       c.s0.prev_tile = c.s0.has ? c.s0.tile : -1;
       c.s1.prev_tile = c.s1.has ? c.s1.tile : -1;
     }
-    if (TRAIN) {  // colour hidden layer of the last tile of each slot
-      if (c.s0.prev_tile >= 0) {
-        mbar_wait(bar_aready(0), c.s0.pa);
-        if (lane == 0) { bulk_s2g(c.stash_c + (static_cast<size_t>(c.s0.prev_tile) << 15), sbase + kOffAct, 32768); bulk_commit(); }
-      }
-      if (c.s1.prev_tile >= 0) {
-        mbar_wait(bar_aready(1), c.s1.pa);
-        if (lane == 0) { bulk_s2g(c.stash_c + (static_cast<size_t>(c.s1.prev_tile) << 15), sbase + kOffAct + kActBytes, 32768); bulk_commit(); }
-      }
-      if (lane == 0) bulk_wait_all();
-      __syncwarp();
-    }
     if (a.stats && blockIdx.x == 0 && lane == 0) { a.stats[2] = clock64() - t0; a.stats[3] = c.w_aready; }
+  } else if (warp >= 2 + kEpiWarps) {
+    // ================= stash warps (TRAIN) =================
+    // A second set of 8 warps drains every finished accumulator again (TMEM reads are cheap and do not touch shared
+    // memory), applies the same ReLU / bf16 rounding and stores the tile to the activation stash.  The stores throttle
+    // at HBM rate (64 KB per tile and layer); issued from the epilogue warps they sat on the critical path of the
+    // next MMA and doubled the forward time.  Here only the TMEM read is ordered before the next MMA of the slot
+    // (these warps arrive on the same aready barrier), the stores drain in the background.
+    if (TRAIN) {
+      const int sw = warp - (2 + kEpiWarps);
+      const int q = warp & 3, hh = sw >> 2, row = q * 32 + lane;
+      const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
+      uint32_t pf[2] = {0, 0};
+      for (int t = 0; t < 2; ++t) {   // counterpart of the initial PE publish
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_aready(t));
+      }
+      for (int it = 0; it < n_it; ++it)
+        for (int j = 0; j < kNumJobs; ++j)
+          for (int t = 0; t < 2; ++t) {
+            const int tile = tile_of(it, t);
+            if (tile >= a.n_tiles) continue;
+            const uint32_t tacc = tmem_base + t * 256 + lane_sel;
+            mbar_wait(bar_accfull(t), pf[t]);
+            pf[t] ^= 1;
+            tc_fence_after();
+            uint32_t v[32], keep[64];
+            if (j < 9) {
+              const int c0 = hh * 128;
+#pragma unroll
+              for (int cc = 0; cc < 4; ++cc) {
+                tmem_ld32(tacc + c0 + cc * 32, v);
+                tmem_ld_wait();
+                if (j == 8) emit32<false>(v, nullptr, 0, row, keep + cc * 16);
+                else emit32<true>(v, nullptr, 0, row, keep + cc * 16);
+              }
+            } else {
+              const int c0 = hh * 64;
+#pragma unroll
+              for (int cc = 0; cc < 2; ++cc) {
+                tmem_ld32(tacc + c0 + cc * 32, v);
+                tmem_ld_wait();
+                emit32<true>(v, nullptr, 0, row, keep + cc * 16);
+              }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_aready(t));
+            if (j < 8) stash_row<4>(a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16), hh * 128, row, keep);
+            else if (j == 8) stash_row<4>(a.stash_f + (static_cast<size_t>(tile) << 16), hh * 128, row, keep);
+            else stash_row<2>(a.stash_c + (static_cast<size_t>(tile) << 15), hh * 64, row, keep);
+          }
+    }
   } else {
     // ================= epilogue / PE warps =================
     const int ew = warp - 2;
@@ -498,7 +532,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
             for (int cc = 0; cc < 2; ++cc) {
               uint32_t (&cur)[32] = cc ? v1 : v0;
               const int col0 = c0 + cc * 32;
-              emit32<true>(cur, TRAIN ? act : nullptr, col0, row, pk);   // TRAIN: the issuer stashes it from act
+              emit32<true>(cur, nullptr, col0, row, pk);
               const float* w0 = consts + kConstWc2 + col0;
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
@@ -645,10 +679,10 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   }
   if (stash) {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<true><<<grid, kThreadsTrain, kSmemBytes, st>>>(a);
   } else {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<false><<<grid, kThreadsInfer, kSmemBytes, st>>>(a);
   }
   DFN_CHECK_LAUNCH("mlp_forward");
   if (a.stats) {
