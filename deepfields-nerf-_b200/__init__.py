@@ -4,7 +4,7 @@ mohamedhaiham94/DeepFields-NeRF- (scripts/sampling.py, model.py, train.py, extra
 Import as `deepfields_nerf_b200` (see deepfields_nerf_b200.py at the repository root)."""
 from . import _lib, ops  # noqa: F401
 from .sampling import StratifiedSampler  # noqa: F401
-from .model import OptimizedPositionalEncoding, OptimizedVanillaNeRF, get_nerf_models  # noqa: F401
+from .model import OptimizedPositionalEncoding, OptimizedVanillaNeRF, get_nerf_models, InstantNGP  # noqa: F401
 from .train import (  # noqa: F401
     sample_pdf, raw2outputs, process_rays_in_chunks, forward_pass, FusedTrainer, RayStore, onecycle_tables, train,
 )
@@ -14,7 +14,7 @@ from .extract_vol import (  # noqa: F401
 from .config import load_config  # noqa: F401
 
 __all__ = [
-    "StratifiedSampler", "OptimizedPositionalEncoding", "OptimizedVanillaNeRF", "get_nerf_models", "sample_pdf",
+    "StratifiedSampler", "OptimizedPositionalEncoding", "OptimizedVanillaNeRF", "get_nerf_models", "InstantNGP", "sample_pdf",
     "raw2outputs", "process_rays_in_chunks", "forward_pass", "FusedTrainer", "RayStore", "onecycle_tables", "train", "generate_3d_grid",
     "volume_extraction", "apply_otsu_threshold", "save_volume", "extract_volume_fused", "load_config", "ops",
 ]

@@ -172,3 +172,15 @@ def get_nerf_models(pos_L=10, dir_L=4, hidden_dim=256, include_input_pos=True, i
     coarse = OptimizedVanillaNeRF(pos_L, dir_L, hidden_dim, include_input_pos, include_input_dir).to(device)
     fine = OptimizedVanillaNeRF(pos_L, dir_L, hidden_dim, include_input_pos, include_input_dir).to(device)
     return coarse, fine
+
+
+class InstantNGP:
+    """scripts/instantngp.py:7-104.  Same constructor contract (ValueError for an unknown nerf_type, :9-21); the
+    hash-grid / SH / FullyFusedMLP arithmetic lives in tiny-cuda-nn (un-vendored submodule, commit 74ea173d), which
+    cannot be pinned here, so the variant is not built yet."""
+
+    def __init__(self, nerf_type="large"):
+        if nerf_type not in ("small", "medium", "large"):
+            raise ValueError(f"Unknown nerf_type: {nerf_type}")
+        raise NotImplementedError("InstantNGP (tiny-cuda-nn semantics) is not built in this round: use ngp: false "
+                                  "(OptimizedVanillaNeRF); see DESIGN.md section 7")

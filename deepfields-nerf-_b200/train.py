@@ -353,3 +353,17 @@ def train(cfg_in):
         tr.save_checkpoint(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
         print(f"Training completed in {time.time() - t0:.2f}s")
     return tr
+
+
+def main(argv=None):
+    """CLI of scripts/train.py:373-380: `--cfg_path cfg/<scene>.yml`."""
+    import argparse
+    from .config import load_config
+    ap = argparse.ArgumentParser(description="Train a NeRF (B200-native hot path)")
+    ap.add_argument("--cfg_path", type=str, required=True)
+    args = ap.parse_args(argv)
+    train(load_config(args.cfg_path))
+
+
+if __name__ == "__main__":
+    main()
