@@ -272,7 +272,7 @@ int dfn_launch_wgrad(const dfn_point_source* src, long long P, int n_tiles, cons
                      float* grads, cudaStream_t st);
 
 extern "C" long long dfn_mlp_dz_bytes(long long P) {
-  const long long nt = (P + kTile - 1) / kTile;
+  const long long nt = num_tiles(P);
   return nt * (9LL * 65536 + 32768 + 2048);
 }
 
@@ -283,7 +283,7 @@ extern "C" int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const f
   DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward_dgrad: P out of range");
   if (P == 0) return DFN_OK;
   DgradArgs a{};
-  a.P = P; a.n_tiles = static_cast<int>((P + kTile - 1) / kTile);
+  a.P = P; a.n_tiles = static_cast<int>(num_tiles(P));
   a.wpack = static_cast<const uint8_t*>(bwd_pack); a.consts = consts; a.rgb = rgb; a.sigma = sigma;
   a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.stash = static_cast<const uint8_t*>(stash); a.dz = static_cast<uint8_t*>(dz);
   const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
@@ -299,7 +299,7 @@ extern "C" int dfn_mlp_backward_wgrad(const dfn_point_source* src, long long P, 
   DFN_CHECK_ARG(src && stash && dz && grads, "mlp_backward_wgrad: null pointer");
   DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_backward_wgrad: P out of range");
   if (P == 0) return DFN_OK;
-  return dfn_launch_wgrad(src, P, static_cast<int>((P + kTile - 1) / kTile), static_cast<const uint8_t*>(stash),
+  return dfn_launch_wgrad(src, P, static_cast<int>(num_tiles(P)), static_cast<const uint8_t*>(stash),
                           static_cast<const uint8_t*>(dz), grads, static_cast<cudaStream_t>(stream));
 }
 

@@ -46,6 +46,15 @@ __host__ __device__ constexpr uint32_t job_off(int j) {
   return o;
 }
 constexpr uint32_t kFwdPackBytes = job_off(kNumJobs);
+// The forward kernel runs as CTA pairs (tcgen05 cta_group::2, M = 256): CTA r of a pair holds rows [r*N/2, (r+1)*N/2)
+// of every weight block, so a job's image is stored as two halves, each [K/8 chunks][N/2 rows][8] bf16:
+//   byte offset = job_off(j) + r * job_bytes(j)/2 + kc * job_half_chunk(j) + n_local * 16 + (k % 8) * 2
+__host__ __device__ constexpr uint32_t job_half_chunk(int j) { return static_cast<uint32_t>(job_N(j) / 2) * 16u; }  // bytes per K chunk per CTA
+__host__ __device__ constexpr uint32_t job_half_bytes(int j) { return job_bytes(j) / 2; }
+
+// Number of 128-point tiles the MLP kernels work on for P points: whole 256-point pairs (the forward processes
+// two tiles per CTA pair), so the stash / dz layouts of all three kernels agree.
+__host__ __device__ constexpr long long num_tiles(long long P) { return 2 * ((P + 2 * kTile - 1) / (2 * kTile)); }
 
 // dgrad job table (backward chain; B operand = W^T, reduction over the layer's outputs)
 //   b0: d feat = dZ_c0 [128x128] * color_layer.0[:, :256]      K=128 N=256

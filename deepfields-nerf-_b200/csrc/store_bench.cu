@@ -131,3 +131,70 @@ extern "C" int dfn_store_bench(int mode, int iters, int grid, void* buf, long lo
   DFN_CHECK_LAUNCH("store_bench");
   return DFN_OK;
 }
+
+// ---- cta_group::2 issue-rate probe: the leader of a CTA pair streams M=256 N=256 K=16 MMAs -----------------
+namespace {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1) pair_mma_kernel(int iters, int N, long long* cycles) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_ptr;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const uint32_t sa = smem_u32(smem), sb = sa + 65536;
+  if (threadIdx.x == 0) { mbar_init(smem_u32(&bars[0]), 1); mbar_init(smem_u32(&bars[1]), 1); fence_mbar_init(); }
+  for (uint32_t i = threadIdx.x; i < (65536u + 65536u) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3F003F00u + i;
+  fence_proxy_async();
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_ptr)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  tc_fence_after();
+  const uint32_t tbase = *reinterpret_cast<volatile uint32_t*>(&tmem_ptr);
+  if (warp == 0 && rank == 0) {
+    const uint32_t idesc = instr_desc_bf16(256, N, 0, 0);
+    const uint32_t cb = (N / 2) * 16;   // bytes per K chunk of this CTA's half of B
+    const uint32_t bar0 = smem_u32(&bars[0]);
+    uint32_t ph[2] = {0, 0}; int pend[2] = {0, 0};
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      for (int k = 0; k < 16; k += 2) {
+        const int s = (k >> 1) & 1;
+        if (pend[s]) { mbar_wait(bar0 + 8 * s, ph[s]); ph[s] ^= 1; tc_fence_after(); }
+        if (elect_one()) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const uint64_t da = smem_desc(sa + (k + i) * 4096u, 2048u, 128u), db = smem_desc(sb + (k + i) * 2 * cb, cb, 128u);
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tbase + (it & 1) * 256), "l"(da), "l"(db),
+                         "r"(idesc), "r"(k + i > 0 ? 1u : 0u) : "memory");
+          }
+          asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar0 + 8 * s),
+                       "h"(static_cast<uint16_t>(1)) : "memory");
+        }
+        __syncwarp();
+        pend[s] = 1;
+      }
+    }
+    if (pend[0]) mbar_wait(bar0, ph[0]);
+    if (pend[1]) mbar_wait(bar0 + 8, ph[1]);
+    if (lane == 0) cycles[blockIdx.x >> 1] = (clock64() - t0) / (iters * 16);
+  }
+  tc_fence_before();
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(512u) : "memory");
+}
+}  // namespace
+
+extern "C" int dfn_pair_mma_bench(int iters, int N, int grid, long long* cycles_out, void* stream) {
+  DFN_CHECK_ARG(cycles_out && iters > 0 && grid > 0 && grid % 2 == 0 && N >= 32 && N <= 256 && N % 32 == 0, "pair_mma_bench: bad args");
+  const uint32_t smem = 65536 + 65536;
+  DFN_CUDA(cudaFuncSetAttribute(pair_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "pair_mma_bench");
+  pair_mma_kernel<<<grid, 64, smem, static_cast<cudaStream_t>(stream)>>>(iters, N, cycles_out);
+  DFN_CHECK_LAUNCH("pair_mma_bench");
+  return DFN_OK;
+}

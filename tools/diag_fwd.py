@@ -29,7 +29,7 @@ if len(sys.argv) > 2 and sys.argv[2] == "child":
 else:
     lg = sys.argv[1] if len(sys.argv) > 1 else "20"
     for train in ("0", "1"):
-        for dbg in ("0", "32", "64", "96", "128", "16"):
+        for dbg in ("0",):
             env = dict(os.environ, DFN_FWD_DEBUG=dbg)
             subprocess.run([sys.executable, __file__, lg, "child", train], env=env)
     for train in ():

@@ -1,0 +1,688 @@
+// Fused vanilla-NeRF MLP forward (reference scripts/model.py:139-187) for sm_100a.
+//
+// Persistent kernel, one CTA per SM, CTAs paired into clusters of two (tcgen05 cta_group::2): a pair works on
+// 256-point super-tiles, CTA r owning rows [128r, 128r+128), and two super-tiles (slots X/Y) are in flight per pair.
+//   warp 0      : weight producer (both CTAs) - streams ITS HALF (N/2 rows) of the packed bf16 weight blocks from L2
+//                 into a shared memory ring with 1-D bulk async copies (TMA engine, mbarrier complete_tx).  The pair
+//                 shares the B operand, so each SM pulls only half of the 1.2 MB of weights per super-tile: the weight
+//                 stream (L2 -> SM latency x ring depth) is what bounds this kernel, see DESIGN.md section 5.
+//   warp 1      : leader CTA: MMA issuer - the warp runs converged and one elected lane issues
+//                 tcgen05.mma.cta_group::2 (M=256, N=256/128, K=16, bf16 -> fp32 in TMEM); slot X accumulates in TMEM
+//                 columns [0,256) of both CTAs, slot Y in [256,512).  One ring stage (wait, MMAs, commit) is a single
+//                 asm block with the election inside.  Commits are multicast to the barriers of both CTAs.
+//                 peer CTA: relay - forwards "my half of stage s has landed" to the leader's full barrier.
+//   warps 2..9  : epilogue (both CTAs) - tcgen05.ld the accumulator, ReLU, round to bf16, write the next layer's A
+//                 operand back to shared memory in the UMMA chunk layout (activations never leave the SM);
+//                 positional encodings are computed here too.  Publishing a tile = one arrive per warp on the
+//                 LEADER's aready barrier (remote arrive from the peer).
+// While the tensor cores run layer L of slot X the epilogue warps drain layer L-1 of slot Y.
+// Biases ride along as one extra K=16 MMA per layer against a constant "ones" tile (mlp_common.cuh).
+// The sigma head (N=1) and color_layer.2 (N=3) are CUDA-core dot products inside the epilogues.
+// TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
+// backward kernels: each epilogue thread stores the 16-byte groups it has rounded straight to global memory
+// (a warp covers 512 contiguous bytes per chunk), after the tile has been published to the issuer.
+#include "mlp_common.cuh"
+#include <stdlib.h>
+#include <string.h>
+#include <utility>
+
+namespace {
+using namespace mlp;
+using namespace umma;
+
+constexpr int kStages = 3;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epilogue warps
+constexpr int kCPS = 8;                      // K chunks per ring stage (= 4 MMAs); 16 KB (N=256) or 8 KB (N=128) per CTA
+
+// shared memory map (bytes), identical in both CTAs of a pair (the MMA addresses the peer's tiles by the same offsets)
+constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
+constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;            // 2 x 16 KB
+constexpr uint32_t kOffRing = kOffAux + 2 * kAuxBytes;           // kStages x 16 KB
+constexpr uint32_t kOffOnes = kOffRing + kStages * kStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
+constexpr uint32_t kOnesBytes = 2 * kChunkBytes;
+constexpr uint32_t kOffConst = kOffOnes + kOnesBytes;
+// partial head dot products of the upper column half, [2 slots][128 rows][3] f32 (sigma uses [..][0];
+// reuse across j7 / j9 of a slot is ordered by the other slot's named barrier in between)
+constexpr uint32_t kOffPart = kOffConst + kConstBytes;
+constexpr uint32_t kOffBars = kOffPart + 2 * 128 * 3 * 4;
+// barriers: full[slot][stage], empty[slot][stage] (one set per slot: a parity wait can only tell adjacent phases
+// apart), accfull[slot], aready[slot] (leader only)
+constexpr uint32_t kNumBars = 4 * kStages + 4;
+__host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
+__host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }
+__host__ __device__ constexpr uint32_t bar_accfull_i(int t) { return 4 * kStages + t; }
+__host__ __device__ constexpr uint32_t bar_aready_i(int t) { return 4 * kStages + 2 + t; }
+constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
+constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
+static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
+
+struct FwdArgs {
+  PointSource src;
+  long long P;
+  int n_tiles;            // 128-point tiles, even (num_tiles(P))
+  const uint8_t* wpack;   // packed forward weights
+  const float* consts;    // fp32 consts block
+  const float* noise;     // [P] sigma noise or null (model.py:160-162)
+  float* rgb;             // [P,3]
+  float* sigma;           // [P]
+  uint8_t* stash_h;       // TRAIN: [8][n_tiles][64 KB]
+  uint8_t* stash_f;       // TRAIN: [n_tiles][64 KB]
+  uint8_t* stash_c;       // TRAIN: [n_tiles][32 KB]
+};
+
+// ---- cluster helpers --------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// wait with cluster-scope acquire: the arrivals come from the peer CTA
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  long long t0 = 0;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) return;
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > 4000000000LL) {
+      printf("dfn: cluster mbarrier timeout (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+
+// tile of (iteration, slot) for this CTA: super-tile index * 2 + rank
+__device__ __forceinline__ int tile_of(int it, int t, int rank) {
+  const int n_pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
+  return 2 * ((it * 2 + t) * n_pairs + pair) + rank;
+}
+
+// ---- epilogue helpers ------------------------------------------------------------------------------
+// the first NC packed 32-column groups of one row -> stash (global); a warp covers 512 contiguous bytes per chunk
+template <int NC>
+__device__ __forceinline__ void stash_row(uint8_t* stash, int col0, int row, const uint32_t (&keep)[64]) {
+#pragma unroll
+  for (int g = 0; g < NC * 4; ++g) {
+    const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
+    st_global_v4(stash + off, keep[g * 4], keep[g * 4 + 1], keep[g * 4 + 2], keep[g * 4 + 3]);
+  }
+}
+
+// 32 accumulator columns -> optional ReLU, bf16 -> 4 x 16 B into the act tile
+template <bool RELU>
+__device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, int col0, int row, uint32_t* packed /* 16 */) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const float x0 = __uint_as_float(v[g * 8 + 0]), x1 = __uint_as_float(v[g * 8 + 1]);
+    const float x2 = __uint_as_float(v[g * 8 + 2]), x3 = __uint_as_float(v[g * 8 + 3]);
+    const float x4 = __uint_as_float(v[g * 8 + 4]), x5 = __uint_as_float(v[g * 8 + 5]);
+    const float x6 = __uint_as_float(v[g * 8 + 6]), x7 = __uint_as_float(v[g * 8 + 7]);
+    uint4 q;
+    if (RELU) {
+      q.x = pack_bf16x2_relu(x0, x1); q.y = pack_bf16x2_relu(x2, x3);
+      q.z = pack_bf16x2_relu(x4, x5); q.w = pack_bf16x2_relu(x6, x7);
+    } else {
+      q.x = pack_bf16x2(x0, x1); q.y = pack_bf16x2(x2, x3);
+      q.z = pack_bf16x2(x4, x5); q.w = pack_bf16x2(x6, x7);
+    }
+    packed[g * 4 + 0] = q.x; packed[g * 4 + 1] = q.y; packed[g * 4 + 2] = q.z; packed[g * 4 + 3] = q.w;
+    const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
+    if (act) *reinterpret_cast<uint4*>(act + off) = q;
+  }
+}
+
+// ---- weight ring + MMA issue, one instantiation per job so every shape is a compile-time constant -----
+// A generic issue loop with run-time shapes costs ~300 cycles per tcgen05.mma in address arithmetic alone
+// (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
+// whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
+// A ring stage holds kCPS K-chunks of this CTA's half of the weight block (N/2 rows each).
+constexpr int job_stages(int j) { return (job_kcb(j) + kCPS - 1) / kCPS; }
+constexpr int stage_chunks(int j, int k) { return (job_kcb(j) - k * kCPS) < kCPS ? (job_kcb(j) - k * kCPS) : kCPS; }
+constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
+  int n = 0;
+  for (int i = 0; i < j; ++i) n += 2 * job_stages(i);
+  return n + t * job_stages(j);
+}
+
+struct ProdState {
+  uint32_t use[2][kStages];   // parity of the number of fills so far per (slot, stage)
+  int last[kStages];          // slot that used the stage last (-1: never)
+};
+
+template <int J>
+__device__ __forceinline__ void produce_job(const uint8_t* wpack, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2]) {
+  constexpr uint32_t cb = job_half_chunk(J);
+  const uint8_t* src = wpack + job_off(J) + rank * job_half_bytes(J);
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    if (!has[t]) continue;
+#pragma unroll
+    for (int k = 0; k < job_stages(J); ++k) {
+      constexpr uint32_t kFull = kCPS * cb;
+      const uint32_t off = k * kFull;
+      const uint32_t nb = static_cast<uint32_t>(stage_chunks(J, k)) * cb;
+      const int stage = (stage_prefix(J, t) + k) % kStages;
+      // the previous user of this stage (either slot) must have released it (multicast commit of the leader)
+      if (ps.last[stage] == 0) mbar_wait(bar0 + 8u * bar_empty_i(0, stage), ps.use[0][stage] ^ 1);
+      else if (ps.last[stage] == 1) mbar_wait(bar0 + 8u * bar_empty_i(1, stage), ps.use[1][stage] ^ 1);
+      ps.use[t][stage] ^= 1;
+      ps.last[stage] = t;
+      const uint32_t full = bar0 + 8u * bar_full_i(t, stage);
+      mbar_arrive_expect_tx(full, nb);
+      bulk_g2s(ring + stage * kStageBytes, src + off, nb, full);
+    }
+  }
+}
+template <int... Js>
+__device__ __forceinline__ void produce_all(const uint8_t* wpack, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2], std::integer_sequence<int, Js...>) {
+  (produce_job<Js>(wpack, rank, ring, bar0, ps, has), ...);
+}
+
+// One ring stage as a single asm block: bounded wait for the weights of BOTH CTAs (the leader's full barrier counts
+// its own producer and the peer's relay; a protocol bug traps instead of hanging), NMMA x tcgen05.mma.cta_group::2
+// (K = 16 each) and the multicast commit that releases the stage in both CTAs.  MMA i < NMMA-1 reads A at
+// a_lo + i*256 (two chunks further), the last one at a_last; B advances by B_STEP descriptor units per MMA.
+#define DFN_STAGE_HEAD                                                        \
+  "{\n\t"                                                                     \
+  ".reg .pred q, p, pe;\n\t"                                                  \
+  ".reg .b32 cnt, al, bl;\n\t"                                                \
+  ".reg .b64 da, db;\n\t"                                                     \
+  "mov.u32 cnt, 0;\n\t"                                                       \
+  "SW_WAIT:\n\t"                                                              \
+  "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 q, [%0], %1;\n\t" \
+  "@q bra SW_GO;\n\t"                                                         \
+  "add.u32 cnt, cnt, 1;\n\t"                                                  \
+  "setp.lt.u32 p, cnt, 8000000;\n\t"                                          \
+  "@p bra SW_WAIT;\n\t"                                                       \
+  "trap;\n\t"                                                                 \
+  "SW_GO:\n\t"                                                                \
+  "tcgen05.fence::after_thread_sync;\n\t"                                     \
+  "elect.sync _|pe, 0xffffffff;\n\t"                                          \
+  "setp.ne.b32 p, %7, 0;\n\t"
+#define DFN_STAGE_FIRST                                         \
+  "mov.b64 da, {%3, %5};\n\t"                                   \
+  "mov.b64 db, {%4, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
+#define DFN_STAGE_NEXT(i)                                       \
+  "add.u32 al, %3, " #i "*256;\n\t"                             \
+  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
+  "mov.b64 da, {al, %5};\n\t"                                   \
+  "mov.b64 db, {bl, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
+#define DFN_STAGE_LAST(i)                                       \
+  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
+  "mov.b64 da, {%9, %5};\n\t"                                   \
+  "mov.b64 db, {bl, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
+#define DFN_STAGE_ONLY                                          \
+  "mov.b64 da, {%9, %5};\n\t"                                   \
+  "mov.b64 db, {%4, %5};\n\t"                                   \
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
+#define DFN_COMMIT(b) \
+  "@pe tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [" b "], %12;\n\t"
+#define DFN_STAGE_TAIL DFN_COMMIT("%8") "}"
+// last stage of a job: the second commit tells the epilogues of both CTAs that the accumulator is complete
+#define DFN_STAGE_TAIL_ACC DFN_COMMIT("%8") DFN_COMMIT("%11") "}"
+#define DFN_STAGE_OPERANDS                                                                                     \
+  ::"r"(full_bar), "r"(parity), "r"(tacc), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc_first), "r"(empty_bar), \
+      "r"(a_last), "n"(B_STEP), "r"(acc_bar), "h"(static_cast<uint16_t>(3))                                       \
+      : "memory"
+
+// Executed by the whole (converged) issuer warp of the leader CTA.
+template <int NMMA, int B_STEP, bool ACC>
+__device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, uint32_t tacc, uint32_t a_lo, uint32_t a_last,
+                                          uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc_first, uint32_t empty_bar,
+                                          uint32_t acc_bar) {
+  static_assert(NMMA >= 1 && NMMA <= 4, "1..4 MMAs per stage");
+  if constexpr (ACC) {
+    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 3)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL_ACC
+                       DFN_STAGE_OPERANDS);
+  } else {
+    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 3)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL
+                       DFN_STAGE_OPERANDS);
+  }
+}
+
+struct SlotCtx {
+  uint32_t ph0, ph1, ph2;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
+  uint32_t pa;              // phase of this slot's aready barrier
+  bool has;                 // the slot has a tile in the current iteration
+};
+struct IssueCtx {
+  uint32_t sbase, bar0, tmem_base, rank;
+  SlotCtx s0, s1;
+  int lane;
+};
+template <int T>
+__device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
+  if constexpr (T == 0) return c.s0; else return c.s1;
+}
+template <int S>
+__device__ __forceinline__ uint32_t& ph_of(SlotCtx& c) {
+  if constexpr (S == 0) return c.ph0;
+  else if constexpr (S == 1) return c.ph1;
+  else return c.ph2;
+}
+
+// where chunk kc of job J's A operand lives (descriptor address units relative to the three bases)
+template <int J>
+__device__ __forceinline__ uint32_t a_chunk_lo(int kc, uint32_t a_act, uint32_t a_aux, uint32_t a_ones) {
+  constexpr int KC = job_kc(J), KC_ACT = job_kc_act(J);
+  if (kc >= KC) return a_ones + (kc - KC) * (kChunkBytes >> 4);
+  if (kc < KC_ACT) return a_act + kc * (kChunkBytes >> 4);
+  return a_aux + (kc - KC_ACT) * (kChunkBytes >> 4);
+}
+
+template <int J, int T, int K>
+__device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc) {
+  constexpr int N = job_N(J);
+  constexpr uint32_t idesc = instr_desc_bf16(256, N, 0, 0);   // M = 256 over the CTA pair
+  constexpr uint32_t cb = job_half_chunk(J);                  // bytes per K chunk of this CTA's half of B
+  constexpr uint32_t hi = desc_hi(128);
+  constexpr int B_STEP = 2 * (cb >> 4);                       // descriptor address units per MMA (two K chunks)
+  constexpr int kc0 = K * kCPS;
+  constexpr int stage = (stage_prefix(J, T) + K) % kStages;
+  constexpr int nchunk = stage_chunks(J, K);
+  constexpr bool last = K == job_stages(J) - 1;
+  static_assert(nchunk % 2 == 0, "a K=16 MMA consumes two chunks");
+  const uint32_t full = c.bar0 + 8u * bar_full_i(T, stage), empty = c.bar0 + 8u * bar_empty_i(T, stage);
+  uint32_t& ph = ph_of<stage>(slot_of<T>(c));
+  if (c.rank == 0) {
+    const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
+    const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kStageBytes, cb);
+    const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
+    const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
+    constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
+    stage_mma<nchunk / 2, B_STEP, last>(full, ph, tacc, a_lo, a_last, b_lo, hi, idesc, accf, empty, accfull);
+  } else {
+    // relay: this CTA's half of the stage has landed -> one arrive on the leader's full barrier
+    if (c.lane == 0) {
+      mbar_wait(full, ph);
+      mbar_arrive_cluster(map_to_cta(full, 0));
+    }
+    __syncwarp();
+  }
+  ph ^= 1;
+}
+template <int J, int T, int... Ks>
+__device__ __forceinline__ void issue_stages(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc,
+                                             std::integer_sequence<int, Ks...>) {
+  (issue_stage<J, T, Ks>(c, a_act, a_aux, a_ones, tacc), ...);
+}
+
+// Runs on the whole warp 1 (converged) of both CTAs: issuer in the leader, relay in the peer.
+template <int J, int T>
+__device__ __forceinline__ void issue_job(IssueCtx& c) {
+  SlotCtx& sc = slot_of<T>(c);
+  if (!sc.has) return;
+  if (c.rank == 0) {   // the A operand of this job (both CTAs' tiles) has been published
+    mbar_wait_cluster(c.bar0 + 8u * bar_aready_i(T), sc.pa);
+    sc.pa ^= 1;
+    tc_fence_after();
+  }
+  const uint32_t a_act = desc_lo(c.sbase + kOffAct + T * kActBytes, kChunkBytes);
+  const uint32_t a_aux = desc_lo(c.sbase + kOffAux + T * kAuxBytes, kChunkBytes);
+  const uint32_t a_ones = desc_lo(c.sbase + kOffOnes, kChunkBytes);
+  const uint32_t tacc = c.tmem_base + T * 256;
+  issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J)>{});
+}
+template <int... Js>
+__device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
+  ((issue_job<Js, 0>(c), issue_job<Js, 1>(c)), ...);
+}
+
+template <bool TRAIN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t bar0 = sbase + kOffBars;
+  auto bar_accfull = [&](int t) { return bar0 + 8u * bar_accfull_i(t); };
+  auto bar_aready = [&](int t) { return bar0 + 8u * bar_aready_i(t); };
+  float* consts = reinterpret_cast<float*>(smem + kOffConst);
+
+  if (threadIdx.x == 0) {
+    for (int t = 0; t < 2; ++t)
+      for (int s = 0; s < kStages; ++s) {
+        // leader: its own producer's arrive.expect_tx + the peer's relay; peer: its own producer only
+        mbar_init(bar0 + 8u * bar_full_i(t, s), rank == 0 ? 2 : 1);
+        mbar_init(bar0 + 8u * bar_empty_i(t, s), 1);
+      }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), 2 * kEpiWarps); }
+    fence_mbar_init();
+  }
+  if (warp == 1) {   // one warp per CTA allocates all 512 TMEM columns of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + kOffTmemPtr), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
+  // ones tile: [2 chunks][128 rows][8 bf16], column 0 of every row = 1.0
+  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += kThreads)
+    *reinterpret_cast<uint4*>(smem + kOffOnes + i * 16) = make_uint4(i < 128 ? 0x3F80u : 0u, 0u, 0u, 0u);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // barriers of both CTAs are initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
+
+  const int n_pairs = gridDim.x >> 1;
+  const int n_super = a.n_tiles >> 1;
+  const int n_it = (n_super + 2 * n_pairs - 1) / (2 * n_pairs);
+
+  if (warp == 0) {
+    // ================= weight producer (this CTA's half of every block) =================
+    if (lane == 0) {
+      ProdState ps;
+#pragma unroll
+      for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
+      for (int it = 0; it < n_it; ++it) {
+        const bool has[2] = {tile_of(it, 0, rank) < a.n_tiles, tile_of(it, 1, rank) < a.n_tiles};
+        produce_all(a.wpack, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumJobs>{});
+      }
+    }
+  } else if (warp == 1) {
+    // ================= leader: MMA issuer (whole warp, converged; one elected lane issues); peer: relay =================
+    IssueCtx c{};
+    c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.lane = lane; c.rank = rank;
+    c.s0 = SlotCtx{0, 0, 0, 0, false};
+    c.s1 = c.s0;
+    for (int it = 0; it < n_it; ++it) {
+      c.s0.has = tile_of(it, 0, rank) < a.n_tiles;
+      c.s1.has = tile_of(it, 1, rank) < a.n_tiles;
+      issue_all(c, std::make_integer_sequence<int, kNumJobs>{});
+    }
+  } else {
+    // ================= epilogue / PE warps =================
+    const int ew = warp - 2;
+    const int q = warp & 3;         // TMEM lane quadrant this warp may access
+    const int hh = ew >> 2;         // column half
+    const int row = q * 32 + lane;  // row of the tile == TMEM lane
+    const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
+    float* part = reinterpret_cast<float*>(smem + kOffPart);
+    uint32_t pf[2] = {0, 0};
+    const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
+
+    auto point_of = [&](int tile) {
+      long long p = static_cast<long long>(tile) * kTile + row;
+      return p < a.P ? p : a.P - 1;
+    };
+    // activations / encodings written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one
+    // arrive per warp on the leader's barrier
+    auto publish = [&](int t) {
+      tc_fence_before();
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(aready_leader[t]);
+    };
+    // initial PE for both slots
+    for (int t = 0; t < 2; ++t) {
+      const int tile = tile_of(0, t, rank);
+      if (tile < a.n_tiles) {
+        float x[3], d[3];
+        load_point(a.src, point_of(tile), x, d);
+        write_pe_row(smem + kOffAux + t * kAuxBytes, nullptr, row, hh, x, d);
+      }
+      publish(t);
+    }
+
+    for (int it = 0; it < n_it; ++it) {
+      for (int j = 0; j < kNumJobs; ++j) {
+        for (int t = 0; t < 2; ++t) {
+          const int tile = tile_of(it, t, rank);
+          if (tile >= a.n_tiles) continue;
+          uint8_t* act = smem + kOffAct + t * kActBytes;
+          uint8_t* aux = smem + kOffAux + t * kAuxBytes;
+          const uint32_t tacc = tmem_base + t * 256 + lane_sel;
+          const long long p = static_cast<long long>(tile) * kTile + row;
+          // TRAIN: the bf16 tile this job produces (h1..h8, features, colour hidden) also goes to the stash
+          uint8_t* st = nullptr;
+          if (TRAIN) {
+            if (j < 8) st = a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16);
+            else if (j == 8) st = a.stash_f + (static_cast<size_t>(tile) << 16);
+            else st = a.stash_c + (static_cast<size_t>(tile) << 15);
+          }
+          mbar_wait(bar_accfull(t), pf[t]);
+          pf[t] ^= 1;
+          tc_fence_after();
+
+          if (j < 9) {
+            float sdot = 0.f;
+            const int c0 = hh * 128;
+            uint32_t v0[32], v1[32], keep[64];
+            tmem_ld32(tacc + c0, v0);
+            tmem_ld_wait();
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+              uint32_t (&cur)[32] = (cc & 1) ? v1 : v0;
+              uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
+              if (cc < 3) tmem_ld32(tacc + c0 + (cc + 1) * 32, nxt);
+              const int col0 = c0 + cc * 32;
+              uint32_t* pk = keep + cc * 16;
+              if (j == 8) emit32<false>(cur, act, col0, row, pk);
+              else emit32<true>(cur, act, col0, row, pk);
+              if (j == 7) {
+                const float* ws = consts + kConstWsig + col0;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  sdot += bf16lo_to_f32(pk[i]) * ws[2 * i];
+                  sdot += bf16hi_to_f32(pk[i]) * ws[2 * i + 1];
+                }
+              }
+              if (cc < 3) tmem_ld_wait();
+            }
+            if (j == 4) {  // pos-PE is dead once job 4's MMAs finished: overlay the dir-PE
+              float x[3], d[3];
+              load_point(a.src, p < a.P ? p : a.P - 1, x, d);
+              write_pe_row(nullptr, aux, row, hh, x, d);
+            }
+            publish(t);
+            if (TRAIN) stash_row<4>(st, c0, row, keep);
+            if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
+              if (hh == 1) part[(t * 128 + row) * 3] = sdot;
+              named_bar_sync(1, kEpiThreads);
+              if (hh == 0 && p < a.P) {
+                float s = sdot + part[(t * 128 + row) * 3] + consts[kConstBsig];
+                s = round_bf16(s);
+                if (a.noise) s = round_bf16(s + round_bf16(a.noise[p]));
+                a.sigma[p] = fmaxf(s, 0.f);
+              }
+            }
+          } else {
+            // j == 9: colour hidden layer (N=128) + color_layer.2 + sigmoid
+            float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+            const int c0 = hh * 64;
+            uint32_t v0[32], v1[32], keep[64];
+            tmem_ld32(tacc + c0, v0);
+            tmem_ld32(tacc + c0 + 32, v1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+              uint32_t (&cur)[32] = cc ? v1 : v0;
+              const int col0 = c0 + cc * 32;
+              uint32_t* pk = keep + cc * 16;
+              emit32<true>(cur, nullptr, col0, row, pk);
+              const float* w0 = consts + kConstWc2 + col0;
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const float lo = bf16lo_to_f32(pk[i]), hi = bf16hi_to_f32(pk[i]);
+                r0 += lo * w0[2 * i] + hi * w0[2 * i + 1];
+                r1 += lo * w0[128 + 2 * i] + hi * w0[128 + 2 * i + 1];
+                r2 += lo * w0[256 + 2 * i] + hi * w0[256 + 2 * i + 1];
+              }
+            }
+            // next tile of this slot: its pos-PE goes into aux (dir-PE was consumed by job 9's MMAs)
+            const int ntile = tile_of(it + 1, t, rank);
+            if (ntile < a.n_tiles) {
+              float x[3], d[3];
+              load_point(a.src, point_of(ntile), x, d);
+              write_pe_row(aux, nullptr, row, hh, x, d);
+              publish(t);   // (no publish after the slot's last tile: nobody waits for it)
+            }
+            if (TRAIN) stash_row<2>(st, c0, row, keep);
+            float* pr = part + (t * 128 + row) * 3;
+            if (hh == 1) { pr[0] = r0; pr[1] = r1; pr[2] = r2; }
+            named_bar_sync(1, kEpiThreads);
+            if (hh == 0 && p < a.P) {
+              const float own[3] = {r0, r1, r2};
+#pragma unroll
+              for (int o = 0; o < 3; ++o) {
+                const float xo = round_bf16(own[o] + pr[o] + consts[kConstBc2 + o]);
+                a.rgb[p * 3 + o] = 1.0f / (1.0f + __expf(-xo));
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // the leader's MMAs read the peer's shared memory: nobody leaves before both are done
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+}
+
+}  // namespace
+// ---------------------------------------------------------------------------------------------------
+// weight packing: flat fp32 parameters -> bf16 operand images + fp32 consts
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ float param_w(const float* params, int layer, int o, int i) {
+  constexpr ParamOffsets po = param_offsets();
+  return params[po.w[layer] + o * layer_in(layer) + i];
+}
+
+__global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ fwd,
+                                    __nv_bfloat16* __restrict__ bwd, float* __restrict__ consts) {
+  constexpr ParamOffsets po = param_offsets();
+  const int nf = kFwdPackBytes / 2, nb = kBwdPackBytes / 2;
+  const int total = nf + nb + kConstFloats;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    if (idx < nf) {
+      int j = 0;
+      while (j + 1 < kNumJobs && static_cast<uint32_t>(idx) * 2u >= job_off(j + 1)) ++j;
+      const int e0 = idx - job_off(j) / 2;
+      const int N = job_N(j), NH = N / 2;
+      const int half_elems = job_half_bytes(j) / 2;
+      const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half
+      const int kc = e / (NH * 8), n = r * NH + (e / 8) % NH, k = kc * 8 + (e & 7);
+      const int layer = j < 8 ? j : (j == 8 ? 9 : 10);   // reference layer index of job j
+      const int kdata = job_kc(j) * 8;
+      float v = 0.f;
+      if (k >= kdata) {  // bias slice: column 0 carries the bias, the other 15 are zero
+        if (k == kdata) v = params[po.b[layer] + n];
+      } else if (j == 0) { if (k < 63) v = param_w(params, 0, n, k); }
+      else if (j == 4) { if (k < 256 + 63) v = param_w(params, 4, n, k); }
+      else if (j == 9) { if (k < 256 + 27) v = param_w(params, 10, n, k); }
+      else v = param_w(params, layer, n, k);
+      fwd[idx] = __float2bfloat16_rn(v);
+    } else if (idx < nf + nb) {
+      const int bi = idx - nf;
+      int b = 0;
+      while (b + 1 < kNumBwdJobs && static_cast<uint32_t>(bi) * 2u >= bjob_off(b + 1)) ++b;
+      const int e = bi - bjob_off(b) / 2;
+      const int kc = e / (256 * 8), i = (e / 8) % 256, o = kc * 8 + (e & 7);
+      const int layer_of[kNumBwdJobs] = {10, 9, 7, 6, 5, 4, 3, 2, 1};
+      bwd[bi] = __float2bfloat16_rn(param_w(params, layer_of[b], o, i));
+    } else {
+      const int c = idx - nf - nb;
+      float v = 0.f;
+      if (c < kConstWc2) v = round_bf16(params[po.w[8] + (c - kConstWsig)]);
+      else if (c < kConstBsig) v = round_bf16(params[po.w[11] + (c - kConstWc2)]);
+      else if (c == kConstBsig) v = round_bf16(params[po.b[8]]);
+      else if (c < kConstBc2 + 3) v = round_bf16(params[po.b[11] + (c - kConstBc2)]);
+      consts[c] = v;
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" long long dfn_mlp_fwd_pack_bytes(void) { return kFwdPackBytes; }
+extern "C" long long dfn_mlp_bwd_pack_bytes(void) { return kBwdPackBytes; }
+extern "C" long long dfn_mlp_consts_bytes(void) { return kConstBytes; }
+extern "C" long long dfn_mlp_stash_bytes(long long P) {
+  const long long nt = num_tiles(P);
+  return nt * (8LL * 65536 + 65536 + 32768);
+}
+
+extern "C" int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream) {
+  DFN_CHECK_ARG(params && fwd_pack && bwd_pack && consts, "mlp_pack_weights: null pointer");
+  pack_weights_kernel<<<dfn_num_sms() * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      params, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts);
+  DFN_CHECK_LAUNCH("mlp_pack_weights");
+  return DFN_OK;
+}
+
+static int check_source(const dfn_point_source* s, long long P, const char* who) {
+  DFN_CHECK_ARG(s, "%s: null point source", who);
+  if (s->mode == 0) DFN_CHECK_ARG(s->pos && s->view, "%s: mode 0 needs pos and view", who);
+  else if (s->mode == 1) DFN_CHECK_ARG(s->rays_o && s->rays_d && s->z && s->S > 0 && P % s->S == 0, "%s: mode 1 needs rays_o/rays_d/z and P %% S == 0", who);
+  else if (s->mode == 2) DFN_CHECK_ARG(s->lin && s->view && s->R > 0 && s->p_offset >= 0 && s->p_offset + P <= 1LL * s->R * s->R * s->R, "%s: mode 2 needs lin/view and a range inside R^3", who);
+  else DFN_CHECK_ARG(false, "%s: unknown point source mode %d", who, s->mode);
+  return DFN_OK;
+}
+
+extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                               const float* noise, float* rgb, float* sigma, void* stash, void* stream) {
+  if (int rc = check_source(src, P, "mlp_forward")) return rc;
+  DFN_CHECK_ARG(fwd_pack && consts && rgb && sigma, "mlp_forward: null pointer");
+  DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_forward: P out of range");
+  if (P == 0) return DFN_OK;
+  FwdArgs a{};
+  a.src = *src; a.P = P; a.n_tiles = static_cast<int>(num_tiles(P));
+  a.wpack = static_cast<const uint8_t*>(fwd_pack); a.consts = consts; a.noise = noise; a.rgb = rgb; a.sigma = sigma;
+  if (stash) {
+    uint8_t* s = static_cast<uint8_t*>(stash);
+    a.stash_h = s;
+    a.stash_f = s + 8LL * a.n_tiles * 65536;
+    a.stash_c = a.stash_f + 1LL * a.n_tiles * 65536;
+  }
+  // one CTA per SM, paired: grid = 2 * min(#SM / 2, #super-tiles)
+  const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  const int grid = 2 * pairs;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (stash) {
+    DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
+    mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
+  } else {
+    DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
+    mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
+  }
+  DFN_CHECK_LAUNCH("mlp_forward");
+  return DFN_OK;
+}
