@@ -14,7 +14,8 @@
 // Biases ride along as one extra K=16 MMA per layer against a constant "ones" tile (mlp_common.cuh).
 // The sigma head (N=1) and color_layer.2 (N=3) are CUDA-core dot products inside the epilogues.
 // TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
-// backward kernels; that is done by 8 extra "stash" warps which read the accumulator a second time (see below).
+// backward kernels: each epilogue thread stores the 16-byte groups it has rounded straight to global memory
+// (a warp covers 512 contiguous bytes per chunk), after the tile has been published to the issuer.
 #include "mlp_common.cuh"
 #include <stdlib.h>
 #include <string.h>
@@ -24,18 +25,19 @@ namespace {
 using namespace mlp;
 using namespace umma;
 
+// Ring geometry: 3 x 16 KB (two N=256 MMAs per stage).  7 x 8 KB (one MMA per stage, deeper prefetch) was measured
+// 40 % SLOWER: the per-stage cost of the issuer (try_wait + fence + elect + commit) is about one MMA time.
 constexpr int kStages = 3;
+constexpr uint32_t kRingStageBytes = 16384;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kStashWarps = 8;               // TRAIN only
-constexpr int kThreadsInfer = 64 + kEpiThreads;                    // producer, issuer, 8 epilogue warps
-constexpr int kThreadsTrain = kThreadsInfer + kStashWarps * 32;    // + 8 stash warps
+constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
 
 // shared memory map (bytes)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;            // 2 x 16 KB
 constexpr uint32_t kOffRing = kOffAux + 2 * kAuxBytes;           // kStages x 16 KB
-constexpr uint32_t kOffOnes = kOffRing + kStages * kStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
+constexpr uint32_t kOffOnes = kOffRing + kStages * kRingStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
 constexpr uint32_t kOnesBytes = 2 * kChunkBytes;
 constexpr uint32_t kOffConst = kOffOnes + kOnesBytes;
 // partial head dot products of the upper column half, [2 slots][128 rows][3] f32 (sigma uses [..][0];
@@ -109,7 +111,7 @@ __device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, in
 // A generic issue loop with run-time shapes costs ~300 cycles per tcgen05.mma in address arithmetic alone
 // (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
 // whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
-constexpr int job_stages(int j) { return (job_bytes(j) + kStageBytes - 1) / kStageBytes; }
+constexpr int job_stages(int j) { return (job_bytes(j) + kRingStageBytes - 1) / kRingStageBytes; }
 constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
   int n = 0;
   for (int i = 0; i < j; ++i) n += 2 * job_stages(i);
@@ -138,7 +140,7 @@ __device__ __forceinline__ void produce_job(const uint8_t* wpack, uint32_t ring,
     if (!has[t]) continue;
 #pragma unroll
     for (int k = 0; k < job_stages(J); ++k) {
-      constexpr uint32_t kFull = kStageBytes;
+      constexpr uint32_t kFull = kRingStageBytes;
       const uint32_t off = k * kFull;
       const uint32_t nb = (jbytes - off) < kFull ? (jbytes - off) : kFull;
       const int stage = (stage_prefix(J, t) + k) % kStages;
@@ -151,7 +153,7 @@ __device__ __forceinline__ void produce_job(const uint8_t* wpack, uint32_t ring,
       if (debug & 1) mbar_arrive(full);
       else {
         mbar_arrive_expect_tx(full, nb);
-        bulk_g2s(ring + stage * kStageBytes, src + off, nb, full);
+        bulk_g2s(ring + stage * kRingStageBytes, src + off, nb, full);
       }
     }
   }
@@ -240,7 +242,7 @@ __device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, ui
 }
 
 struct SlotCtx {
-  uint32_t ph0, ph1, ph2;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
+  uint32_t ph0, ph1, ph2, ph3, ph4, ph5, ph6;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
   uint32_t pa;              // phase of this slot's aready barrier
   bool has;                 // the slot has a tile in the current iteration
   int tile, prev_tile;      // the slot's tile in the current / previous iteration (-1: none)
@@ -259,9 +261,14 @@ __device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
 }
 template <int S>
 __device__ __forceinline__ uint32_t& ph_of(SlotCtx& c) {
+  static_assert(kStages <= 7, "one phase scalar per ring stage");
   if constexpr (S == 0) return c.ph0;
   else if constexpr (S == 1) return c.ph1;
-  else return c.ph2;
+  else if constexpr (S == 2) return c.ph2;
+  else if constexpr (S == 3) return c.ph3;
+  else if constexpr (S == 4) return c.ph4;
+  else if constexpr (S == 5) return c.ph5;
+  else return c.ph6;
 }
 
 // where chunk kc of job J's A operand lives (descriptor address units relative to the three bases)
@@ -278,7 +285,7 @@ __device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_
   constexpr int N = job_N(J), KCB = job_kcb(J);
   constexpr uint32_t idesc = instr_desc_bf16(128, N, 0, 0);
   constexpr uint32_t b_chunk = N * 16;                    // bytes per K chunk of the weight block
-  constexpr int CPS = kStageBytes / b_chunk;              // chunks per stage: 4 (N=256) or 8 (N=128)
+  constexpr int CPS = kRingStageBytes / b_chunk;              // chunks per stage: 4 (N=256) or 8 (N=128)
   constexpr uint32_t hi = desc_hi(128);
   constexpr int B_STEP = 2 * (b_chunk >> 4);              // descriptor address units per MMA (two K chunks)
   constexpr int kc0 = K * CPS;
@@ -287,7 +294,7 @@ __device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_
   constexpr bool last = K == job_stages(J) - 1;
   const uint32_t full = c.bar0 + 8u * bar_full_i(T, stage), empty = c.bar0 + 8u * bar_empty_i(T, stage);
   const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
-  const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kStageBytes, b_chunk);
+  const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kRingStageBytes, b_chunk);
   const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
   const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
   constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
@@ -324,7 +331,7 @@ __device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int
 }
 
 template <bool TRAIN>
-__global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_fwd_kernel(const FwdArgs a) {
+__global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t sbase = smem_u32(smem);
@@ -335,7 +342,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < 4 * kStages; ++i) mbar_init(bar0 + 8u * i, 1);
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (TRAIN ? kStashWarps : 0)); }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
@@ -367,7 +374,8 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
     IssueCtx c{};
     c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.debug = a.debug; c.lane = lane;
     c.n_tiles = a.n_tiles; c.stash_h = a.stash_h; c.stash_f = a.stash_f; c.stash_c = a.stash_c;
-    c.s0 = SlotCtx{0, 0, 0, 0, false, -1, -1};
+    c.s0 = SlotCtx{};
+    c.s0.tile = c.s0.prev_tile = -1;
     c.s1 = c.s0;
     c.w_aready = 0;
     const long long t0 = clock64();
@@ -379,58 +387,6 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
       c.s1.prev_tile = c.s1.has ? c.s1.tile : -1;
     }
     if (a.stats && blockIdx.x == 0 && lane == 0) { a.stats[2] = clock64() - t0; a.stats[3] = c.w_aready; }
-  } else if (warp >= 2 + kEpiWarps) {
-    // ================= stash warps (TRAIN) =================
-    // A second set of 8 warps drains every finished accumulator again (TMEM reads are cheap and do not touch shared
-    // memory), applies the same ReLU / bf16 rounding and stores the tile to the activation stash.  The stores throttle
-    // at HBM rate (64 KB per tile and layer); issued from the epilogue warps they sat on the critical path of the
-    // next MMA and doubled the forward time.  Here only the TMEM read is ordered before the next MMA of the slot
-    // (these warps arrive on the same aready barrier), the stores drain in the background.
-    if (TRAIN) {
-      const int sw = warp - (2 + kEpiWarps);
-      const int q = warp & 3, hh = sw >> 2, row = q * 32 + lane;
-      const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
-      uint32_t pf[2] = {0, 0};
-      for (int t = 0; t < 2; ++t) {   // counterpart of the initial PE publish
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_aready(t));
-      }
-      for (int it = 0; it < n_it; ++it)
-        for (int j = 0; j < kNumJobs; ++j)
-          for (int t = 0; t < 2; ++t) {
-            const int tile = tile_of(it, t);
-            if (tile >= a.n_tiles) continue;
-            const uint32_t tacc = tmem_base + t * 256 + lane_sel;
-            mbar_wait(bar_accfull(t), pf[t]);
-            pf[t] ^= 1;
-            tc_fence_after();
-            uint32_t v[32], keep[64];
-            if (j < 9) {
-              const int c0 = hh * 128;
-#pragma unroll
-              for (int cc = 0; cc < 4; ++cc) {
-                tmem_ld32(tacc + c0 + cc * 32, v);
-                tmem_ld_wait();
-                if (j == 8) emit32<false>(v, nullptr, 0, row, keep + cc * 16);
-                else emit32<true>(v, nullptr, 0, row, keep + cc * 16);
-              }
-            } else {
-              const int c0 = hh * 64;
-#pragma unroll
-              for (int cc = 0; cc < 2; ++cc) {
-                tmem_ld32(tacc + c0 + cc * 32, v);
-                tmem_ld_wait();
-                emit32<true>(v, nullptr, 0, row, keep + cc * 16);
-              }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_aready(t));
-            if (j < 8) stash_row<4>(a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16), hh * 128, row, keep);
-            else if (j == 8) stash_row<4>(a.stash_f + (static_cast<size_t>(tile) << 16), hh * 128, row, keep);
-            else stash_row<2>(a.stash_c + (static_cast<size_t>(tile) << 15), hh * 64, row, keep);
-          }
-    }
   } else {
     // ================= epilogue / PE warps =================
     const int ew = warp - 2;
@@ -474,6 +430,12 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
           uint8_t* aux = smem + kOffAux + t * kAuxBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
           const long long p = static_cast<long long>(tile) * kTile + row;
+          uint8_t* st = nullptr;   // TRAIN: where the bf16 tile this job produces goes in the stash
+          if (TRAIN) {
+            if (j < 8) st = a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16);
+            else if (j == 8) st = a.stash_f + (static_cast<size_t>(tile) << 16);
+            else st = a.stash_c + (static_cast<size_t>(tile) << 15);
+          }
           if (a.debug & 8) mbar_wait_t(bar_accfull(t), pf[t], w_acc); else mbar_wait(bar_accfull(t), pf[t]);
           pf[t] ^= 1;
           tc_fence_after();
@@ -483,7 +445,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
           } else if (j < 9) {
             float sdot = 0.f;
             const int c0 = hh * 128;
-            uint32_t v0[32], v1[32], pk[16];
+            uint32_t v0[32], v1[32], keep[64];
             tmem_ld32(tacc + c0, v0);
             tmem_ld_wait();
 #pragma unroll
@@ -492,6 +454,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
               uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
               if (cc < 3) tmem_ld32(tacc + c0 + (cc + 1) * 32, nxt);
               const int col0 = c0 + cc * 32;
+              uint32_t* pk = keep + cc * 16;
               if (j == 8) emit32<false>(cur, act, col0, row, pk);
               else emit32<true>(cur, act, col0, row, pk);
               if (j == 7) {
@@ -510,6 +473,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
               write_pe_row(nullptr, aux, row, hh, x, d);
             }
             publish(t);
+            if (TRAIN) stash_row<4>(st, c0, row, keep);
             if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
               if (hh == 1) part[(t * 128 + row) * 3] = sdot;
               named_bar_sync(1, kEpiThreads);
@@ -524,7 +488,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
             // j == 9: colour hidden layer (N=128) + color_layer.2 + sigmoid
             float r0 = 0.f, r1 = 0.f, r2 = 0.f;
             const int c0 = hh * 64;
-            uint32_t v0[32], v1[32], pk[16];
+            uint32_t v0[32], v1[32], keep[64];
             tmem_ld32(tacc + c0, v0);
             tmem_ld32(tacc + c0 + 32, v1);
             tmem_ld_wait();
@@ -532,6 +496,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
             for (int cc = 0; cc < 2; ++cc) {
               uint32_t (&cur)[32] = cc ? v1 : v0;
               const int col0 = c0 + cc * 32;
+              uint32_t* pk = keep + cc * 16;
               emit32<true>(cur, nullptr, col0, row, pk);
               const float* w0 = consts + kConstWc2 + col0;
 #pragma unroll
@@ -550,6 +515,7 @@ __global__ void __launch_bounds__(TRAIN ? kThreadsTrain : kThreadsInfer, 1) mlp_
               write_pe_row(aux, nullptr, row, hh, x, d);
             }
             publish(t);
+            if (TRAIN) stash_row<2>(st, c0, row, keep);
             float* pr = part + (t * 128 + row) * 3;
             if (hh == 1) { pr[0] = r0; pr[1] = r1; pr[2] = r2; }
             named_bar_sync(1, kEpiThreads);
@@ -633,7 +599,7 @@ extern "C" long long dfn_mlp_fwd_pack_bytes(void) { return kFwdPackBytes; }
 extern "C" long long dfn_mlp_bwd_pack_bytes(void) { return kBwdPackBytes; }
 extern "C" long long dfn_mlp_consts_bytes(void) { return kConstBytes; }
 extern "C" long long dfn_mlp_stash_bytes(long long P) {
-  const long long nt = (P + kTile - 1) / kTile;
+  const long long nt = num_tiles(P);
   return nt * (8LL * 65536 + 65536 + 32768);
 }
 
@@ -661,7 +627,7 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_forward: P out of range");
   if (P == 0) return DFN_OK;
   FwdArgs a{};
-  a.src = *src; a.P = P; a.n_tiles = static_cast<int>((P + kTile - 1) / kTile);
+  a.src = *src; a.P = P; a.n_tiles = static_cast<int>(num_tiles(P));
   a.wpack = static_cast<const uint8_t*>(fwd_pack); a.consts = consts; a.noise = noise; a.rgb = rgb; a.sigma = sigma;
   if (stash) {
     uint8_t* s = static_cast<uint8_t*>(stash);
@@ -679,10 +645,10 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   }
   if (stash) {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<true><<<grid, kThreadsTrain, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
   } else {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<false><<<grid, kThreadsInfer, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
   }
   DFN_CHECK_LAUNCH("mlp_forward");
   if (a.stats) {

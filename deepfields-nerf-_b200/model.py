@@ -161,7 +161,7 @@ class OptimizedVanillaNeRF(nn.Module):
         stash = torch.empty(ops.mlp_stash_bytes(P), dtype=torch.uint8, device=pos2.device)
         view = torch.zeros_like(pos2)
         _, sigma = ops.mlp_forward(self._packed, pos=pos2, view=view, noise=noise, stash=stash)
-        nt = (P + ops.TILE - 1) // ops.TILE
+        nt = ops.mlp_num_tiles(P)
         f = stash[8 * nt * 65536: 9 * nt * 65536].view(torch.bfloat16).view(nt, 32, ops.TILE, 8)
         feat = f.permute(0, 2, 1, 3).reshape(nt * ops.TILE, 256)[:P]
         return sigma.reshape(*lead, 1), feat.reshape(*lead, 256)

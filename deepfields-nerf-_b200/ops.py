@@ -209,6 +209,11 @@ def _source(pos=None, view=None, rays=None, grid=None):
     return s, P, keep
 
 
+def mlp_num_tiles(P: int) -> int:
+    """128-point tiles the MLP kernels lay the stash / dz scratch out for (whole 256-point pairs, mlp_common.cuh)."""
+    return 2 * ((P + 2 * TILE - 1) // (2 * TILE))
+
+
 def mlp_stash_bytes(P: int) -> int:
     return _lib.load().dfn_mlp_stash_bytes(P)
 
