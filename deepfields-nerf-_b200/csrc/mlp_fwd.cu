@@ -1,22 +1,30 @@
 // Fused vanilla-NeRF MLP forward (reference scripts/model.py:139-187) for sm_100a.
 //
-// Persistent kernel, one CTA per SM, two 128-point tiles (slots X/Y) in flight per CTA:
-//   warp 0      : weight producer - streams packed bf16 weight blocks (16 KB stages) from L2 into a shared
-//                 memory ring with 1-D bulk async copies (TMA engine, mbarrier complete_tx)
-//   warp 1      : MMA issuer - the warp runs converged and one elected lane issues tcgen05.mma (M=128,
-//                 N=256/128, K=16, bf16 -> fp32 in TMEM); slot X accumulates in TMEM columns [0,256), slot Y in
-//                 [256,512).  One ring stage (wait, MMAs, commit) is a single asm block with the election
-//                 inside: ~60 issue cycles per MMA against 128 of execution (tools/umma_bench.py, mode 9).
-//   warps 2..9  : epilogue - tcgen05.ld the accumulator, ReLU, round to bf16, write the next layer's A
+// Persistent kernel, one CTA per SM, CTAs paired into clusters of two (tcgen05 cta_group::2): a pair works on
+// 256-point super-tiles, CTA r owning rows [128r, 128r+128), and two super-tiles (slots X/Y) are in flight per pair.
+//   warp 0      : weight producer (both CTAs) - streams ITS HALF (N/2 rows) of the packed bf16 weight blocks from L2
+//                 into a shared memory ring with tensor-map TMA loads (cp.async.bulk.tensor ... .cta_group::2) whose
+//                 complete_tx goes to the LEADER's full barrier, whichever CTA issued the load.  The pair
+//                 shares the B operand, so each SM pulls only half of the 1.2 MB of weights per super-tile: the weight
+//                 stream (L2 -> SM latency x ring depth) is what bounds this kernel, see DESIGN.md section 5.
+//   warp 1      : leader CTA: MMA issuer - the warp runs converged and one elected lane issues
+//                 tcgen05.mma.cta_group::2 (M=256, N=256/128, K=16, bf16 -> fp32 in TMEM); slot X accumulates in TMEM
+//                 columns [0,256) of both CTAs, slot Y in [256,512).  One ring stage (wait, MMAs, commit) is a single
+//                 asm block with the election inside.  Commits are multicast to the barriers of both CTAs.
+//                 peer CTA: idle.
+//   warps 2..9  : epilogue (both CTAs) - tcgen05.ld the accumulator, ReLU, round to bf16, write the next layer's A
 //                 operand back to shared memory in the UMMA chunk layout (activations never leave the SM);
-//                 positional encodings are computed here too.
-// While the tensor core runs layer L of slot X the epilogue warps drain layer L-1 of slot Y.
+//                 positional encodings are computed here too.  Publishing a tile = one arrive per warp on the
+//                 LEADER's aready barrier (remote arrive from the peer).
+// While the tensor cores run layer L of slot X the epilogue warps drain layer L-1 of slot Y.
 // Biases ride along as one extra K=16 MMA per layer against a constant "ones" tile (mlp_common.cuh).
 // The sigma head (N=1) and color_layer.2 (N=3) are CUDA-core dot products inside the epilogues.
 // TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
 // backward kernels: each epilogue thread stores the 16-byte groups it has rounded straight to global memory
 // (a warp covers 512 contiguous bytes per chunk), after the tile has been published to the issuer.
 #include "mlp_common.cuh"
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include <stdlib.h>
 #include <string.h>
 #include <utility>
@@ -25,27 +33,25 @@ namespace {
 using namespace mlp;
 using namespace umma;
 
-// Ring geometry: 3 x 16 KB (two N=256 MMAs per stage).  7 x 8 KB (one MMA per stage, deeper prefetch) was measured
-// 40 % SLOWER: the per-stage cost of the issuer (try_wait + fence + elect + commit) is about one MMA time.
 constexpr int kStages = 3;
-constexpr uint32_t kRingStageBytes = 16384;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
+constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epilogue warps
+constexpr int kCPS = 8;                      // K chunks per ring stage (= 4 MMAs); 16 KB (N=256) or 8 KB (N=128) per CTA
 
-// shared memory map (bytes)
+// shared memory map (bytes), identical in both CTAs of a pair (the MMA addresses the peer's tiles by the same offsets)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;            // 2 x 16 KB
 constexpr uint32_t kOffRing = kOffAux + 2 * kAuxBytes;           // kStages x 16 KB
-constexpr uint32_t kOffOnes = kOffRing + kStages * kRingStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
+constexpr uint32_t kOffOnes = kOffRing + kStages * kStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
 constexpr uint32_t kOnesBytes = 2 * kChunkBytes;
 constexpr uint32_t kOffConst = kOffOnes + kOnesBytes;
 // partial head dot products of the upper column half, [2 slots][128 rows][3] f32 (sigma uses [..][0];
 // reuse across j7 / j9 of a slot is ordered by the other slot's named barrier in between)
 constexpr uint32_t kOffPart = kOffConst + kConstBytes;
 constexpr uint32_t kOffBars = kOffPart + 2 * 128 * 3 * 4;
-// barriers: full[slot][stage], empty[slot][stage] (one set per issuer: a parity wait can only tell adjacent phases
-// apart, so the two issuers must never wait on the same barrier), accfull[slot], aready[slot]
+// barriers: full[slot][stage], empty[slot][stage] (one set per slot: a parity wait can only tell adjacent phases
+// apart), accfull[slot], aready[slot] (leader only)
 constexpr uint32_t kNumBars = 4 * kStages + 4;
 __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
 __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }
@@ -55,10 +61,14 @@ constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 
+// The packed weight image seen as a 2-D byte tensor [bytes/128][128]; one map per box height (= stage size / 128):
+// 128 rows = 16 KB (a full N=256 stage), 32 rows = the 2-chunk tail stage, 64 / 48 rows = the N=128 job's stages.
+struct WeightMaps { CUtensorMap m[4]; };
+
 struct FwdArgs {
   PointSource src;
   long long P;
-  int n_tiles;
+  int n_tiles;            // 128-point tiles, even (num_tiles(P))
   const uint8_t* wpack;   // packed forward weights
   const float* consts;    // fp32 consts block
   const float* noise;     // [P] sigma noise or null (model.py:160-162)
@@ -67,11 +77,51 @@ struct FwdArgs {
   uint8_t* stash_h;       // TRAIN: [8][n_tiles][64 KB]
   uint8_t* stash_f;       // TRAIN: [n_tiles][64 KB]
   uint8_t* stash_c;       // TRAIN: [n_tiles][32 KB]
-  long long* stats;       // bring-up only: wait-time counters of block 0 (DFN_FWD_STATS)
-  int debug;              // bring-up only (DFN_FWD_DEBUG): 1 = no weight copies, 2 = no epilogue math, 8 = wait statistics
 };
 
-__device__ __forceinline__ int tile_of(int it, int t) { return (it * 2 + t) * gridDim.x + blockIdx.x; }
+// ---- cluster helpers --------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// wait with cluster-scope acquire: the arrivals come from the peer CTA
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  long long t0 = 0;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) return;
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > 4000000000LL) {
+      printf("dfn: cluster mbarrier timeout (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+
+// tile of (iteration, slot) for this CTA: super-tile index * 2 + rank
+__device__ __forceinline__ int tile_of(int it, int t, int rank) {
+  const int n_pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
+  return 2 * ((it * 2 + t) * n_pairs + pair) + rank;
+}
 
 // ---- epilogue helpers ------------------------------------------------------------------------------
 // the first NC packed 32-column groups of one row -> stash (global); a warp covers 512 contiguous bytes per chunk
@@ -111,18 +161,13 @@ __device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, in
 // A generic issue loop with run-time shapes costs ~300 cycles per tcgen05.mma in address arithmetic alone
 // (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
 // whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
-constexpr int job_stages(int j) { return (job_bytes(j) + kRingStageBytes - 1) / kRingStageBytes; }
+// A ring stage holds kCPS K-chunks of this CTA's half of the weight block (N/2 rows each).
+constexpr int job_stages(int j) { return (job_kcb(j) + kCPS - 1) / kCPS; }
+constexpr int stage_chunks(int j, int k) { return (job_kcb(j) - k * kCPS) < kCPS ? (job_kcb(j) - k * kCPS) : kCPS; }
 constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
   int n = 0;
   for (int i = 0; i < j; ++i) n += 2 * job_stages(i);
   return n + t * job_stages(j);
-}
-
-// mbar_wait that also accumulates the cycles spent waiting (bring-up statistics)
-__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, long long& acc) {
-  const long long t0 = clock64();
-  mbar_wait(bar, parity);
-  acc += clock64() - t0;
 }
 
 struct ProdState {
@@ -130,93 +175,99 @@ struct ProdState {
   int last[kStages];          // slot that used the stage last (-1: never)
 };
 
+// tensor-map TMA load of `rows` x 128 bytes starting at row y of the weight image; completion (bytes) is signalled on
+// `mbar`, a shared::cluster address that may belong to the peer (leader) CTA
+__device__ __forceinline__ void tma_load_rows(uint32_t dst_smem, const CUtensorMap* map, uint32_t y, uint32_t mbar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(0u), "r"(y), "r"(mbar)
+      : "memory");
+}
+
 template <int J>
-__device__ __forceinline__ void produce_job(const uint8_t* wpack, uint32_t ring, uint32_t bar0, ProdState& ps,
-                                            const bool (&has)[2], int debug) {
-  constexpr uint32_t jbytes = job_bytes(J);
-  const uint8_t* src = wpack + job_off(J);
+__device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2]) {
+  constexpr uint32_t cb = job_half_chunk(J);
+  const uint32_t src = job_off(J) + rank * job_half_bytes(J);   // byte offset in the weight image
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     if (!has[t]) continue;
 #pragma unroll
     for (int k = 0; k < job_stages(J); ++k) {
-      constexpr uint32_t kFull = kRingStageBytes;
+      constexpr uint32_t kFull = kCPS * cb;
       const uint32_t off = k * kFull;
-      const uint32_t nb = (jbytes - off) < kFull ? (jbytes - off) : kFull;
+      const uint32_t nb = static_cast<uint32_t>(stage_chunks(J, k)) * cb;
       const int stage = (stage_prefix(J, t) + k) % kStages;
-      // the previous user of this stage (either slot) must have released it
+      // the previous user of this stage (either slot) must have released it (multicast commit of the leader)
       if (ps.last[stage] == 0) mbar_wait(bar0 + 8u * bar_empty_i(0, stage), ps.use[0][stage] ^ 1);
       else if (ps.last[stage] == 1) mbar_wait(bar0 + 8u * bar_empty_i(1, stage), ps.use[1][stage] ^ 1);
       ps.use[t][stage] ^= 1;
       ps.last[stage] = t;
+      // both halves complete on the LEADER's full barrier; its producer expects the bytes of the pair
       const uint32_t full = bar0 + 8u * bar_full_i(t, stage);
-      if (debug & 1) mbar_arrive(full);
-      else {
-        mbar_arrive_expect_tx(full, nb);
-        bulk_g2s(ring + stage * kRingStageBytes, src + off, nb, full);
-      }
+      const int mi = nb == 16384 ? 0 : (nb == 4096 ? 1 : (nb == 8192 ? 2 : 3));
+      if (rank == 0) mbar_arrive_expect_tx(full, 2 * nb);
+      tma_load_rows(ring + stage * kStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0));
     }
   }
 }
 template <int... Js>
-__device__ __forceinline__ void produce_all(const uint8_t* wpack, uint32_t ring, uint32_t bar0, ProdState& ps,
-                                            const bool (&has)[2], int debug, std::integer_sequence<int, Js...>) {
-  (produce_job<Js>(wpack, ring, bar0, ps, has, debug), ...);
+__device__ __forceinline__ void produce_all(const WeightMaps& maps, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
+                                            const bool (&has)[2], std::integer_sequence<int, Js...>) {
+  (produce_job<Js>(maps, rank, ring, bar0, ps, has), ...);
 }
 
-// One ring stage as a single asm block: bounded wait for the weights (a protocol bug traps instead of hanging),
-// NMMA x tcgen05.mma (K = 16 each) and the commit that releases the stage.  MMA i < NMMA-1 reads A at
+// One ring stage as a single asm block: bounded wait for the weights of BOTH CTAs (the leader's full barrier counts
+// its own producer and the peer's relay; a protocol bug traps instead of hanging), NMMA x tcgen05.mma.cta_group::2
+// (K = 16 each) and the multicast commit that releases the stage in both CTAs.  MMA i < NMMA-1 reads A at
 // a_lo + i*256 (two chunks further), the last one at a_last; B advances by B_STEP descriptor units per MMA.
-#define DFN_STAGE_HEAD                                          \
-  "{\n\t"                                                       \
-  ".reg .pred q, p, pe;\n\t"                                    \
-  ".reg .b32 cnt, al, bl;\n\t"                                  \
-  ".reg .b64 da, db;\n\t"                                       \
-  "mov.u32 cnt, 0;\n\t"                                         \
-  "SW_WAIT:\n\t"                                                \
-  "mbarrier.try_wait.parity.shared::cta.b64 q, [%0], %1;\n\t"   \
-  "@q bra SW_GO;\n\t"                                           \
-  "add.u32 cnt, cnt, 1;\n\t"                                    \
-  "setp.lt.u32 p, cnt, 8000000;\n\t"                            \
-  "@p bra SW_WAIT;\n\t"                                         \
-  "trap;\n\t"                                                   \
-  "SW_GO:\n\t"                                                  \
-  "tcgen05.fence::after_thread_sync;\n\t"                       \
-  "elect.sync _|pe, 0xffffffff;\n\t"                            \
+#define DFN_STAGE_HEAD                                                        \
+  "{\n\t"                                                                     \
+  ".reg .pred q, p, pe;\n\t"                                                  \
+  ".reg .b32 cnt, al, bl;\n\t"                                                \
+  ".reg .b64 da, db;\n\t"                                                     \
+  "mov.u32 cnt, 0;\n\t"                                                       \
+  "SW_WAIT:\n\t"                                                              \
+  "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 q, [%0], %1;\n\t" \
+  "@q bra SW_GO;\n\t"                                                         \
+  "add.u32 cnt, cnt, 1;\n\t"                                                  \
+  "setp.lt.u32 p, cnt, 8000000;\n\t"                                          \
+  "@p bra SW_WAIT;\n\t"                                                       \
+  "trap;\n\t"                                                                 \
+  "SW_GO:\n\t"                                                                \
+  "tcgen05.fence::after_thread_sync;\n\t"                                     \
+  "elect.sync _|pe, 0xffffffff;\n\t"                                          \
   "setp.ne.b32 p, %7, 0;\n\t"
 #define DFN_STAGE_FIRST                                         \
   "mov.b64 da, {%3, %5};\n\t"                                   \
   "mov.b64 db, {%4, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, p;\n\t"
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
 #define DFN_STAGE_NEXT(i)                                       \
   "add.u32 al, %3, " #i "*256;\n\t"                             \
   "add.u32 bl, %4, " #i "*%10;\n\t"                             \
   "mov.b64 da, {al, %5};\n\t"                                   \
   "mov.b64 db, {bl, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, 1;\n\t"
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
 #define DFN_STAGE_LAST(i)                                       \
   "add.u32 bl, %4, " #i "*%10;\n\t"                             \
   "mov.b64 da, {%9, %5};\n\t"                                   \
   "mov.b64 db, {bl, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, 1;\n\t"
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
 #define DFN_STAGE_ONLY                                          \
   "mov.b64 da, {%9, %5};\n\t"                                   \
   "mov.b64 db, {%4, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::1.kind::f16 [%2], da, db, %6, p;\n\t"
-#define DFN_STAGE_TAIL                                                                       \
-  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t"       \
-  "}"
-// last stage of a job: the second commit tells the epilogue that the accumulator is complete
-#define DFN_STAGE_TAIL_ACC                                                                   \
-  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t"       \
-  "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%11];\n\t"      \
-  "}"
+  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
+#define DFN_COMMIT(b) \
+  "@pe tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [" b "], %12;\n\t"
+#define DFN_STAGE_TAIL DFN_COMMIT("%8") "}"
+// last stage of a job: the second commit tells the epilogues of both CTAs that the accumulator is complete
+#define DFN_STAGE_TAIL_ACC DFN_COMMIT("%8") DFN_COMMIT("%11") "}"
 #define DFN_STAGE_OPERANDS                                                                                     \
   ::"r"(full_bar), "r"(parity), "r"(tacc), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc_first), "r"(empty_bar), \
-      "r"(a_last), "n"(B_STEP), "r"(acc_bar)                                                                      \
+      "r"(a_last), "n"(B_STEP), "r"(acc_bar), "h"(static_cast<uint16_t>(3))                                       \
       : "memory"
 
-// Executed by the whole (converged) issuer warp.
+// Executed by the whole (converged) issuer warp of the leader CTA.
 template <int NMMA, int B_STEP, bool ACC>
 __device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, uint32_t tacc, uint32_t a_lo, uint32_t a_last,
                                           uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc_first, uint32_t empty_bar,
@@ -242,18 +293,17 @@ __device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, ui
 }
 
 struct SlotCtx {
-  uint32_t ph0, ph1, ph2, ph3, ph4, ph5, ph6;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
+  uint32_t ph0, ph1, ph2;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
   uint32_t pa;              // phase of this slot's aready barrier
   bool has;                 // the slot has a tile in the current iteration
-  int tile, prev_tile;      // the slot's tile in the current / previous iteration (-1: none)
 };
 struct IssueCtx {
-  uint32_t sbase, bar0, tmem_base;
+  uint32_t sbase, bar0, tmem_base, rank;
   SlotCtx s0, s1;
-  int n_tiles, lane;
-  uint8_t *stash_h, *stash_f, *stash_c;
-  int debug;
-  long long w_aready;
+  int lane;
+#ifdef DFN_FWD_STATS
+  long long w_full, w_aready;   // bring-up build (-DDFN_FWD_STATS): cycles the issuer waits for weights / for the epilogues
+#endif
 };
 template <int T>
 __device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
@@ -261,14 +311,9 @@ __device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
 }
 template <int S>
 __device__ __forceinline__ uint32_t& ph_of(SlotCtx& c) {
-  static_assert(kStages <= 7, "one phase scalar per ring stage");
   if constexpr (S == 0) return c.ph0;
   else if constexpr (S == 1) return c.ph1;
-  else if constexpr (S == 2) return c.ph2;
-  else if constexpr (S == 3) return c.ph3;
-  else if constexpr (S == 4) return c.ph4;
-  else if constexpr (S == 5) return c.ph5;
-  else return c.ph6;
+  else return c.ph2;
 }
 
 // where chunk kc of job J's A operand lives (descriptor address units relative to the three bases)
@@ -282,24 +327,29 @@ __device__ __forceinline__ uint32_t a_chunk_lo(int kc, uint32_t a_act, uint32_t 
 
 template <int J, int T, int K>
 __device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc) {
-  constexpr int N = job_N(J), KCB = job_kcb(J);
-  constexpr uint32_t idesc = instr_desc_bf16(128, N, 0, 0);
-  constexpr uint32_t b_chunk = N * 16;                    // bytes per K chunk of the weight block
-  constexpr int CPS = kRingStageBytes / b_chunk;              // chunks per stage: 4 (N=256) or 8 (N=128)
+  constexpr int N = job_N(J);
+  constexpr uint32_t idesc = instr_desc_bf16(256, N, 0, 0);   // M = 256 over the CTA pair
+  constexpr uint32_t cb = job_half_chunk(J);                  // bytes per K chunk of this CTA's half of B
   constexpr uint32_t hi = desc_hi(128);
-  constexpr int B_STEP = 2 * (b_chunk >> 4);              // descriptor address units per MMA (two K chunks)
-  constexpr int kc0 = K * CPS;
+  constexpr int B_STEP = 2 * (cb >> 4);                       // descriptor address units per MMA (two K chunks)
+  constexpr int kc0 = K * kCPS;
   constexpr int stage = (stage_prefix(J, T) + K) % kStages;
-  constexpr int nchunk = (KCB - kc0) < CPS ? (KCB - kc0) : CPS;
+  constexpr int nchunk = stage_chunks(J, K);
   constexpr bool last = K == job_stages(J) - 1;
+  static_assert(nchunk % 2 == 0, "a K=16 MMA consumes two chunks");
   const uint32_t full = c.bar0 + 8u * bar_full_i(T, stage), empty = c.bar0 + 8u * bar_empty_i(T, stage);
-  const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
-  const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kRingStageBytes, b_chunk);
-  const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
-  const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
-  constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
   uint32_t& ph = ph_of<stage>(slot_of<T>(c));
-  stage_mma<nchunk / 2, B_STEP, last>(full, ph, tacc, a_lo, a_last, b_lo, hi, idesc, accf, empty, accfull);
+  if (c.rank == 0) {
+#ifdef DFN_FWD_STATS
+    { const long long t0 = clock64(); mbar_wait_cluster(full, ph); c.w_full += clock64() - t0; }
+#endif
+    const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
+    const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kStageBytes, cb);
+    const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
+    const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
+    constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
+    stage_mma<nchunk / 2, B_STEP, last>(full, ph, tacc, a_lo, a_last, b_lo, hi, idesc, accf, empty, accfull);
+  }
   ph ^= 1;
 }
 template <int J, int T, int... Ks>
@@ -308,32 +358,38 @@ __device__ __forceinline__ void issue_stages(IssueCtx& c, uint32_t a_act, uint32
   (issue_stage<J, T, Ks>(c, a_act, a_aux, a_ones, tacc), ...);
 }
 
-// Runs on the whole issuer warp (converged); single-lane work (bulk copies) is done by lane 0.
-template <int J, int T, bool TRAIN>
+// Runs on the whole warp 1 (converged) of both CTAs: issuer in the leader, relay in the peer.
+template <int J, int T>
 __device__ __forceinline__ void issue_job(IssueCtx& c) {
   SlotCtx& sc = slot_of<T>(c);
   if (!sc.has) return;
-  const uint32_t aready = c.bar0 + 8u * bar_aready_i(T);
-  if (c.debug & 8) mbar_wait_t(aready, sc.pa, c.w_aready); else mbar_wait(aready, sc.pa);
-  sc.pa ^= 1;
-  tc_fence_after();
-  const uint32_t act_addr = c.sbase + kOffAct + T * kActBytes;
-  const uint32_t a_act = desc_lo(act_addr, kChunkBytes);
+  if (c.rank == 0) {   // the A operand of this job (both CTAs' tiles) has been published
+#ifdef DFN_FWD_STATS
+    const long long t0 = clock64();
+#endif
+    mbar_wait_cluster(c.bar0 + 8u * bar_aready_i(T), sc.pa);
+#ifdef DFN_FWD_STATS
+    c.w_aready += clock64() - t0;
+#endif
+    sc.pa ^= 1;
+    tc_fence_after();
+  }
+  const uint32_t a_act = desc_lo(c.sbase + kOffAct + T * kActBytes, kChunkBytes);
   const uint32_t a_aux = desc_lo(c.sbase + kOffAux + T * kAuxBytes, kChunkBytes);
   const uint32_t a_ones = desc_lo(c.sbase + kOffOnes, kChunkBytes);
   const uint32_t tacc = c.tmem_base + T * 256;
-  // the last stage also commits accfull
   issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J)>{});
 }
-template <bool TRAIN, int... Js>
+template <int... Js>
 __device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
-  ((issue_job<Js, 0, TRAIN>(c), issue_job<Js, 1, TRAIN>(c)), ...);
+  ((issue_job<Js, 0>(c), issue_job<Js, 1>(c)), ...);
 }
 
 template <bool TRAIN>
-__global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a, const __grid_constant__ WeightMaps maps) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar0 = sbase + kOffBars;
   auto bar_accfull = [&](int t) { return bar0 + 8u * bar_accfull_i(t); };
@@ -341,52 +397,65 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
   float* consts = reinterpret_cast<float*>(smem + kOffConst);
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 4 * kStages; ++i) mbar_init(bar0 + 8u * i, 1);
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps); }
+    for (int t = 0; t < 2; ++t)
+      for (int s = 0; s < kStages; ++s) {
+        // full: used in the leader only (one arrive.expect_tx for the bytes of both CTAs' halves)
+        mbar_init(bar0 + 8u * bar_full_i(t, s), 1);
+        mbar_init(bar0 + 8u * bar_empty_i(t, s), 1);
+      }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), 2 * kEpiWarps); }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
-  for (int i = threadIdx.x; i < kConstFloats; i += blockDim.x) consts[i] = a.consts[i];
+  if (warp == 1) {   // one warp per CTA allocates all 512 TMEM columns of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + kOffTmemPtr), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
   // ones tile: [2 chunks][128 rows][8 bf16], column 0 of every row = 1.0
-  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += blockDim.x)
+  for (int i = threadIdx.x; i < static_cast<int>(kOnesBytes / 16); i += kThreads)
     *reinterpret_cast<uint4*>(smem + kOffOnes + i * 16) = make_uint4(i < 128 ? 0x3F80u : 0u, 0u, 0u, 0u);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();   // barriers of both CTAs are initialised before any remote arrive / multicast commit
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
 
-  const int n_it = (a.n_tiles + 2 * gridDim.x - 1) / (2 * gridDim.x);
+  const int n_pairs = gridDim.x >> 1;
+  const int n_super = a.n_tiles >> 1;
+  const int n_it = (n_super + 2 * n_pairs - 1) / (2 * n_pairs);
 
   if (warp == 0) {
-    // ================= weight producer =================
+    // ================= weight producer (this CTA's half of every block) =================
     if (lane == 0) {
       ProdState ps;
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
       for (int it = 0; it < n_it; ++it) {
-        const bool has[2] = {tile_of(it, 0) < a.n_tiles, tile_of(it, 1) < a.n_tiles};
-        produce_all(a.wpack, sbase + kOffRing, bar0, ps, has, a.debug, std::make_integer_sequence<int, kNumJobs>{});
+        const bool has[2] = {tile_of(it, 0, rank) < a.n_tiles, tile_of(it, 1, rank) < a.n_tiles};
+        produce_all(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumJobs>{});
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer (whole warp, converged; one elected lane issues) =================
+    // ================= leader: MMA issuer (whole warp, converged; one elected lane issues); peer: bookkeeping only =================
     IssueCtx c{};
-    c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.debug = a.debug; c.lane = lane;
-    c.n_tiles = a.n_tiles; c.stash_h = a.stash_h; c.stash_f = a.stash_f; c.stash_c = a.stash_c;
-    c.s0 = SlotCtx{};
-    c.s0.tile = c.s0.prev_tile = -1;
+    c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.lane = lane; c.rank = rank;
+    c.s0 = SlotCtx{0, 0, 0, 0, false};
     c.s1 = c.s0;
-    c.w_aready = 0;
-    const long long t0 = clock64();
+#ifdef DFN_FWD_STATS
+    c.w_full = c.w_aready = 0;
+    const long long t_start = clock64();
+#endif
     for (int it = 0; it < n_it; ++it) {
-      c.s0.tile = tile_of(it, 0); c.s0.has = c.s0.tile < a.n_tiles;
-      c.s1.tile = tile_of(it, 1); c.s1.has = c.s1.tile < a.n_tiles;
-      issue_all<TRAIN>(c, std::make_integer_sequence<int, kNumJobs>{});
-      c.s0.prev_tile = c.s0.has ? c.s0.tile : -1;
-      c.s1.prev_tile = c.s1.has ? c.s1.tile : -1;
+      c.s0.has = tile_of(it, 0, rank) < a.n_tiles;
+      c.s1.has = tile_of(it, 1, rank) < a.n_tiles;
+      issue_all(c, std::make_integer_sequence<int, kNumJobs>{});
     }
-    if (a.stats && blockIdx.x == 0 && lane == 0) { a.stats[2] = clock64() - t0; a.stats[3] = c.w_aready; }
+#ifdef DFN_FWD_STATS
+    if (blockIdx.x == 0 && lane == 0)
+      printf("fwd stats (leader of pair 0, cycles): issuer total %lld wait_aready %lld wait_weights %lld\n", clock64() - t_start,
+             c.w_aready, c.w_full);
+#endif
   } else {
     // ================= epilogue / PE warps =================
     const int ew = warp - 2;
@@ -396,23 +465,23 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     float* part = reinterpret_cast<float*>(smem + kOffPart);
     uint32_t pf[2] = {0, 0};
-    long long w_acc = 0;
-    const long long t_epi0 = clock64();
+    const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
 
     auto point_of = [&](int tile) {
       long long p = static_cast<long long>(tile) * kTile + row;
       return p < a.P ? p : a.P - 1;
     };
-    // activations / encodings written -> visible to the async proxy -> one arrive per warp
+    // activations / encodings written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one
+    // arrive per warp on the leader's barrier
     auto publish = [&](int t) {
       tc_fence_before();
-      fence_proxy_async();
+      asm volatile("fence.proxy.async;" ::: "memory");
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_aready(t));
+      if (lane == 0) mbar_arrive_cluster(aready_leader[t]);
     };
     // initial PE for both slots
     for (int t = 0; t < 2; ++t) {
-      const int tile = tile_of(0, t);
+      const int tile = tile_of(0, t, rank);
       if (tile < a.n_tiles) {
         float x[3], d[3];
         load_point(a.src, point_of(tile), x, d);
@@ -424,25 +493,24 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
     for (int it = 0; it < n_it; ++it) {
       for (int j = 0; j < kNumJobs; ++j) {
         for (int t = 0; t < 2; ++t) {
-          const int tile = tile_of(it, t);
+          const int tile = tile_of(it, t, rank);
           if (tile >= a.n_tiles) continue;
           uint8_t* act = smem + kOffAct + t * kActBytes;
           uint8_t* aux = smem + kOffAux + t * kAuxBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
           const long long p = static_cast<long long>(tile) * kTile + row;
-          uint8_t* st = nullptr;   // TRAIN: where the bf16 tile this job produces goes in the stash
+          // TRAIN: the bf16 tile this job produces (h1..h8, features, colour hidden) also goes to the stash
+          uint8_t* st = nullptr;
           if (TRAIN) {
             if (j < 8) st = a.stash_h + ((static_cast<size_t>(j) * a.n_tiles + tile) << 16);
             else if (j == 8) st = a.stash_f + (static_cast<size_t>(tile) << 16);
             else st = a.stash_c + (static_cast<size_t>(tile) << 15);
           }
-          if (a.debug & 8) mbar_wait_t(bar_accfull(t), pf[t], w_acc); else mbar_wait(bar_accfull(t), pf[t]);
+          mbar_wait(bar_accfull(t), pf[t]);
           pf[t] ^= 1;
           tc_fence_after();
 
-          if (a.debug & 2) {
-            publish(t);
-          } else if (j < 9) {
+          if (j < 9) {
             float sdot = 0.f;
             const int c0 = hh * 128;
             uint32_t v0[32], v1[32], keep[64];
@@ -508,13 +576,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
               }
             }
             // next tile of this slot: its pos-PE goes into aux (dir-PE was consumed by job 9's MMAs)
-            const int ntile = tile_of(it + 1, t);
+            const int ntile = tile_of(it + 1, t, rank);
             if (ntile < a.n_tiles) {
               float x[3], d[3];
               load_point(a.src, point_of(ntile), x, d);
               write_pe_row(aux, nullptr, row, hh, x, d);
+              publish(t);   // (no publish after the slot's last tile: nobody waits for it)
             }
-            publish(t);
             if (TRAIN) stash_row<2>(st, c0, row, keep);
             float* pr = part + (t * 128 + row) * 3;
             if (hh == 1) { pr[0] = r0; pr[1] = r1; pr[2] = r2; }
@@ -531,16 +599,15 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
         }
       }
     }
-    if (a.stats && blockIdx.x == 0 && threadIdx.x == 64) { a.stats[5] = clock64() - t_epi0; a.stats[6] = w_acc; }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();   // the leader's MMAs read the peer's shared memory: nobody leaves before both are done
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
 }
 
 }  // namespace
-
 // ---------------------------------------------------------------------------------------------------
 // weight packing: flat fp32 parameters -> bf16 operand images + fp32 consts
 // ---------------------------------------------------------------------------------------------------
@@ -560,9 +627,11 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
     if (idx < nf) {
       int j = 0;
       while (j + 1 < kNumJobs && static_cast<uint32_t>(idx) * 2u >= job_off(j + 1)) ++j;
-      const int e = idx - job_off(j) / 2;
-      const int N = job_N(j);
-      const int kc = e / (N * 8), n = (e / 8) % N, k = kc * 8 + (e & 7);
+      const int e0 = idx - job_off(j) / 2;
+      const int N = job_N(j), NH = N / 2;
+      const int half_elems = job_half_bytes(j) / 2;
+      const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half
+      const int kc = e / (NH * 8), n = r * NH + (e / 8) % NH, k = kc * 8 + (e & 7);
       const int layer = j < 8 ? j : (j == 8 ? 9 : 10);   // reference layer index of job j
       const int kdata = job_kc(j) * 8;
       float v = 0.f;
@@ -620,6 +689,30 @@ static int check_source(const dfn_point_source* s, long long P, const char* who)
   return DFN_OK;
 }
 
+// tensor maps over the packed weight image (rebuilt per call: a few hundred ns of host time, no device work)
+static int make_weight_maps(const void* fwd_pack, WeightMaps* out) {
+  static PFN_cuTensorMapEncodeTiled encode = nullptr;
+  if (!encode) {
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    DFN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "mlp_forward(driver entry point)");
+    DFN_CHECK_ARG(fn && q == cudaDriverEntryPointSuccess, "mlp_forward: cuTensorMapEncodeTiled not available");
+    encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
+  }
+  const cuuint32_t rows[4] = {128, 32, 64, 48};
+  for (int i = 0; i < 4; ++i) {
+    const cuuint64_t gdim[2] = {128, kFwdPackBytes / 128};
+    const cuuint64_t gstride[1] = {128};
+    const cuuint32_t box[2] = {128, rows[i]};
+    const cuuint32_t estride[2] = {1, 1};
+    const CUresult r = encode(&out->m[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(fwd_pack), gdim, gstride, box, estride,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DFN_CHECK_ARG(r == CUDA_SUCCESS, "mlp_forward: cuTensorMapEncodeTiled failed (%d)", static_cast<int>(r));
+  }
+  return DFN_OK;
+}
+
 extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
                                const float* noise, float* rgb, float* sigma, void* stash, void* stream) {
   if (int rc = check_source(src, P, "mlp_forward")) return rc;
@@ -635,27 +728,19 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
     a.stash_f = s + 8LL * a.n_tiles * 65536;
     a.stash_c = a.stash_f + 1LL * a.n_tiles * 65536;
   }
-  const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
+  WeightMaps maps;
+  if (int rc = make_weight_maps(fwd_pack, &maps)) return rc;
+  // one CTA per SM, paired: grid = 2 * min(#SM / 2, #super-tiles)
+  const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  const int grid = 2 * pairs;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (const char* e = getenv("DFN_FWD_DEBUG")) a.debug = atoi(e);
-  static long long* d_stats = nullptr;
-  if (getenv("DFN_FWD_STATS")) {
-    if (!d_stats) cudaMalloc(&d_stats, 64);
-    a.stats = d_stats;
-  }
   if (stash) {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a, maps);
   } else {
     DFN_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_forward");
-    mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
+    mlp_fwd_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a, maps);
   }
   DFN_CHECK_LAUNCH("mlp_forward");
-  if (a.stats) {
-    long long h[8];
-    cudaMemcpy(h, a.stats, 64, cudaMemcpyDeviceToHost);
-    fprintf(stderr, "fwd stats (block 0, cycles): mma total %lld wait_aready %lld | epi total %lld wait_accfull %lld\n", h[2], h[3],
-            h[5], h[6]);
-  }
   return DFN_OK;
 }
