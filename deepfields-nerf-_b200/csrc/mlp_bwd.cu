@@ -1,6 +1,7 @@
 // Backward of the fused vanilla-NeRF MLP, part 1: the data-gradient chain (autograd of reference
-// scripts/model.py:139-187 w.r.t. the hidden activations), same persistent two-slot tcgen05 pipeline as
-// the forward kernel.  Per 128-point tile:
+// scripts/model.py:139-187 w.r.t. the hidden activations).  Same pipeline as the forward kernel (mlp_pipe.cuh):
+// persistent CTA pairs (tcgen05 cta_group::2, M = 256), two 256-point super-tiles in flight, W^T streamed through
+// a 6 x 16 KB ring by tensor-map TMA loads (each SM holds half of every block).  Per 128-point tile:
 //   prologue : dZ_c2 = d_rgb * rgb(1-rgb)            (sigmoid', 3 columns, fp32 -> global)
 //              dZ_c0 = (dZ_c2 * color_layer.2.weight) masked by c > 0   (CUDA cores, K = 3)
 //   b0       : d feat = dZ_c0 * color_layer.0.weight[:, :256]           (tcgen05, K = 128)
@@ -8,8 +9,8 @@
 //   b2..b8   : d h7 .. d h1 through skip_layers / pos_layers (skip_layers.0 uses its first 256 columns)
 // Every dZ is rounded to bf16 (what bf16 autocast autograd does), written back to shared memory as the next
 // job's A operand and stored to the dz scratch (chunk layout) for the weight-gradient kernel.  ReLU masks come
-// from the forward's activation stash (h > 0), read straight from global memory by the epilogue threads.
-#include "mlp_common.cuh"
+// from the bit tiles the forward wrote beside its activation stash (32 B per point and layer instead of 512 B).
+#include "mlp_pipe.cuh"
 
 namespace mlp {
 // dz scratch layout (per n_tiles): [8][nt][64K] dZ_1..dZ_8 | [nt][64K] dZ_f | [nt][32K] dZ_c0 | [nt][128][4] f32
@@ -25,25 +26,48 @@ __host__ __device__ inline size_t dz_off_small(int nt, int tile) {
 namespace {
 using namespace mlp;
 using namespace umma;
+using namespace mlp_pipe;
 
-constexpr int kStages = 4;
+constexpr int kStages = 6;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;
+constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
 
-constexpr uint32_t kOffAct = 0;
-constexpr uint32_t kOffRing = kOffAct + 2 * kActBytes;
+// shared memory map (bytes), identical in both CTAs of a pair
+constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB (dZ tiles = A operands)
+constexpr uint32_t kOffRing = kOffAct + 2 * kActBytes;           // kStages x 16 KB
 constexpr uint32_t kOffConst = kOffRing + kStages * kStageBytes;
 constexpr uint32_t kOffBars = kOffConst + kConstBytes;
-constexpr uint32_t kNumBars = 2 * kStages + 4;
+constexpr uint32_t kNumBars = 4 * kStages + 4;
 constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 
+// pipeline policy: 9 jobs, all N = 256; K = 128 (b0) or 256; no bias slices; A operand = the slot's dZ tile
+struct BwdPipe {
+  static constexpr int kNumJobs = kNumBwdJobs;
+  static constexpr int kStages = ::kStages;
+  static constexpr uint32_t kOffRing = ::kOffRing;
+  static __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
+  static __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }
+  static __host__ __device__ constexpr uint32_t bar_accfull_i(int t) { return 4 * kStages + t; }
+  static __host__ __device__ constexpr uint32_t bar_aready_i(int t) { return 4 * kStages + 2 + t; }
+  static __host__ __device__ constexpr int job_N(int) { return 256; }
+  static __host__ __device__ constexpr int job_chunks(int b) { return bjob_kc(b); }
+  static __host__ __device__ constexpr uint32_t job_off(int b) { return bjob_off(b); }
+  static __host__ __device__ constexpr uint32_t job_half_chunk(int) { return 128u * 16u; }
+  static __host__ __device__ constexpr uint32_t job_half_bytes(int b) { return bjob_bytes(b) / 2; }
+  struct ABases { uint32_t act; };
+  static __device__ __forceinline__ ABases bases(uint32_t sbase, int T) {
+    return ABases{desc_lo(sbase + kOffAct + T * kActBytes, kChunkBytes)};
+  }
+  template <int J>
+  static __device__ __forceinline__ uint32_t a_chunk_lo(int kc, const ABases& b) { return b.act + kc * (kChunkBytes >> 4); }
+};
+
 struct DgradArgs {
   long long P;
-  int n_tiles;
-  const uint8_t* wpack;  // packed W^T images
+  int n_tiles;           // even (num_tiles(P))
   const float* consts;
   const float* rgb;      // [P,3] forward output
   const float* sigma;    // [P]
@@ -53,93 +77,88 @@ struct DgradArgs {
   uint8_t* dz;
 };
 
-__device__ __forceinline__ int tile_of(int it, int t) { return (it * 2 + t) * gridDim.x + blockIdx.x; }
-
 __device__ __forceinline__ uint32_t relu_mask2(uint32_t h2) {
   // 0xFFFF per bf16 half that is > 0 (post-ReLU activations are >= +0)
   return ((h2 & 0x0000FFFFu) ? 0x0000FFFFu : 0u) | ((h2 & 0xFFFF0000u) ? 0xFFFF0000u : 0u);
 }
 
-__global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs a) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs a, const __grid_constant__ WeightMaps maps) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar0 = sbase + kOffBars;
-  auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
-  auto bar_wempty = [&](int s) { return bar0 + 8u * (kStages + s); };
-  auto bar_accfull = [&](int t) { return bar0 + 8u * (2 * kStages + t); };
-  auto bar_aready = [&](int t) { return bar0 + 8u * (2 * kStages + 2 + t); };
+  auto bar_accfull = [&](int t) { return bar0 + 8u * BwdPipe::bar_accfull_i(t); };
+  auto bar_aready = [&](int t) { return bar0 + 8u * BwdPipe::bar_aready_i(t); };
   float* consts = reinterpret_cast<float*>(smem + kOffConst);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(bar_wfull(s), 1); mbar_init(bar_wempty(s), 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiThreads); }
+    for (int t = 0; t < 2; ++t)
+      for (int s = 0; s < kStages; ++s) {
+        mbar_init(bar0 + 8u * BwdPipe::bar_full_i(t, s), 1);    // leader only: expect_tx of both CTAs' halves
+        mbar_init(bar0 + 8u * BwdPipe::bar_empty_i(t, s), 1);
+      }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), 2 * kEpiWarps); }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(sbase + kOffTmemPtr, 512);
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + kOffTmemPtr), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
   for (int i = threadIdx.x; i < kConstFloats; i += kThreads) consts[i] = a.consts[i];
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + kOffTmemPtr);
-  const int n_it = (a.n_tiles + 2 * gridDim.x - 1) / (2 * gridDim.x);
+  const int n_pairs = gridDim.x >> 1;
   const int nt = a.n_tiles;
+  const int n_it = ((nt >> 1) + 2 * n_pairs - 1) / (2 * n_pairs);
 
   if (warp == 0) {
-    if (lane == 0) {  // ---- weight producer
-      int stage = 0; uint32_t ph = 0;
-      for (int it = 0; it < n_it; ++it)
-        for (int b = 0; b < kNumBwdJobs; ++b) {
-          const uint32_t jbytes = bjob_bytes(b);
-          const uint8_t* src = a.wpack + bjob_off(b);
-          for (int t = 0; t < 2; ++t) {
-            if (tile_of(it, t) >= nt) continue;
-            for (uint32_t off = 0; off < jbytes; off += kStageBytes) {
-              mbar_wait(bar_wempty(stage), ph ^ 1);
-              mbar_arrive_expect_tx(bar_wfull(stage), kStageBytes);
-              bulk_g2s(sbase + kOffRing + stage * kStageBytes, src + off, kStageBytes, bar_wfull(stage));
-              if (++stage == kStages) { stage = 0; ph ^= 1; }
-            }
-          }
-        }
+    if (lane == 0) {  // ---- weight producer (this CTA's half of every W^T block)
+      ProdState<BwdPipe> ps;
+#pragma unroll
+      for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
+      for (int it = 0; it < n_it; ++it) {
+        const bool has[2] = {tile_of(it, 0, rank) < nt, tile_of(it, 1, rank) < nt};
+        produce_all<BwdPipe>(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumBwdJobs>{});
+      }
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ---- MMA issuer
-      int stage = 0; uint32_t ph = 0;
-      uint32_t pa[2] = {0, 0};
-      const uint32_t idesc = instr_desc_bf16(128, 256, 0, 0);
-      for (int it = 0; it < n_it; ++it)
-        for (int b = 0; b < kNumBwdJobs; ++b) {
-          const int kc_total = bjob_kc(b);
-          for (int t = 0; t < 2; ++t) {
-            if (tile_of(it, t) >= nt) continue;
-            mbar_wait(bar_aready(t), pa[t]); pa[t] ^= 1;
-            tc_fence_after();
-            const uint32_t act = sbase + kOffAct + t * kActBytes;
-            const uint32_t tacc = tmem_base + t * 256;
-            for (int kc0 = 0; kc0 < kc_total; kc0 += 4) {
-              mbar_wait(bar_wfull(stage), ph);
-              tc_fence_after();
-              const uint32_t wst = sbase + kOffRing + stage * kStageBytes;
-#pragma unroll
-              for (int c = 0; c < 4; c += 2) {
-                const int kc = kc0 + c;
-                mma_bf16(tacc, smem_desc(act + kc * kChunkBytes, kChunkBytes, 128), smem_desc(wst + c * 4096, 4096, 128),
-                         idesc, kc > 0 ? 1u : 0u);
-              }
-              mma_commit(bar_wempty(stage));
-              if (++stage == kStages) { stage = 0; ph ^= 1; }
-            }
-            mma_commit(bar_accfull(t));
-          }
-        }
+    // ---- leader: MMA issuer (whole warp converged, one elected lane issues); peer: bookkeeping only
+    IssueCtx c{};
+    c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.lane = lane; c.rank = rank;
+    c.s0 = SlotCtx{};
+    c.s1 = c.s0;
+#ifdef DFN_FWD_STATS
+    c.w_full = c.w_aready = 0;
+    const long long t_start = clock64();
+#endif
+    for (int it = 0; it < n_it; ++it) {
+      c.s0.has = tile_of(it, 0, rank) < nt;
+      c.s1.has = tile_of(it, 1, rank) < nt;
+      issue_all<BwdPipe>(c, std::make_integer_sequence<int, kNumBwdJobs>{});
     }
+#ifdef DFN_FWD_STATS
+    if (blockIdx.x == 0 && lane == 0)
+      printf("dgrad stats (leader of pair 0, cycles): issuer total %lld wait_aready %lld wait_weights %lld\n", clock64() - t_start,
+             c.w_aready, c.w_full);
+#endif
   } else {
     // ---- epilogue warps
     const int ew = warp - 2, q = warp & 3, hh = ew >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     uint32_t pf[2] = {0, 0};
+    const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
+    // dZ tile written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one arrive per warp
+    auto publish = [&](int t) {
+      tc_fence_before();
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(aready_leader[t]);
+    };
 
     // prologue of a tile: dZ_c0 -> act chunks 0..15 (+ dz scratch), small fp32 grads
     auto prologue = [&](int t, int tile) {
@@ -177,39 +196,34 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
           const float d1 = g[0] * w2[k + 1] + g[1] * w2[128 + k + 1] + g[2] * w2[256 + k + 1];
           o4[i] = pack_bf16x2(d0, d1) & relu_mask2(cw[i]);
         }
-        const uint4 q4 = make_uint4(o4[0], o4[1], o4[2], o4[3]);
-        *reinterpret_cast<uint4*>(act + off) = q4;
+        *reinterpret_cast<uint4*>(act + off) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
         st_global_v4(dzc0 + off, o4[0], o4[1], o4[2], o4[3]);
       }
     };
 
     for (int t = 0; t < 2; ++t) {
-      const int tile = tile_of(0, t);
+      const int tile = tile_of(0, t, rank);
       if (tile < nt) prologue(t, tile);
-      fence_proxy_async();
-      mbar_arrive(bar_aready(t));
+      publish(t);
     }
 
     for (int it = 0; it < n_it; ++it)
       for (int b = 0; b < kNumBwdJobs; ++b)
         for (int t = 0; t < 2; ++t) {
-          const int tile = tile_of(it, t);
+          const int tile = tile_of(it, t, rank);
           if (tile >= nt) continue;
           uint8_t* act = smem + kOffAct + t * kActBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
           const int c0 = hh * 128;
-          // mask source (h_{l+1} of the forward stash) and dz destination
+          // ReLU mask of h_{l+1} (bit tile written by the forward, 16 B per thread) and dz destination
           const int l = 8 - b;  // b >= 1
-          const uint8_t* hsrc = b >= 1 ? a.stash + ((static_cast<size_t>(l) * nt + tile) << 16) : nullptr;
+          uint4 mk = make_uint4(0, 0, 0, 0);
+          if (b >= 1)
+            mk = *reinterpret_cast<const uint4*>(a.stash + stash_off_mask(nt) + ((static_cast<size_t>(l) * nt + tile) << 12) +
+                                                 (hh * 128 + row) * 16);
           uint8_t* dst = b == 0 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(l, nt, tile);
           float dsig = 0.f;
           if (b == 1) dsig = reinterpret_cast<const float4*>(a.dz + dz_off_small(nt, tile))[row].w;
-          uint4 hb[2][4];
-          if (b >= 1) {
-#pragma unroll
-            for (int g4 = 0; g4 < 4; ++g4)
-              hb[0][g4] = *reinterpret_cast<const uint4*>(hsrc + (c0 / 8 + g4) * kChunkBytes + row * 16);
-          }
           mbar_wait(bar_accfull(t), pf[t]); pf[t] ^= 1;
           tc_fence_after();
           uint32_t v0[32], v1[32];
@@ -220,14 +234,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
             uint32_t (&cur)[32] = (cc & 1) ? v1 : v0;
             uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
             const int col0 = c0 + cc * 32;
-            if (cc < 3) {
-              tmem_ld32(tacc + col0 + 32, nxt);
-              if (b >= 1) {
-#pragma unroll
-                for (int g4 = 0; g4 < 4; ++g4)
-                  hb[(cc + 1) & 1][g4] = *reinterpret_cast<const uint4*>(hsrc + ((col0 + 32) / 8 + g4) * kChunkBytes + row * 16);
-              }
-            }
+            if (cc < 3) tmem_ld32(tacc + col0 + 32, nxt);
+            const uint32_t mw = cc == 0 ? mk.x : (cc == 1 ? mk.y : (cc == 2 ? mk.z : mk.w));
 #pragma unroll
             for (int g4 = 0; g4 < 4; ++g4) {
               float x[8];
@@ -242,8 +250,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
               o.x = pack_bf16x2(x[0], x[1]); o.y = pack_bf16x2(x[2], x[3]);
               o.z = pack_bf16x2(x[4], x[5]); o.w = pack_bf16x2(x[6], x[7]);
               if (b >= 1) {
-                const uint4 h = hb[cc & 1][g4];
-                o.x &= relu_mask2(h.x); o.y &= relu_mask2(h.y); o.z &= relu_mask2(h.z); o.w &= relu_mask2(h.w);
+                o.x &= relu_bits_expand(mw, g4 * 4); o.y &= relu_bits_expand(mw, g4 * 4 + 1);
+                o.z &= relu_bits_expand(mw, g4 * 4 + 2); o.w &= relu_bits_expand(mw, g4 * 4 + 3);
               }
               const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
               if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;
@@ -252,18 +260,18 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_dgrad_kernel(const DgradArgs 
             if (cc < 3) tmem_ld_wait();
           }
           if (b == kNumBwdJobs - 1) {
-            const int ntile = tile_of(it + 1, t);
-            if (ntile < nt) prologue(t, ntile);
+            const int ntile = tile_of(it + 1, t, rank);
+            if (ntile < nt) { prologue(t, ntile); publish(t); }
+          } else {
+            publish(t);
           }
-          tc_fence_before();
-          fence_proxy_async();
-          mbar_arrive(bar_aready(t));
         }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();   // the leader's MMAs read the peer's shared memory: nobody leaves before both are done
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
 }
 
 }  // namespace
@@ -284,12 +292,14 @@ extern "C" int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const f
   if (P == 0) return DFN_OK;
   DgradArgs a{};
   a.P = P; a.n_tiles = static_cast<int>(num_tiles(P));
-  a.wpack = static_cast<const uint8_t*>(bwd_pack); a.consts = consts; a.rgb = rgb; a.sigma = sigma;
+  a.consts = consts; a.rgb = rgb; a.sigma = sigma;
   a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.stash = static_cast<const uint8_t*>(stash); a.dz = static_cast<uint8_t*>(dz);
-  const int grid = a.n_tiles < dfn_num_sms() ? a.n_tiles : dfn_num_sms();
+  WeightMaps maps;
+  if (int rc = make_weight_maps(bwd_pack, kBwdPackBytes, &maps)) return rc;
+  const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DFN_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward_dgrad");
-  mlp_dgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
+  mlp_dgrad_kernel<<<2 * pairs, kThreads, kSmemBytes, st>>>(a, maps);
   DFN_CHECK_LAUNCH("mlp_backward_dgrad");
   return DFN_OK;
 }

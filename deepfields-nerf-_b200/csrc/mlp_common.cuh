@@ -110,6 +110,24 @@ __host__ __device__ constexpr int layer_out(int i) {
   return outs[i];
 }
 
+// Activation stash written by a training forward, per nt = num_tiles(P) tiles (bytes):
+//   [8][nt][64 KB] h1..h8 | [nt][64 KB] features | [nt][32 KB] colour hidden | [8][nt][4 KB] ReLU bit masks of h1..h8
+// A mask tile is [2 column halves][128 rows][4 words]; word g of (half hh, row r) covers columns hh*128 + g*32 .. +31 in
+// the order of the packed bf16 pairs: bit i = column 2i, bit 16+i = column 2i+1 of the group (i < 16).
+__host__ __device__ constexpr long long stash_off_feat(long long nt) { return 8 * nt * 65536; }
+__host__ __device__ constexpr long long stash_off_c(long long nt) { return 9 * nt * 65536; }
+__host__ __device__ constexpr long long stash_off_mask(long long nt) { return 9 * nt * 65536 + nt * 32768; }
+__host__ __device__ constexpr long long stash_total_bytes(long long nt) { return stash_off_mask(nt) + 8 * nt * 4096; }
+// 16 packed bf16 pairs (post-ReLU, i.e. >= +0) -> 32 "is positive" bits in the order above
+__device__ __forceinline__ uint32_t relu_bits16(const uint32_t* pk) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) m = (m >> 1) | ((pk[i] + 0x7FFF7FFFu) & 0x80008000u);   // 0x0001..0x7F80 + 0x7FFF sets bit 15
+  return m;
+}
+// the 0xFFFF-per-half AND mask of packed pair i from such a word
+__device__ __forceinline__ uint32_t relu_bits_expand(uint32_t m, int i) { return ((m >> i) & 0x00010001u) * 0xFFFFu; }
+
 // how a tile's points are produced: the public dfn_point_source (include/deepfields_b200.h)
 using PointSource = dfn_point_source;
 

@@ -22,9 +22,7 @@
 // TRAIN=true additionally stashes h1..h8, features and the colour hidden layer (bf16, chunk layout) for the
 // backward kernels: each epilogue thread stores the 16-byte groups it has rounded straight to global memory
 // (a warp covers 512 contiguous bytes per chunk), after the tile has been published to the issuer.
-#include "mlp_common.cuh"
-#include <cuda.h>
-#include <cudaTypedefs.h>
+#include "mlp_pipe.cuh"
 #include <stdlib.h>
 #include <string.h>
 #include <utility>
@@ -32,12 +30,12 @@
 namespace {
 using namespace mlp;
 using namespace umma;
+using namespace mlp_pipe;
 
 constexpr int kStages = 3;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epilogue warps
-constexpr int kCPS = 8;                      // K chunks per ring stage (= 4 MMAs); 16 KB (N=256) or 8 KB (N=128) per CTA
 
 // shared memory map (bytes), identical in both CTAs of a pair (the MMA addresses the peer's tiles by the same offsets)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
@@ -61,9 +59,34 @@ constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 
-// The packed weight image seen as a 2-D byte tensor [bytes/128][128]; one map per box height (= stage size / 128):
-// 128 rows = 16 KB (a full N=256 stage), 32 rows = the 2-chunk tail stage, 64 / 48 rows = the N=128 job's stages.
-struct WeightMaps { CUtensorMap m[4]; };
+// pipeline policy (mlp_pipe.cuh): shared-memory map, job table, A-operand addressing of the forward chain
+struct FwdPipe {
+  static constexpr int kNumJobs = mlp::kNumJobs;
+  static constexpr int kStages = ::kStages;
+  static constexpr uint32_t kOffRing = ::kOffRing;
+  static __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return ::bar_full_i(t, s); }
+  static __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return ::bar_empty_i(t, s); }
+  static __host__ __device__ constexpr uint32_t bar_accfull_i(int t) { return ::bar_accfull_i(t); }
+  static __host__ __device__ constexpr uint32_t bar_aready_i(int t) { return ::bar_aready_i(t); }
+  static __host__ __device__ constexpr int job_N(int j) { return mlp::job_N(j); }
+  static __host__ __device__ constexpr int job_chunks(int j) { return mlp::job_kcb(j); }
+  static __host__ __device__ constexpr uint32_t job_off(int j) { return mlp::job_off(j); }
+  static __host__ __device__ constexpr uint32_t job_half_chunk(int j) { return mlp::job_half_chunk(j); }
+  static __host__ __device__ constexpr uint32_t job_half_bytes(int j) { return mlp::job_half_bytes(j); }
+  struct ABases { uint32_t act, aux, ones; };   // descriptor "lo" words of the slot's tiles
+  static __device__ __forceinline__ ABases bases(uint32_t sbase, int T) {
+    return ABases{desc_lo(sbase + kOffAct + T * kActBytes, kChunkBytes), desc_lo(sbase + kOffAux + T * kAuxBytes, kChunkBytes),
+                  desc_lo(sbase + kOffOnes, kChunkBytes)};
+  }
+  // where chunk kc of job J's A operand lives: hidden activations | positional encoding | ones tile (bias slice)
+  template <int J>
+  static __device__ __forceinline__ uint32_t a_chunk_lo(int kc, const ABases& b) {
+    constexpr int KC = job_kc(J), KC_ACT = job_kc_act(J);
+    if (kc >= KC) return b.ones + (kc - KC) * (kChunkBytes >> 4);
+    if (kc < KC_ACT) return b.act + kc * (kChunkBytes >> 4);
+    return b.aux + (kc - KC_ACT) * (kChunkBytes >> 4);
+  }
+};
 
 struct FwdArgs {
   PointSource src;
@@ -77,51 +100,8 @@ struct FwdArgs {
   uint8_t* stash_h;       // TRAIN: [8][n_tiles][64 KB]
   uint8_t* stash_f;       // TRAIN: [n_tiles][64 KB]
   uint8_t* stash_c;       // TRAIN: [n_tiles][32 KB]
+  uint8_t* stash_m;       // TRAIN: [8][n_tiles][4 KB] ReLU bit masks of h1..h8 (mlp_common.cuh)
 };
-
-// ---- cluster helpers --------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// address of the same shared-memory location in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-// wait with cluster-scope acquire: the arrivals come from the peer CTA
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
-  long long t0 = 0;
-  for (;;) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    if (ok) return;
-    if (t0 == 0) t0 = clock64();
-    else if (clock64() - t0 > 4000000000LL) {
-      printf("dfn: cluster mbarrier timeout (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
-      __trap();
-    }
-  }
-}
-
-// tile of (iteration, slot) for this CTA: super-tile index * 2 + rank
-__device__ __forceinline__ int tile_of(int it, int t, int rank) {
-  const int n_pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
-  return 2 * ((it * 2 + t) * n_pairs + pair) + rank;
-}
 
 // ---- epilogue helpers ------------------------------------------------------------------------------
 // the first NC packed 32-column groups of one row -> stash (global); a warp covers 512 contiguous bytes per chunk
@@ -155,234 +135,6 @@ __device__ __forceinline__ void emit32(const uint32_t (&v)[32], uint8_t* act, in
     const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
     if (act) *reinterpret_cast<uint4*>(act + off) = q;
   }
-}
-
-// ---- weight ring + MMA issue, one instantiation per job so every shape is a compile-time constant -----
-// A generic issue loop with run-time shapes costs ~300 cycles per tcgen05.mma in address arithmetic alone
-// (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
-// whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
-// A ring stage holds kCPS K-chunks of this CTA's half of the weight block (N/2 rows each).
-constexpr int job_stages(int j) { return (job_kcb(j) + kCPS - 1) / kCPS; }
-constexpr int stage_chunks(int j, int k) { return (job_kcb(j) - k * kCPS) < kCPS ? (job_kcb(j) - k * kCPS) : kCPS; }
-constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
-  int n = 0;
-  for (int i = 0; i < j; ++i) n += 2 * job_stages(i);
-  return n + t * job_stages(j);
-}
-
-struct ProdState {
-  uint32_t use[2][kStages];   // parity of the number of fills so far per (slot, stage)
-  int last[kStages];          // slot that used the stage last (-1: never)
-};
-
-// tensor-map TMA load of `rows` x 128 bytes starting at row y of the weight image; completion (bytes) is signalled on
-// `mbar`, a shared::cluster address that may belong to the peer (leader) CTA
-__device__ __forceinline__ void tma_load_rows(uint32_t dst_smem, const CUtensorMap* map, uint32_t y, uint32_t mbar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst_smem),
-      "l"(reinterpret_cast<uint64_t>(map)), "r"(0u), "r"(y), "r"(mbar)
-      : "memory");
-}
-
-template <int J>
-__device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
-                                            const bool (&has)[2]) {
-  constexpr uint32_t cb = job_half_chunk(J);
-  const uint32_t src = job_off(J) + rank * job_half_bytes(J);   // byte offset in the weight image
-#pragma unroll
-  for (int t = 0; t < 2; ++t) {
-    if (!has[t]) continue;
-#pragma unroll
-    for (int k = 0; k < job_stages(J); ++k) {
-      constexpr uint32_t kFull = kCPS * cb;
-      const uint32_t off = k * kFull;
-      const uint32_t nb = static_cast<uint32_t>(stage_chunks(J, k)) * cb;
-      const int stage = (stage_prefix(J, t) + k) % kStages;
-      // the previous user of this stage (either slot) must have released it (multicast commit of the leader)
-      if (ps.last[stage] == 0) mbar_wait(bar0 + 8u * bar_empty_i(0, stage), ps.use[0][stage] ^ 1);
-      else if (ps.last[stage] == 1) mbar_wait(bar0 + 8u * bar_empty_i(1, stage), ps.use[1][stage] ^ 1);
-      ps.use[t][stage] ^= 1;
-      ps.last[stage] = t;
-      // both halves complete on the LEADER's full barrier; its producer expects the bytes of the pair
-      const uint32_t full = bar0 + 8u * bar_full_i(t, stage);
-      const int mi = nb == 16384 ? 0 : (nb == 4096 ? 1 : (nb == 8192 ? 2 : 3));
-      if (rank == 0) mbar_arrive_expect_tx(full, 2 * nb);
-      tma_load_rows(ring + stage * kStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0));
-    }
-  }
-}
-template <int... Js>
-__device__ __forceinline__ void produce_all(const WeightMaps& maps, uint32_t rank, uint32_t ring, uint32_t bar0, ProdState& ps,
-                                            const bool (&has)[2], std::integer_sequence<int, Js...>) {
-  (produce_job<Js>(maps, rank, ring, bar0, ps, has), ...);
-}
-
-// One ring stage as a single asm block: bounded wait for the weights of BOTH CTAs (the leader's full barrier counts
-// its own producer and the peer's relay; a protocol bug traps instead of hanging), NMMA x tcgen05.mma.cta_group::2
-// (K = 16 each) and the multicast commit that releases the stage in both CTAs.  MMA i < NMMA-1 reads A at
-// a_lo + i*256 (two chunks further), the last one at a_last; B advances by B_STEP descriptor units per MMA.
-#define DFN_STAGE_HEAD                                                        \
-  "{\n\t"                                                                     \
-  ".reg .pred q, p, pe;\n\t"                                                  \
-  ".reg .b32 cnt, al, bl;\n\t"                                                \
-  ".reg .b64 da, db;\n\t"                                                     \
-  "mov.u32 cnt, 0;\n\t"                                                       \
-  "SW_WAIT:\n\t"                                                              \
-  "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 q, [%0], %1;\n\t" \
-  "@q bra SW_GO;\n\t"                                                         \
-  "add.u32 cnt, cnt, 1;\n\t"                                                  \
-  "setp.lt.u32 p, cnt, 8000000;\n\t"                                          \
-  "@p bra SW_WAIT;\n\t"                                                       \
-  "trap;\n\t"                                                                 \
-  "SW_GO:\n\t"                                                                \
-  "tcgen05.fence::after_thread_sync;\n\t"                                     \
-  "elect.sync _|pe, 0xffffffff;\n\t"                                          \
-  "setp.ne.b32 p, %7, 0;\n\t"
-#define DFN_STAGE_FIRST                                         \
-  "mov.b64 da, {%3, %5};\n\t"                                   \
-  "mov.b64 db, {%4, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
-#define DFN_STAGE_NEXT(i)                                       \
-  "add.u32 al, %3, " #i "*256;\n\t"                             \
-  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
-  "mov.b64 da, {al, %5};\n\t"                                   \
-  "mov.b64 db, {bl, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
-#define DFN_STAGE_LAST(i)                                       \
-  "add.u32 bl, %4, " #i "*%10;\n\t"                             \
-  "mov.b64 da, {%9, %5};\n\t"                                   \
-  "mov.b64 db, {bl, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, 1;\n\t"
-#define DFN_STAGE_ONLY                                          \
-  "mov.b64 da, {%9, %5};\n\t"                                   \
-  "mov.b64 db, {%4, %5};\n\t"                                   \
-  "@pe tcgen05.mma.cta_group::2.kind::f16 [%2], da, db, %6, p;\n\t"
-#define DFN_COMMIT(b) \
-  "@pe tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [" b "], %12;\n\t"
-#define DFN_STAGE_TAIL DFN_COMMIT("%8") "}"
-// last stage of a job: the second commit tells the epilogues of both CTAs that the accumulator is complete
-#define DFN_STAGE_TAIL_ACC DFN_COMMIT("%8") DFN_COMMIT("%11") "}"
-#define DFN_STAGE_OPERANDS                                                                                     \
-  ::"r"(full_bar), "r"(parity), "r"(tacc), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc_first), "r"(empty_bar), \
-      "r"(a_last), "n"(B_STEP), "r"(acc_bar), "h"(static_cast<uint16_t>(3))                                       \
-      : "memory"
-
-// Executed by the whole (converged) issuer warp of the leader CTA.
-template <int NMMA, int B_STEP, bool ACC>
-__device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, uint32_t tacc, uint32_t a_lo, uint32_t a_last,
-                                          uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc_first, uint32_t empty_bar,
-                                          uint32_t acc_bar) {
-  static_assert(NMMA >= 1 && NMMA <= 4, "1..4 MMAs per stage");
-  if constexpr (ACC) {
-    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
-    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
-    else if constexpr (NMMA == 3)
-      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
-    else
-      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL_ACC
-                       DFN_STAGE_OPERANDS);
-  } else {
-    if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
-    else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
-    else if constexpr (NMMA == 3)
-      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
-    else
-      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL
-                       DFN_STAGE_OPERANDS);
-  }
-}
-
-struct SlotCtx {
-  uint32_t ph0, ph1, ph2;   // phases of this slot's full[stage] barriers (scalars: must stay in registers)
-  uint32_t pa;              // phase of this slot's aready barrier
-  bool has;                 // the slot has a tile in the current iteration
-};
-struct IssueCtx {
-  uint32_t sbase, bar0, tmem_base, rank;
-  SlotCtx s0, s1;
-  int lane;
-#ifdef DFN_FWD_STATS
-  long long w_full, w_aready;   // bring-up build (-DDFN_FWD_STATS): cycles the issuer waits for weights / for the epilogues
-#endif
-};
-template <int T>
-__device__ __forceinline__ SlotCtx& slot_of(IssueCtx& c) {
-  if constexpr (T == 0) return c.s0; else return c.s1;
-}
-template <int S>
-__device__ __forceinline__ uint32_t& ph_of(SlotCtx& c) {
-  if constexpr (S == 0) return c.ph0;
-  else if constexpr (S == 1) return c.ph1;
-  else return c.ph2;
-}
-
-// where chunk kc of job J's A operand lives (descriptor address units relative to the three bases)
-template <int J>
-__device__ __forceinline__ uint32_t a_chunk_lo(int kc, uint32_t a_act, uint32_t a_aux, uint32_t a_ones) {
-  constexpr int KC = job_kc(J), KC_ACT = job_kc_act(J);
-  if (kc >= KC) return a_ones + (kc - KC) * (kChunkBytes >> 4);
-  if (kc < KC_ACT) return a_act + kc * (kChunkBytes >> 4);
-  return a_aux + (kc - KC_ACT) * (kChunkBytes >> 4);
-}
-
-template <int J, int T, int K>
-__device__ __forceinline__ void issue_stage(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc) {
-  constexpr int N = job_N(J);
-  constexpr uint32_t idesc = instr_desc_bf16(256, N, 0, 0);   // M = 256 over the CTA pair
-  constexpr uint32_t cb = job_half_chunk(J);                  // bytes per K chunk of this CTA's half of B
-  constexpr uint32_t hi = desc_hi(128);
-  constexpr int B_STEP = 2 * (cb >> 4);                       // descriptor address units per MMA (two K chunks)
-  constexpr int kc0 = K * kCPS;
-  constexpr int stage = (stage_prefix(J, T) + K) % kStages;
-  constexpr int nchunk = stage_chunks(J, K);
-  constexpr bool last = K == job_stages(J) - 1;
-  static_assert(nchunk % 2 == 0, "a K=16 MMA consumes two chunks");
-  const uint32_t full = c.bar0 + 8u * bar_full_i(T, stage), empty = c.bar0 + 8u * bar_empty_i(T, stage);
-  uint32_t& ph = ph_of<stage>(slot_of<T>(c));
-  if (c.rank == 0) {
-#ifdef DFN_FWD_STATS
-    { const long long t0 = clock64(); mbar_wait_cluster(full, ph); c.w_full += clock64() - t0; }
-#endif
-    const uint32_t accfull = c.bar0 + 8u * bar_accfull_i(T);
-    const uint32_t b_lo = desc_lo(c.sbase + kOffRing + stage * kStageBytes, cb);
-    const uint32_t a_lo = a_chunk_lo<J>(kc0, a_act, a_aux, a_ones);
-    const uint32_t a_last = a_chunk_lo<J>(kc0 + nchunk - 2, a_act, a_aux, a_ones);
-    constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
-    stage_mma<nchunk / 2, B_STEP, last>(full, ph, tacc, a_lo, a_last, b_lo, hi, idesc, accf, empty, accfull);
-  }
-  ph ^= 1;
-}
-template <int J, int T, int... Ks>
-__device__ __forceinline__ void issue_stages(IssueCtx& c, uint32_t a_act, uint32_t a_aux, uint32_t a_ones, uint32_t tacc,
-                                             std::integer_sequence<int, Ks...>) {
-  (issue_stage<J, T, Ks>(c, a_act, a_aux, a_ones, tacc), ...);
-}
-
-// Runs on the whole warp 1 (converged) of both CTAs: issuer in the leader, relay in the peer.
-template <int J, int T>
-__device__ __forceinline__ void issue_job(IssueCtx& c) {
-  SlotCtx& sc = slot_of<T>(c);
-  if (!sc.has) return;
-  if (c.rank == 0) {   // the A operand of this job (both CTAs' tiles) has been published
-#ifdef DFN_FWD_STATS
-    const long long t0 = clock64();
-#endif
-    mbar_wait_cluster(c.bar0 + 8u * bar_aready_i(T), sc.pa);
-#ifdef DFN_FWD_STATS
-    c.w_aready += clock64() - t0;
-#endif
-    sc.pa ^= 1;
-    tc_fence_after();
-  }
-  const uint32_t a_act = desc_lo(c.sbase + kOffAct + T * kActBytes, kChunkBytes);
-  const uint32_t a_aux = desc_lo(c.sbase + kOffAux + T * kAuxBytes, kChunkBytes);
-  const uint32_t a_ones = desc_lo(c.sbase + kOffOnes, kChunkBytes);
-  const uint32_t tacc = c.tmem_base + T * 256;
-  issue_stages<J, T>(c, a_act, a_aux, a_ones, tacc, std::make_integer_sequence<int, job_stages(J)>{});
-}
-template <int... Js>
-__device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
-  ((issue_job<Js, 0>(c), issue_job<Js, 1>(c)), ...);
 }
 
 template <bool TRAIN>
@@ -428,19 +180,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
   if (warp == 0) {
     // ================= weight producer (this CTA's half of every block) =================
     if (lane == 0) {
-      ProdState ps;
+      ProdState<FwdPipe> ps;
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
       for (int it = 0; it < n_it; ++it) {
         const bool has[2] = {tile_of(it, 0, rank) < a.n_tiles, tile_of(it, 1, rank) < a.n_tiles};
-        produce_all(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumJobs>{});
+        produce_all<FwdPipe>(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumJobs>{});
       }
     }
   } else if (warp == 1) {
     // ================= leader: MMA issuer (whole warp, converged; one elected lane issues); peer: bookkeeping only =================
     IssueCtx c{};
     c.sbase = sbase; c.bar0 = bar0; c.tmem_base = tmem_base; c.lane = lane; c.rank = rank;
-    c.s0 = SlotCtx{0, 0, 0, 0, false};
+    c.s0 = SlotCtx{};
     c.s1 = c.s0;
 #ifdef DFN_FWD_STATS
     c.w_full = c.w_aready = 0;
@@ -449,7 +201,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     for (int it = 0; it < n_it; ++it) {
       c.s0.has = tile_of(it, 0, rank) < a.n_tiles;
       c.s1.has = tile_of(it, 1, rank) < a.n_tiles;
-      issue_all(c, std::make_integer_sequence<int, kNumJobs>{});
+      issue_all<FwdPipe>(c, std::make_integer_sequence<int, kNumJobs>{});
     }
 #ifdef DFN_FWD_STATS
     if (blockIdx.x == 0 && lane == 0)
@@ -541,7 +293,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               write_pe_row(nullptr, aux, row, hh, x, d);
             }
             publish(t);
-            if (TRAIN) stash_row<4>(st, c0, row, keep);
+            if (TRAIN) {
+              stash_row<4>(st, c0, row, keep);
+              if (j < 8)   // ReLU bit mask for the data-gradient kernel: 16 B per thread instead of re-reading the tile
+                st_global_v4(a.stash_m + ((static_cast<size_t>(j) * a.n_tiles + tile) << 12) + (hh * 128 + row) * 16, relu_bits16(keep),
+                             relu_bits16(keep + 16), relu_bits16(keep + 32), relu_bits16(keep + 48));
+            }
             if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
               if (hh == 1) part[(t * 128 + row) * 3] = sdot;
               named_bar_sync(1, kEpiThreads);
@@ -646,8 +403,10 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
       const int bi = idx - nf;
       int b = 0;
       while (b + 1 < kNumBwdJobs && static_cast<uint32_t>(bi) * 2u >= bjob_off(b + 1)) ++b;
-      const int e = bi - bjob_off(b) / 2;
-      const int kc = e / (256 * 8), i = (e / 8) % 256, o = kc * 8 + (e & 7);
+      const int e0 = bi - bjob_off(b) / 2;
+      const int half_elems = bjob_bytes(b) / 4;
+      const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half of W^T's N rows
+      const int kc = e / (128 * 8), i = r * 128 + (e / 8) % 128, o = kc * 8 + (e & 7);
       const int layer_of[kNumBwdJobs] = {10, 9, 7, 6, 5, 4, 3, 2, 1};
       bwd[bi] = __float2bfloat16_rn(param_w(params, layer_of[b], o, i));
     } else {
@@ -667,10 +426,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
 extern "C" long long dfn_mlp_fwd_pack_bytes(void) { return kFwdPackBytes; }
 extern "C" long long dfn_mlp_bwd_pack_bytes(void) { return kBwdPackBytes; }
 extern "C" long long dfn_mlp_consts_bytes(void) { return kConstBytes; }
-extern "C" long long dfn_mlp_stash_bytes(long long P) {
-  const long long nt = num_tiles(P);
-  return nt * (8LL * 65536 + 65536 + 32768);
-}
+extern "C" long long dfn_mlp_stash_bytes(long long P) { return stash_total_bytes(num_tiles(P)); }
 
 extern "C" int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream) {
   DFN_CHECK_ARG(params && fwd_pack && bwd_pack && consts, "mlp_pack_weights: null pointer");
@@ -689,30 +445,6 @@ static int check_source(const dfn_point_source* s, long long P, const char* who)
   return DFN_OK;
 }
 
-// tensor maps over the packed weight image (rebuilt per call: a few hundred ns of host time, no device work)
-static int make_weight_maps(const void* fwd_pack, WeightMaps* out) {
-  static PFN_cuTensorMapEncodeTiled encode = nullptr;
-  if (!encode) {
-    cudaDriverEntryPointQueryResult q;
-    void* fn = nullptr;
-    DFN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "mlp_forward(driver entry point)");
-    DFN_CHECK_ARG(fn && q == cudaDriverEntryPointSuccess, "mlp_forward: cuTensorMapEncodeTiled not available");
-    encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
-  }
-  const cuuint32_t rows[4] = {128, 32, 64, 48};
-  for (int i = 0; i < 4; ++i) {
-    const cuuint64_t gdim[2] = {128, kFwdPackBytes / 128};
-    const cuuint64_t gstride[1] = {128};
-    const cuuint32_t box[2] = {128, rows[i]};
-    const cuuint32_t estride[2] = {1, 1};
-    const CUresult r = encode(&out->m[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(fwd_pack), gdim, gstride, box, estride,
-                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DFN_CHECK_ARG(r == CUDA_SUCCESS, "mlp_forward: cuTensorMapEncodeTiled failed (%d)", static_cast<int>(r));
-  }
-  return DFN_OK;
-}
-
 extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
                                const float* noise, float* rgb, float* sigma, void* stash, void* stream) {
   if (int rc = check_source(src, P, "mlp_forward")) return rc;
@@ -725,11 +457,12 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   if (stash) {
     uint8_t* s = static_cast<uint8_t*>(stash);
     a.stash_h = s;
-    a.stash_f = s + 8LL * a.n_tiles * 65536;
-    a.stash_c = a.stash_f + 1LL * a.n_tiles * 65536;
+    a.stash_f = s + stash_off_feat(a.n_tiles);
+    a.stash_c = s + stash_off_c(a.n_tiles);
+    a.stash_m = s + stash_off_mask(a.n_tiles);
   }
   WeightMaps maps;
-  if (int rc = make_weight_maps(fwd_pack, &maps)) return rc;
+  if (int rc = make_weight_maps(fwd_pack, kFwdPackBytes, &maps)) return rc;
   // one CTA per SM, paired: grid = 2 * min(#SM / 2, #super-tiles)
   const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
   const int grid = 2 * pairs;

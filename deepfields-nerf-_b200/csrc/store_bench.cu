@@ -134,7 +134,8 @@ extern "C" int dfn_store_bench(int mode, int iters, int grid, void* buf, long lo
 
 // ---- cta_group::2 issue-rate probe: the leader of a CTA pair streams M=256 N=256 K=16 MMAs -----------------
 namespace {
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1) pair_mma_kernel(int iters, int N, long long* cycles) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) pair_mma_kernel(int iters, int N, long long* cycles, uint8_t* buf,
+                                                                                        long long n_tiles, int mode) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[2];
   __shared__ uint32_t tmem_ptr;
@@ -154,6 +155,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1) pair_mma_kern
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   tc_fence_after();
   const uint32_t tbase = *reinterpret_cast<volatile uint32_t*>(&tmem_ptr);
+  __shared__ volatile int mma_done;
+  if (threadIdx.x == 0) mma_done = 0;
+  __syncthreads();
+  if (warp >= 2 && (mode & 3)) {
+    // 8 warps of each CTA stream 64 KB tiles to global (mode bit 0) and / or read them back (bit 1) until the MMAs finish
+    const int row = (warp & 3) * 32 + lane, hh = (warp - 2) >> 2;
+    uint32_t acc = 0;
+    for (long long it = 0; !mma_done && !(rank == 1 && it >= 16LL * iters); ++it) {
+      const long long tile = (it * gridDim.x + blockIdx.x) % n_tiles;
+      uint8_t* dst = buf + (tile << 16);
+#pragma unroll
+      for (int g = 0; g < 16; ++g) {
+        uint4* p = reinterpret_cast<uint4*>(dst + (hh * 16 + g) * 2048 + row * 16);
+        if (mode & 2) { const uint4 v = *p; acc ^= v.x ^ v.y ^ v.z ^ v.w; }
+        if (mode & 1) *p = make_uint4(static_cast<uint32_t>(it), g, row, acc);
+      }
+    }
+    if (acc == 0x12345u) cycles[0] = 1;
+  }
   if (warp == 0 && rank == 0) {
     const uint32_t idesc = instr_desc_bf16(256, N, 0, 0);
     const uint32_t cb = (N / 2) * 16;   // bytes per K chunk of this CTA's half of B
@@ -182,6 +202,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1) pair_mma_kern
     if (pend[0]) mbar_wait(bar0, ph[0]);
     if (pend[1]) mbar_wait(bar0 + 8, ph[1]);
     if (lane == 0) cycles[blockIdx.x >> 1] = (clock64() - t0) / (iters * 16);
+    mma_done = 1;
   }
   tc_fence_before();
   __syncthreads();
@@ -190,11 +211,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64, 1) pair_mma_kern
 }
 }  // namespace
 
-extern "C" int dfn_pair_mma_bench(int iters, int N, int grid, long long* cycles_out, void* stream) {
+extern "C" int dfn_pair_mma_bench(int iters, int N, int grid, long long* cycles_out, void* buf, long long buf_bytes, int mode,
+                                  void* stream) {
   DFN_CHECK_ARG(cycles_out && iters > 0 && grid > 0 && grid % 2 == 0 && N >= 32 && N <= 256 && N % 32 == 0, "pair_mma_bench: bad args");
   const uint32_t smem = 65536 + 65536;
   DFN_CUDA(cudaFuncSetAttribute(pair_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "pair_mma_bench");
-  pair_mma_kernel<<<grid, 64, smem, static_cast<cudaStream_t>(stream)>>>(iters, N, cycles_out);
+  pair_mma_kernel<<<grid, 320, smem, static_cast<cudaStream_t>(stream)>>>(iters, N, cycles_out, static_cast<uint8_t*>(buf),
+                                                                          buf_bytes >> 16, mode);
   DFN_CHECK_LAUNCH("pair_mma_bench");
   return DFN_OK;
 }
