@@ -120,6 +120,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
       ProdState<BwdPipe> ps;
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
+      ps.pol = make_evict_last_policy();
       for (int it = 0; it < n_it; ++it) {
         const bool has[2] = {tile_of(it, 0, rank) < nt, tile_of(it, 1, rank) < nt};
         produce_all<BwdPipe>(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumBwdJobs>{});
@@ -151,6 +152,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
     const int row = q * 32 + lane;
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     uint32_t pf[2] = {0, 0};
+    const uint64_t pol = make_evict_first_policy();   // dz is written once and read once, much later
     const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
     // dZ tile written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one arrive per warp
     auto publish = [&](int t) {
@@ -197,7 +199,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
           o4[i] = pack_bf16x2(d0, d1) & relu_mask2(cw[i]);
         }
         *reinterpret_cast<uint4*>(act + off) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
-        st_global_v4(dzc0 + off, o4[0], o4[1], o4[2], o4[3]);
+        st_global_v4_hint(dzc0 + off, o4[0], o4[1], o4[2], o4[3], pol);
       }
     };
 
@@ -255,7 +257,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
               }
               const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
               if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;
-              st_global_v4(dst + off, o.x, o.y, o.z, o.w);
+              st_global_v4_hint(dst + off, o.x, o.y, o.z, o.w, pol);
             }
             if (cc < 3) tmem_ld_wait();
           }

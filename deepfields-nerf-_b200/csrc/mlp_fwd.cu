@@ -106,11 +106,11 @@ struct FwdArgs {
 // ---- epilogue helpers ------------------------------------------------------------------------------
 // the first NC packed 32-column groups of one row -> stash (global); a warp covers 512 contiguous bytes per chunk
 template <int NC>
-__device__ __forceinline__ void stash_row(uint8_t* stash, int col0, int row, const uint32_t (&keep)[64]) {
+__device__ __forceinline__ void stash_row(uint8_t* stash, int col0, int row, const uint32_t (&keep)[64], uint64_t pol) {
 #pragma unroll
   for (int g = 0; g < NC * 4; ++g) {
     const uint32_t off = static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16;
-    st_global_v4(stash + off, keep[g * 4], keep[g * 4 + 1], keep[g * 4 + 2], keep[g * 4 + 3]);
+    st_global_v4_hint(stash + off, keep[g * 4], keep[g * 4 + 1], keep[g * 4 + 2], keep[g * 4 + 3], pol);
   }
 }
 
@@ -183,6 +183,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
       ProdState<FwdPipe> ps;
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
+      ps.pol = make_evict_last_policy();
       for (int it = 0; it < n_it; ++it) {
         const bool has[2] = {tile_of(it, 0, rank) < a.n_tiles, tile_of(it, 1, rank) < a.n_tiles};
         produce_all<FwdPipe>(maps, rank, sbase + kOffRing, bar0, ps, has, std::make_integer_sequence<int, kNumJobs>{});
@@ -217,6 +218,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     float* part = reinterpret_cast<float*>(smem + kOffPart);
     uint32_t pf[2] = {0, 0};
+    const uint64_t pol = make_evict_first_policy();
     const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
 
     auto point_of = [&](int tile) {
@@ -294,10 +296,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
             }
             publish(t);
             if (TRAIN) {
-              stash_row<4>(st, c0, row, keep);
+              stash_row<4>(st, c0, row, keep, pol);
               if (j < 8)   // ReLU bit mask for the data-gradient kernel: 16 B per thread instead of re-reading the tile
-                st_global_v4(a.stash_m + ((static_cast<size_t>(j) * a.n_tiles + tile) << 12) + (hh * 128 + row) * 16, relu_bits16(keep),
-                             relu_bits16(keep + 16), relu_bits16(keep + 32), relu_bits16(keep + 48));
+                st_global_v4_hint(a.stash_m + ((static_cast<size_t>(j) * a.n_tiles + tile) << 12) + (hh * 128 + row) * 16, relu_bits16(keep),
+                                  relu_bits16(keep + 16), relu_bits16(keep + 32), relu_bits16(keep + 48), pol);
             }
             if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
               if (hh == 1) part[(t * 128 + row) * 3] = sdot;
@@ -340,7 +342,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               write_pe_row(aux, nullptr, row, hh, x, d);
               publish(t);   // (no publish after the slot's last tile: nobody waits for it)
             }
-            if (TRAIN) stash_row<2>(st, c0, row, keep);
+            if (TRAIN) stash_row<2>(st, c0, row, keep, pol);
             float* pr = part + (t * 128 + row) * 3;
             if (hh == 1) { pr[0] = r0; pr[1] = r1; pr[2] = r2; }
             named_bar_sync(1, kEpiThreads);

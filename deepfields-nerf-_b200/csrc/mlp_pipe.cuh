@@ -80,15 +80,16 @@ template <class PP> constexpr int stage_prefix(int j, int t) {  // ring uses bef
 template <class PP>
 struct ProdState {
   uint32_t use[2][PP::kStages];   // parity of the number of fills so far per (slot, stage)
+  uint64_t pol;               // L2 evict_last policy for the weight loads (the image is re-read by every tile)
   int last[PP::kStages];          // slot that used the stage last (-1: never)
 };
 
 // tensor-map TMA load of `rows` x 128 bytes starting at row y of the weight image; completion (bytes) is signalled on
 // `mbar`, a shared::cluster address that may belong to the peer (leader) CTA
-__device__ __forceinline__ void tma_load_rows(uint32_t dst_smem, const CUtensorMap* map, uint32_t y, uint32_t mbar) {
+__device__ __forceinline__ void tma_load_rows(uint32_t dst_smem, const CUtensorMap* map, uint32_t y, uint32_t mbar, uint64_t pol) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst_smem),
-      "l"(reinterpret_cast<uint64_t>(map)), "r"(0u), "r"(y), "r"(mbar)
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(0u), "r"(y), "r"(mbar), "l"(pol)
       : "memory");
 }
 
@@ -115,7 +116,7 @@ __device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t ran
       const uint32_t full = bar0 + 8u * PP::bar_full_i(t, stage);
       const int mi = nb == 16384 ? 0 : (nb == 4096 ? 1 : (nb == 8192 ? 2 : 3));
       if (rank == 0) mbar_arrive_expect_tx(full, 2 * nb);
-      tma_load_rows(ring + stage * kStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0));
+      tma_load_rows(ring + stage * kStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0), ps.pol);
     }
   }
 }
