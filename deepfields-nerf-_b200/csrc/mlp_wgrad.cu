@@ -156,18 +156,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
   if (warp == 0) {
     if (lane == 0) {  // ================= producer =================
       int si = 0, sd = 0; uint32_t pi = 0, pd = 0;
+      const uint64_t pol = make_evict_first_policy();   // stash and dz tiles are read exactly once here
       for (int tile = tile_begin; tile < tile_end; ++tile) {
         if (type != TYPE_PE) {
           mbar_wait(bar_in_empty(si), pi ^ 1);
           mbar_arrive_expect_tx(bar_in_full(si), kInBytes);
-          bulk_g2s(sbase + kOffIn + si * kInBytes, in_src(tile), 32768, bar_in_full(si));
-          bulk_g2s(sbase + kOffIn + si * kInBytes + 32768, in_src(tile) + 32768, 32768, bar_in_full(si));
+          bulk_g2s_hint(sbase + kOffIn + si * kInBytes, in_src(tile), 32768, bar_in_full(si), pol);
+          bulk_g2s_hint(sbase + kOffIn + si * kInBytes + 32768, in_src(tile) + 32768, 32768, bar_in_full(si), pol);
           if (++si == 2) { si = 0; pi ^= 1; }
         }
         for (int i = 0; i < n_dz; ++i) {
           mbar_wait(bar_dz_empty(sd), pd ^ 1);
           mbar_arrive_expect_tx(bar_dz_full(sd), kDzBytes);
-          bulk_g2s(sbase + kOffDz + sd * kDzBytes, dz_src(tile, i), kDzBytes, bar_dz_full(sd));
+          bulk_g2s_hint(sbase + kOffDz + sd * kDzBytes, dz_src(tile, i), kDzBytes, bar_dz_full(sd), pol);
           if (++sd == 2) { sd = 0; pd ^= 1; }
         }
       }
