@@ -98,7 +98,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
         mbar_init(bar0 + 8u * BwdPipe::bar_full_i(t, s), 1);    // leader only: expect_tx of both CTAs' halves
         mbar_init(bar0 + 8u * BwdPipe::bar_empty_i(t, s), 1);
       }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), 2 * kEpiWarps); }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); }   // + the peer's relay
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -153,13 +153,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     uint32_t pf[2] = {0, 0};
     const uint64_t pol = make_evict_first_policy();   // dz is written once and read once, much later
-    const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
     // dZ tile written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one arrive per warp
     auto publish = [&](int t) {
       tc_fence_before();
-      asm volatile("fence.proxy.async;" ::: "memory");
+      fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(aready_leader[t]);
+      if (lane == 0) mbar_arrive(bar_aready(t));   // own CTA's barrier; the peer's warp 1 relays it to the leader
     };
 
     // prologue of a tile: dZ_c0 -> act chunks 0..15 (+ dz scratch), small fp32 grads

@@ -155,7 +155,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
         mbar_init(bar0 + 8u * bar_full_i(t, s), 1);
         mbar_init(bar0 + 8u * bar_empty_i(t, s), 1);
       }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), 2 * kEpiWarps); }
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); }   // + the peer's relay
     fence_mbar_init();
   }
   if (warp == 1) {   // one warp per CTA allocates all 512 TMEM columns of the pair
@@ -219,7 +219,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     float* part = reinterpret_cast<float*>(smem + kOffPart);
     uint32_t pf[2] = {0, 0};
     const uint64_t pol = make_evict_first_policy();
-    const uint32_t aready_leader[2] = {map_to_cta(bar_aready(0), 0), map_to_cta(bar_aready(1), 0)};
 
     auto point_of = [&](int tile) {
       long long p = static_cast<long long>(tile) * kTile + row;
@@ -229,9 +228,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     // arrive per warp on the leader's barrier
     auto publish = [&](int t) {
       tc_fence_before();
-      asm volatile("fence.proxy.async;" ::: "memory");
+      fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(aready_leader[t]);
+      if (lane == 0) mbar_arrive(bar_aready(t));   // own CTA's barrier; the peer's warp 1 relays it to the leader
     };
     // initial PE for both slots
     for (int t = 0; t < 2; ++t) {

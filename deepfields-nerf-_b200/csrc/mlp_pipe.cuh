@@ -267,17 +267,27 @@ template <class PP, int J, int T>
 __device__ __forceinline__ void issue_job(IssueCtx& c) {
   SlotCtx& sc = slot_of<T>(c);
   if (!sc.has) return;
-  if (c.rank == 0) {   // the A operand of this job (both CTAs' tiles) has been published
+  const uint32_t aready = c.bar0 + 8u * PP::bar_aready_i(T);
+  if (c.rank == 0) {   // the A operand of this job has been published: 8 local epilogue warps + the peer's relay
 #ifdef DFN_FWD_STATS
     const long long t0 = clock64();
 #endif
-    mbar_wait_cluster(c.bar0 + 8u * PP::bar_aready_i(T), sc.pa);
+    mbar_wait_cluster(aready, sc.pa);
 #ifdef DFN_FWD_STATS
     c.w_aready += clock64() - t0;
 #endif
-    sc.pa ^= 1;
     tc_fence_after();
+  } else {
+    // peer: relay "my 8 epilogue warps have published their tile" to the leader.  The epilogue warps arrive on their
+    // OWN CTA's barrier (cheap CTA-scope release); the cluster-scope release is paid once, by a thread with no memory
+    // traffic of its own - issued from the epilogue warps it made every publish wait for their outstanding global stores.
+    if (c.lane == 0) {
+      mbar_wait(aready, sc.pa);
+      mbar_arrive_cluster(map_to_cta(aready, 0));
+    }
+    __syncwarp();
   }
+  sc.pa ^= 1;
   const typename PP::ABases ab = PP::bases(c.sbase, T);
   const uint32_t tacc = c.tmem_base + T * 256;
   issue_stages<PP, J, T>(c, ab, tacc, std::make_integer_sequence<int, job_stages<PP>(J)>{});
