@@ -47,6 +47,8 @@ static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 struct BwdPipe {
   static constexpr int kNumJobs = kNumBwdJobs;
   static constexpr int kStages = ::kStages;
+  static constexpr int kCPS = 8;                          // 16 KB per stage = 4 MMAs
+  static constexpr uint32_t kRingStageBytes = kStageBytes;
   static constexpr uint32_t kOffRing = ::kOffRing;
   static __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
   static __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }

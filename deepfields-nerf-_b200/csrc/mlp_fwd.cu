@@ -32,7 +32,11 @@ using namespace mlp;
 using namespace umma;
 using namespace mlp_pipe;
 
+// Ring: 3 stages x 16 KB = 8 K-chunks (4 MMAs) of this CTA's half of B per stage.  6 x 8 KB (2 MMAs per stage, finer
+// release) was measured 35 % slower: the issuer's per-stage cost (try_wait, fence, election, commits) is ~2 MMA times.
 constexpr int kStages = 3;
+constexpr int kFwdCPS = 8;
+constexpr uint32_t kFwdStageBytes = 16384;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epilogue warps
@@ -41,7 +45,7 @@ constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epil
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;            // 2 x 16 KB
 constexpr uint32_t kOffRing = kOffAux + 2 * kAuxBytes;           // kStages x 16 KB
-constexpr uint32_t kOffOnes = kOffRing + kStages * kStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
+constexpr uint32_t kOffOnes = kOffRing + kStages * kFwdStageBytes;  // 128 x 16 bf16, column 0 = 1 (bias operand)
 constexpr uint32_t kOnesBytes = 2 * kChunkBytes;
 constexpr uint32_t kOffConst = kOffOnes + kOnesBytes;
 // partial head dot products of the upper column half, [2 slots][128 rows][3] f32 (sigma uses [..][0];
@@ -63,6 +67,8 @@ static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 struct FwdPipe {
   static constexpr int kNumJobs = mlp::kNumJobs;
   static constexpr int kStages = ::kStages;
+  static constexpr int kCPS = kFwdCPS;
+  static constexpr uint32_t kRingStageBytes = kFwdStageBytes;
   static constexpr uint32_t kOffRing = ::kOffRing;
   static __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return ::bar_full_i(t, s); }
   static __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return ::bar_empty_i(t, s); }

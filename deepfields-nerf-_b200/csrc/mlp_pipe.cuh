@@ -1,7 +1,7 @@
 // The pipeline shared by the forward and data-gradient kernels (mlp_fwd.cu, mlp_bwd.cu): CTA pairs
 // (tcgen05 cta_group::2), a weight ring fed by tensor-map TMA loads, and the unrolled MMA issue path.
 // A kernel instantiates the templates with a policy class PP that provides
-//   kNumJobs, kStages, kOffRing, bar_full_i / bar_empty_i / bar_accfull_i / bar_aready_i      (shared memory map)
+//   kNumJobs, kStages, kCPS (K chunks per ring stage), kRingStageBytes, kOffRing, bar_full_i / bar_empty_i / bar_accfull_i / bar_aready_i      (shared memory map)
 //   job_N(j), job_chunks(j) (K chunks of 8, bias slice included), job_off(j), job_half_chunk(j), job_half_bytes(j)
 //   struct ABases, bases(sbase, slot), a_chunk_lo<J>(kc, bases)                                  (where the A operand lives)
 #pragma once
@@ -14,11 +14,14 @@ namespace mlp_pipe {
 using namespace mlp;
 using namespace umma;
 
-constexpr int kCPS = 8;   // K chunks per ring stage (= 4 MMAs); 16 KB (N=256) or 8 KB (N=128) per CTA
 
 // The packed weight image seen as a 2-D byte tensor [bytes/128][128]; one map per box height (= stage size / 128):
 // 128 rows = 16 KB (a full N=256 stage), 32 rows = the 2-chunk tail stage, 64 / 48 rows = the N=128 job's stages.
-struct WeightMaps { CUtensorMap m[4]; };
+struct WeightMaps { CUtensorMap m[6]; };
+constexpr unsigned kMapRows[6] = {128, 64, 48, 32, 16, 8};   // box heights (x 128 bytes) a ring stage can have
+__host__ __device__ constexpr int map_index(uint32_t stage_bytes) {
+  return stage_bytes == 16384 ? 0 : stage_bytes == 8192 ? 1 : stage_bytes == 6144 ? 2 : stage_bytes == 4096 ? 3 : stage_bytes == 2048 ? 4 : 5;
+}
 
 // ---- cluster helpers --------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -69,8 +72,8 @@ __device__ __forceinline__ int tile_of(int it, int t, int rank) {
 // (N = 256 executes in 128).  Everything below is therefore unrolled with static ring-stage indices, and a
 // whole stage (wait, MMAs, commit) is one asm block (tools/umma_bench.py measures both forms).
 // A ring stage holds kCPS K-chunks of this CTA's half of the weight block (N/2 rows each).
-template <class PP> constexpr int job_stages(int j) { return (PP::job_chunks(j) + kCPS - 1) / kCPS; }
-template <class PP> constexpr int stage_chunks(int j, int k) { return (PP::job_chunks(j) - k * kCPS) < kCPS ? (PP::job_chunks(j) - k * kCPS) : kCPS; }
+template <class PP> constexpr int job_stages(int j) { return (PP::job_chunks(j) + PP::kCPS - 1) / PP::kCPS; }
+template <class PP> constexpr int stage_chunks(int j, int k) { return (PP::job_chunks(j) - k * PP::kCPS) < PP::kCPS ? (PP::job_chunks(j) - k * PP::kCPS) : PP::kCPS; }
 template <class PP> constexpr int stage_prefix(int j, int t) {  // ring uses before (job j, slot t) within one iteration
   int n = 0;
   for (int i = 0; i < j; ++i) n += 2 * job_stages<PP>(i);
@@ -103,7 +106,7 @@ __device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t ran
     if (!has[t]) continue;
 #pragma unroll
     for (int k = 0; k < job_stages<PP>(J); ++k) {
-      constexpr uint32_t kFull = kCPS * cb;
+      constexpr uint32_t kFull = PP::kCPS * cb;
       const uint32_t off = k * kFull;
       const uint32_t nb = static_cast<uint32_t>(stage_chunks<PP>(J, k)) * cb;
       const int stage = (stage_prefix<PP>(J, t) + k) % PP::kStages;
@@ -114,9 +117,9 @@ __device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t ran
       ps.last[stage] = t;
       // both halves complete on the LEADER's full barrier; its producer expects the bytes of the pair
       const uint32_t full = bar0 + 8u * PP::bar_full_i(t, stage);
-      const int mi = nb == 16384 ? 0 : (nb == 4096 ? 1 : (nb == 8192 ? 2 : 3));
+      const int mi = map_index(nb);
       if (rank == 0) mbar_arrive_expect_tx(full, 2 * nb);
-      tma_load_rows(ring + stage * kStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0), ps.pol);
+      tma_load_rows(ring + stage * PP::kRingStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0), ps.pol);
     }
   }
 }
@@ -236,7 +239,7 @@ __device__ __forceinline__ void issue_stage(IssueCtx& c, const typename PP::ABas
   constexpr uint32_t cb = PP::job_half_chunk(J);              // bytes per K chunk of this CTA's half of B
   constexpr uint32_t hi = desc_hi(128);
   constexpr int B_STEP = 2 * (cb >> 4);                       // descriptor address units per MMA (two K chunks)
-  constexpr int kc0 = K * kCPS;
+  constexpr int kc0 = K * PP::kCPS;
   constexpr int stage = (stage_prefix<PP>(J, T) + K) % PP::kStages;
   constexpr int nchunk = stage_chunks<PP>(J, K);
   constexpr bool last = K == job_stages<PP>(J) - 1;
@@ -248,7 +251,7 @@ __device__ __forceinline__ void issue_stage(IssueCtx& c, const typename PP::ABas
     { const long long t0 = clock64(); mbar_wait_cluster(full, ph); c.w_full += clock64() - t0; }
 #endif
     const uint32_t accfull = c.bar0 + 8u * PP::bar_accfull_i(T);
-    const uint32_t b_lo = desc_lo(c.sbase + PP::kOffRing + stage * kStageBytes, cb);
+    const uint32_t b_lo = desc_lo(c.sbase + PP::kOffRing + stage * PP::kRingStageBytes, cb);
     const uint32_t a_lo = PP::template a_chunk_lo<J>(kc0, ab);
     const uint32_t a_last = PP::template a_chunk_lo<J>(kc0 + nchunk - 2, ab);
     constexpr uint32_t accf = kc0 > 0 ? 1u : 0u;
@@ -307,11 +310,10 @@ static inline int make_weight_maps(const void* image, unsigned long long image_b
     DFN_CHECK_ARG(fn && q == cudaDriverEntryPointSuccess, "mlp: cuTensorMapEncodeTiled not available");
     encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
   }
-  const cuuint32_t rows[4] = {128, 32, 64, 48};
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < 6; ++i) {
     const cuuint64_t gdim[2] = {128, image_bytes / 128};
     const cuuint64_t gstride[1] = {128};
-    const cuuint32_t box[2] = {128, rows[i]};
+    const cuuint32_t box[2] = {128, kMapRows[i]};
     const cuuint32_t estride[2] = {1, 1};
     const CUresult r = encode(&out->m[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(image), gdim, gstride, box, estride,
                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
