@@ -28,7 +28,8 @@ using namespace mlp;
 using namespace umma;
 using namespace mlp_pipe;
 
-constexpr int kStages = 6;
+constexpr int kStages = 3;
+constexpr uint32_t kBwdStageBytes = 32768;   // 16 K-chunks = 8 MMAs of this CTA's half of W^T per stage
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
@@ -36,7 +37,7 @@ constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue war
 // shared memory map (bytes), identical in both CTAs of a pair
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB (dZ tiles = A operands)
 constexpr uint32_t kOffRing = kOffAct + 2 * kActBytes;           // kStages x 16 KB
-constexpr uint32_t kOffConst = kOffRing + kStages * kStageBytes;
+constexpr uint32_t kOffConst = kOffRing + kStages * kBwdStageBytes;
 constexpr uint32_t kOffBars = kOffConst + kConstBytes;
 constexpr uint32_t kNumBars = 4 * kStages + 4;
 constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
@@ -47,8 +48,8 @@ static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 struct BwdPipe {
   static constexpr int kNumJobs = kNumBwdJobs;
   static constexpr int kStages = ::kStages;
-  static constexpr int kCPS = 8;                          // 16 KB per stage = 4 MMAs
-  static constexpr uint32_t kRingStageBytes = kStageBytes;
+  static constexpr int kCPS = 16;
+  static constexpr uint32_t kRingStageBytes = kBwdStageBytes;
   static constexpr uint32_t kOffRing = ::kOffRing;
   static __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
   static __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }

@@ -17,10 +17,10 @@ using namespace umma;
 
 // The packed weight image seen as a 2-D byte tensor [bytes/128][128]; one map per box height (= stage size / 128):
 // 128 rows = 16 KB (a full N=256 stage), 32 rows = the 2-chunk tail stage, 64 / 48 rows = the N=128 job's stages.
-struct WeightMaps { CUtensorMap m[6]; };
-constexpr unsigned kMapRows[6] = {128, 64, 48, 32, 16, 8};   // box heights (x 128 bytes) a ring stage can have
+struct WeightMaps { CUtensorMap m[7]; };
+constexpr unsigned kMapRows[7] = {128, 64, 48, 32, 16, 8, 256};   // box heights (x 128 bytes) a ring stage can have
 __host__ __device__ constexpr int map_index(uint32_t stage_bytes) {
-  return stage_bytes == 16384 ? 0 : stage_bytes == 8192 ? 1 : stage_bytes == 6144 ? 2 : stage_bytes == 4096 ? 3 : stage_bytes == 2048 ? 4 : 5;
+  return stage_bytes == 32768 ? 6 : stage_bytes == 16384 ? 0 : stage_bytes == 8192 ? 1 : stage_bytes == 6144 ? 2 : stage_bytes == 4096 ? 3 : stage_bytes == 2048 ? 4 : 5;
 }
 
 // ---- cluster helpers --------------------------------------------------------------------------------
@@ -184,12 +184,15 @@ template <int NMMA, int B_STEP, bool ACC>
 __device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, uint32_t tacc, uint32_t a_lo, uint32_t a_last,
                                           uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc_first, uint32_t empty_bar,
                                           uint32_t acc_bar) {
-  static_assert(NMMA >= 1 && NMMA <= 4, "1..4 MMAs per stage");
+  static_assert((NMMA >= 1 && NMMA <= 4) || NMMA == 8, "1..4 or 8 MMAs per stage");
   if constexpr (ACC) {
     if constexpr (NMMA == 1) asm volatile(DFN_STAGE_HEAD DFN_STAGE_ONLY DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
     else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
     else if constexpr (NMMA == 3)
       asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 8)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_NEXT(3) DFN_STAGE_NEXT(4) DFN_STAGE_NEXT(5)
+                       DFN_STAGE_NEXT(6) DFN_STAGE_LAST(7) DFN_STAGE_TAIL_ACC DFN_STAGE_OPERANDS);
     else
       asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL_ACC
                        DFN_STAGE_OPERANDS);
@@ -198,6 +201,9 @@ __device__ __forceinline__ void stage_mma(uint32_t full_bar, uint32_t parity, ui
     else if constexpr (NMMA == 2) asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_LAST(1) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
     else if constexpr (NMMA == 3)
       asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_LAST(2) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
+    else if constexpr (NMMA == 8)
+      asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_NEXT(3) DFN_STAGE_NEXT(4) DFN_STAGE_NEXT(5)
+                       DFN_STAGE_NEXT(6) DFN_STAGE_LAST(7) DFN_STAGE_TAIL DFN_STAGE_OPERANDS);
     else
       asm volatile(DFN_STAGE_HEAD DFN_STAGE_FIRST DFN_STAGE_NEXT(1) DFN_STAGE_NEXT(2) DFN_STAGE_LAST(3) DFN_STAGE_TAIL
                        DFN_STAGE_OPERANDS);
@@ -310,7 +316,7 @@ static inline int make_weight_maps(const void* image, unsigned long long image_b
     DFN_CHECK_ARG(fn && q == cudaDriverEntryPointSuccess, "mlp: cuTensorMapEncodeTiled not available");
     encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
   }
-  for (int i = 0; i < 6; ++i) {
+  for (int i = 0; i < 7; ++i) {
     const cuuint64_t gdim[2] = {128, image_bytes / 128};
     const cuuint64_t gstride[1] = {128};
     const cuuint32_t box[2] = {128, kMapRows[i]};
