@@ -43,6 +43,12 @@ FLOP_DGRAD = 2 * 557696
 FLOP_WGRAD = 2 * 593408
 FLOP_PER_RAY_TRAIN = (S_COARSE + T_FINE) * (FLOP_FWD + FLOP_DGRAD + FLOP_WGRAD)
 STAGE_FLOP = {"mlp_fwd": FLOP_FWD, "dgrad": FLOP_DGRAD, "wgrad": FLOP_WGRAD}
+# algorithmic HBM bytes per MLP evaluation: stash = h1..h8 + features + colour hidden (bf16) + 8 bit
+# masks; dz = dZ1..dZ8 + dZ_feat + dZ_c0 + 16 B of head gradients.  fwd writes the stash (+16 B outputs); dgrad reads the masks,
+# the colour tile and 32 B of outputs/gradients and writes dz; wgrad reads stash tiles and dz once each.
+STASH_B, MASK_B, DZ_B = 4864, 256, 4880
+STAGE_BYTES = {"mlp_fwd": STASH_B + MASK_B + 16, "dgrad": MASK_B + 256 + 32 + DZ_B, "wgrad": STASH_B + DZ_B}
+STAGE_BOUND = {"mlp_fwd": "tensor", "dgrad": "tensor", "wgrad": "hbm"}   # what limits the kernel by design
 METRIC, UNIT = "train_rays_per_s", "rays/s"
 WORKLOAD = ("vanilla NeRF train step (model.py, PE L=10/4, hidden 256), 4096 rays/GPU x (64 stratified + 128 "
             "hierarchical) samples, coarse+fine nets, bf16 MLP, fp32 sampling/compositing/AdamW")
@@ -71,7 +77,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "50", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
             self.thr = threading.Thread(target=self._read, daemon=True)
             self.thr.start()
         except OSError:
@@ -271,20 +277,29 @@ def run_ours(args):
     dom = max(mlp, key=lambda k: mlp[k] * len(stages[k]))
     kind, net = dom.rsplit("_", 1)
     flop = STAGE_FLOP[kind] * pts[net]
-    achieved = flop / (mlp[dom] * 1e-3) / 1e12
+    nbytes = STAGE_BYTES[kind] * pts[net]
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as fh:
             traffic = json.load(fh).get(dom)
-    roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tensor_sustained"], "unit": "TFLOP/s",
-                "frac": achieved / pk["tensor_sustained"], "traffic": traffic, "peak_source": pk["src"] + ", sustained bf16",
-                "flop_per_launch": flop, "ms_per_launch": mlp[dom]}
+    if STAGE_BOUND[kind] == "tensor":
+        achieved = flop / (mlp[dom] * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tensor_sustained"], "unit": "TFLOP/s",
+                    "frac": achieved / pk["tensor_sustained"], "traffic": traffic,
+                    "peak_source": pk["src"] + ", sustained bf16", "flop_per_launch": flop, "ms_per_launch": mlp[dom]}
+    else:
+        achieved = nbytes / (mlp[dom] * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
+                    "frac": achieved / pk["hbm"], "traffic": traffic, "peak_source": pk["src"] + ", copy bandwidth",
+                    "bytes_per_launch": nbytes, "ms_per_launch": mlp[dom]}
     step_tflops = world * FLOP_PER_RAY_TRAIN * B_RAYS * K / (ms_total * 1e-3) / 1e12
     stage_report = {k: {"ms": round(mean[k], 4), "share": round(sum(stages[k]) / tot, 4)} for k in stages}
     for k in mlp:
         kk, nn = k.rsplit("_", 1)
         stage_report[k]["tflops"] = round(STAGE_FLOP[kk] * pts[nn] / (mean[k] * 1e-3) / 1e12, 1)
+        stage_report[k]["hbm_gbs"] = round(STAGE_BYTES[kk] * pts[nn] / (mean[k] * 1e-3) / 1e9, 0)
+        stage_report[k]["bound"] = STAGE_BOUND[kk]
 
     # ---- extract_vol 512^3 (BASELINE.json config 4), slab-sharded, reported beside the headline ---------------
     extract = None

@@ -91,6 +91,22 @@ def save_volume(occupancy, rgb_values, output_path, resolution, bounds, threshol
                 "rgb_volume": col.reshape(R, R, R, 3).cpu(), "metadata": meta}, output_path)
 
 
+def slab_range(resolution: int, rank: int, world: int):
+    """x-planes [x0, x1) owned by `rank`: x is the slowest index of the ij meshgrid
+    (extract_vol.py:74-77), so a slab is the contiguous flat range [x0*R*R, x1*R*R)."""
+    planes = (resolution + world - 1) // world
+    return min(rank * planes, resolution), min((rank + 1) * planes, resolution)
+
+
+def global_otsu(local_hist: torch.Tensor, lo: float, hi: float, group=None) -> float:
+    """Threshold every rank agrees on: the per-slab 256-bin histograms (all over the same global [lo,hi]) are summed
+    with one all-reduce and Otsu runs on the sum."""
+    hist = local_hist.clone()
+    if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+        torch.distributed.all_reduce(hist, group=group)
+    return otsu_from_histogram(hist, lo, hi)
+
+
 def extract_volume_fused(model: OptimizedVanillaNeRF, resolution: int, bounds=(-1.0, 1.0), view_direction=(0.0, 0.0, -1.0),
                          rank: int = 0, world: int = 1, group=None, out=None):
     """Slab-sharded dense query: rank r owns x-planes [r*R/G,(r+1)*R/G) == a contiguous range of
@@ -98,8 +114,7 @@ def extract_volume_fused(model: OptimizedVanillaNeRF, resolution: int, bounds=(-
     dev = next(model.parameters()).device
     model._sync_packed()
     R = resolution
-    planes = (R + world - 1) // world
-    x0, x1 = min(rank * planes, R), min((rank + 1) * planes, R)
+    x0, x1 = slab_range(R, rank, world)
     start, count = x0 * R * R, (x1 - x0) * R * R
     lin = torch.linspace(bounds[0], bounds[1], R, device=dev)
     view = torch.tensor(view_direction, dtype=torch.float32, device=dev)

@@ -293,6 +293,12 @@ class FusedTrainer:
         }, path)
 
 
+def shard_slice(batch_size: int, rank: int, world: int) -> slice:
+    """Rays of one global batch owned by `rank` (rank r takes rays [r*B/G, (r+1)*B/G))."""
+    per = batch_size // world
+    return slice(rank * per, (rank + 1) * per)
+
+
 class RayStore:
     """GPU-resident replacement for scripts/dataset.py + DataLoader: the whole .npz (keys rgbs, rays_o,
     rays_d, t_near, t_far; dataset.py:32-60) lives in HBM, batches are gathered with an on-device permutation."""
@@ -307,9 +313,9 @@ class RayStore:
 
     def batches(self, batch_size, generator=None):
         perm = torch.randperm(self.n, device=self.rgb.device, generator=generator)
-        per = batch_size // self.world
+        sl = shard_slice(batch_size, self.rank, self.world)
         for i in range(0, self.n - batch_size + 1, batch_size):
-            idx = perm[i + self.rank * per: i + (self.rank + 1) * per]
+            idx = perm[i:i + batch_size][sl]
             yield self.o[idx], self.d[idx], self.near[idx], self.far[idx], self.rgb[idx]
 
     def __len__(self):

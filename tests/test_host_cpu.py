@@ -29,7 +29,7 @@ def test_header_symbols_exported(D):
         assert name in D._lib.SIGNATURES, f"{name} has no ctypes signature"
     assert lib.dfn_abi_version() == 1
     assert lib.dfn_mlp_fwd_pack_bytes() == 1265664
-    assert lib.dfn_mlp_stash_bytes(129) == 2 * (9 * 65536 + 32768)
+    assert lib.dfn_mlp_stash_bytes(129) == 2 * (9 * 65536 + 32768 + 8 * 4096)  # 2 tiles: h1..h8, features, colour, bit masks
 
 
 def test_state_dict_layout_matches_reference(D, golden):

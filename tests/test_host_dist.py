@@ -1,0 +1,67 @@
+"""world_size-2 gloo tests (CPU) of the host-side multi-GPU logic: slab partition of the dense grid, the globally agreed
+Otsu threshold (min/max + histogram all-reduce), ray sharding of a global batch and the 1/G gradient
+averaging convention of the flat all-reduce."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import deepfields_nerf_b200 as D
+    from deepfields_nerf_b200 import extract_vol as X
+    from deepfields_nerf_b200.train import shard_slice
+    R = 10
+    g = torch.Generator().manual_seed(7)
+    sigma = torch.rand(R ** 3, generator=g) ** 3 * 40.0          # every rank builds the same full volume ...
+    x0, x1 = X.slab_range(R, rank, world)
+    mine = sigma[x0 * R * R: x1 * R * R]                          # ... and owns one slab of it
+    lo, hi = mine.min(), mine.max()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    hist = torch.histc(mine, bins=256, min=float(lo), max=float(hi)).to(torch.int64)
+    thr = X.global_otsu(hist, float(lo), float(hi))
+    # gradient averaging: SUM all-reduce of per-rank mean-loss gradients, scaled by 1/G, equals the global-mean gradient
+    B = 8
+    x = torch.arange(B, dtype=torch.float32)
+    sl = shard_slice(B, rank, world)
+    gsum = (2.0 * x[sl]).mean().reshape(1)                        # d/dw mean((w*x)^2)/... stand-in: per-rank mean
+    dist.all_reduce(gsum)
+    out[rank] = {"slab": (x0, x1), "thr": thr, "lo": float(lo), "hi": float(hi), "grad": float(gsum) / world,
+                 "rays": (sl.start, sl.stop)}
+    dist.destroy_process_group()
+
+
+def test_two_rank_host_logic():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, 29731, out), nprocs=world, join=True)
+    from deepfields_nerf_b200 import extract_vol as X
+    R = 10
+    assert out[0]["slab"] == (0, 5) and out[1]["slab"] == (5, 10)            # contiguous, disjoint, covering
+    assert out[0]["thr"] == out[1]["thr"]                                     # every rank derives the same threshold
+    g = torch.Generator().manual_seed(7)
+    sigma = torch.rand(R ** 3, generator=g) ** 3 * 40.0
+    assert out[0]["lo"] == float(sigma.min()) and out[0]["hi"] == float(sigma.max())
+    hist = torch.histc(sigma, bins=256, min=float(sigma.min()), max=float(sigma.max())).to(torch.int64)
+    assert out[0]["thr"] == X.otsu_from_histogram(hist, float(sigma.min()), float(sigma.max()))   # == single process
+    assert out[0]["rays"] == (0, 4) and out[1]["rays"] == (4, 8)
+    assert out[0]["grad"] == pytest.approx(float((2.0 * torch.arange(8.0)).mean()))
+
+
+def test_slab_ranges_cover_ragged_resolutions():
+    from deepfields_nerf_b200 import extract_vol as X
+    for R in (1, 7, 12, 512):
+        for world in (1, 2, 3, 8):
+            edges = [X.slab_range(R, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == R
+            assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
