@@ -72,6 +72,7 @@ __device__ __forceinline__ void st_global_v4(void* p, uint32_t a, uint32_t b, ui
 }
 // the same with an L2 eviction-priority hint (policy from make_evict_first_policy): write-once streams (activation
 // stash, dz scratch) should not displace the weight images the same kernel keeps re-reading from L2
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ uint64_t make_evict_first_policy() {
   uint64_t pol;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));

@@ -32,14 +32,15 @@ constexpr int kStages = 3;
 constexpr uint32_t kBwdStageBytes = 32768;   // 16 K-chunks = 8 MMAs of this CTA's half of W^T per stage
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer, 8 epilogue warps
+constexpr int kStoreWarp = 2 + kEpiWarps;     // ships published dZ tiles to the dz scratch (bulk shared -> global)
+constexpr int kThreads = 64 + kEpiThreads + 32;   // producer, issuer, 8 epilogue warps, dz store warp
 
 // shared memory map (bytes), identical in both CTAs of a pair
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB (dZ tiles = A operands)
 constexpr uint32_t kOffRing = kOffAct + 2 * kActBytes;           // kStages x 16 KB
 constexpr uint32_t kOffConst = kOffRing + kStages * kBwdStageBytes;
 constexpr uint32_t kOffBars = kOffConst + kConstBytes;
-constexpr uint32_t kNumBars = 4 * kStages + 4;
+constexpr uint32_t kNumBars = 4 * kStages + 6;
 constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
@@ -93,6 +94,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
   const uint32_t bar0 = sbase + kOffBars;
   auto bar_accfull = [&](int t) { return bar0 + 8u * BwdPipe::bar_accfull_i(t); };
   auto bar_aready = [&](int t) { return bar0 + 8u * BwdPipe::bar_aready_i(t); };
+  auto bar_stored = [&](int t) { return bar0 + 8u * (4 * kStages + 4 + t); };   // dZ tile of slot t may be overwritten
   float* consts = reinterpret_cast<float*>(smem + kOffConst);
 
   if (threadIdx.x == 0) {
@@ -101,7 +103,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
         mbar_init(bar0 + 8u * BwdPipe::bar_full_i(t, s), 1);    // leader only: expect_tx of both CTAs' halves
         mbar_init(bar0 + 8u * BwdPipe::bar_empty_i(t, s), 1);
       }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); }   // + the peer's relay
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); mbar_init(bar_stored(t), 1); }   // aready: + the peer's relay
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -149,12 +151,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
       printf("dgrad stats (leader of pair 0, cycles): issuer total %lld wait_aready %lld wait_weights %lld\n", clock64() - t_start,
              c.w_aready, c.w_full);
 #endif
+  } else if (warp == kStoreWarp) {
+    // ---- dz store (one thread): the dZ tile an epilogue publishes for the next job is exactly the tile the weight-gradient
+    // kernel reads later (same chunk layout), so it leaves the SM as one 64 KB bulk copy and the epilogue warps never stall
+    // on the store path.  `stored` tells them the tile may be overwritten; one arrive per (job, slot) keeps the aready
+    // phases this thread has to observe in lockstep with the epilogues.
+    if (lane == 0) {
+      uint32_t pa[2] = {0, 0};
+      const uint64_t pol = make_evict_first_policy();   // dz is written once and read once, much later
+      for (int it = 0; it < n_it; ++it)
+        for (int b = 0; b < kNumBwdJobs; ++b)
+          for (int t = 0; t < 2; ++t) {
+            const int tile = tile_of(it, t, rank);
+            if (tile >= nt) continue;
+            mbar_wait(bar_aready(t), pa[t]);   // A operand of job b: dZ_c0 (b = 0, stored by the prologue itself) or job b-1's output
+            pa[t] ^= 1;
+            if (b >= 1) {
+              uint8_t* dst = b == 1 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(9 - b, nt, tile);
+              bulk_s2g_hint(dst, sbase + kOffAct + t * kActBytes, kActBytes, pol);
+              bulk_commit();
+              bulk_wait_read_all();
+            }
+            mbar_arrive(bar_stored(t));
+          }
+      bulk_wait_all();
+    }
   } else {
     // ---- epilogue warps
     const int ew = warp - 2, q = warp & 3, hh = ew >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
-    uint32_t pf[2] = {0, 0};
+    uint32_t pf[2] = {0, 0}, pst[2] = {0, 0};
     const uint64_t pol = make_evict_first_policy();   // dz is written once and read once, much later
     // dZ tile written -> visible to the async proxy (the leader's MMA reads both CTAs' tiles) -> one arrive per warp
     auto publish = [&](int t) {
@@ -165,7 +192,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
     };
 
     // prologue of a tile: dZ_c0 -> act chunks 0..15 (+ dz scratch), small fp32 grads
-    auto prologue = [&](int t, int tile) {
+    auto prologue = [&](int t, int tile) -> float {
       uint8_t* act = smem + kOffAct + t * kActBytes;
       const long long p = static_cast<long long>(tile) * kTile + row;
       const bool valid = p < a.P;
@@ -203,14 +230,36 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
         *reinterpret_cast<uint4*>(act + off) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
         st_global_v4_hint(dzc0 + off, o4[0], o4[1], o4[2], o4[3], pol);
       }
+      return ds;
     };
+    // L2 prefetch of everything the prologue of `tile` will read (issued a few jobs ahead: its loads sit on the
+    // critical path between two tiles of a slot)
+    auto prefetch_prologue = [&](int tile) {
+      const long long p = static_cast<long long>(tile) * kTile + row;
+      const uint8_t* cst = a.stash + (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(tile) << 15);
+      if ((lane & 7) == 0) {
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) prefetch_l2(cst + (hh * 8 + ch) * kChunkBytes + row * 16);
+      }
+      if (hh == 0 && p < a.P && (lane & 3) == 0) {
+        prefetch_l2(a.rgb + p * 3);
+        prefetch_l2(a.d_rgb + p * 3);
+        if ((lane & 15) == 0) { prefetch_l2(a.sigma + p); prefetch_l2(a.d_sigma + p); }
+      }
+    };
+    float ds0 = 0.f, ds1 = 0.f;          // d sigma_pre of the slot's current tile (job 1 adds it into d h8)
+    uint4 mk_next = make_uint4(0, 0, 0, 0);   // ReLU bit mask for the NEXT epilogue in program order, loaded one epilogue ahead
 
     for (int t = 0; t < 2; ++t) {
       const int tile = tile_of(0, t, rank);
-      if (tile < nt) prologue(t, tile);
+      if (tile < nt) { const float ds = prologue(t, tile); if (t) ds1 = ds; else ds0 = ds; }
       publish(t);
     }
 
+#ifdef DFN_FWD_STATS
+    long long e_wait = 0, e_stored = 0;
+    const long long e_start = clock64();
+#endif
     for (int it = 0; it < n_it; ++it)
       for (int b = 0; b < kNumBwdJobs; ++b)
         for (int t = 0; t < 2; ++t) {
@@ -219,17 +268,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
           uint8_t* act = smem + kOffAct + t * kActBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
           const int c0 = hh * 128;
-          // ReLU mask of h_{l+1} (bit tile written by the forward, 16 B per thread) and dz destination
+          // ReLU mask of h_{l+1} (bit tile written by the forward, 16 B per thread): loaded during the previous epilogue;
+          // now fetch the one the next epilogue in program order needs - (b, slot 1) or (b+1, slot 0)
           const int l = 8 - b;  // b >= 1
-          uint4 mk = make_uint4(0, 0, 0, 0);
-          if (b >= 1)
-            mk = *reinterpret_cast<const uint4*>(a.stash + stash_off_mask(nt) + ((static_cast<size_t>(l) * nt + tile) << 12) +
-                                                 (hh * 128 + row) * 16);
+          const uint4 mk = mk_next;
+          {
+            const int tile1 = tile_of(it, 1, rank);
+            const bool other = t == 0 && tile1 < nt;
+            const int nb = other ? b : b + 1;
+            const int ntl = other ? tile1 : tile_of(it, 0, rank);
+            if (nb >= 1 && nb < kNumBwdJobs)
+              mk_next = *reinterpret_cast<const uint4*>(a.stash + stash_off_mask(nt) + ((static_cast<size_t>(8 - nb) * nt + ntl) << 12) +
+                                                        (hh * 128 + row) * 16);
+          }
           uint8_t* dst = b == 0 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(l, nt, tile);
-          float dsig = 0.f;
-          if (b == 1) dsig = reinterpret_cast<const float4*>(a.dz + dz_off_small(nt, tile))[row].w;
+          const float dsig = t ? ds1 : ds0;
+          if (b == 4) {
+            const int ntile = tile_of(it + 1, t, rank);
+            if (ntile < nt) prefetch_prologue(ntile);
+          }
+#ifdef DFN_FWD_STATS
+          const long long tw0 = clock64();
+#endif
           mbar_wait(bar_accfull(t), pf[t]); pf[t] ^= 1;
+#ifdef DFN_FWD_STATS
+          e_wait += clock64() - tw0;
+#endif
           tc_fence_after();
+#ifdef DFN_FWD_STATS
+          const long long ts0 = clock64();
+#endif
+          mbar_wait(bar_stored(t), pst[t]); pst[t] ^= 1;   // the store warp has read the previous dZ tile out of act
+#ifdef DFN_FWD_STATS
+          e_stored += clock64() - ts0;
+#endif
           uint32_t v0[32], v1[32];
           tmem_ld32(tacc + c0, v0);
           tmem_ld_wait();
@@ -258,18 +330,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
                 o.z &= relu_bits_expand(mw, g4 * 4 + 2); o.w &= relu_bits_expand(mw, g4 * 4 + 3);
               }
               const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
-              if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;
-              st_global_v4_hint(dst + off, o.x, o.y, o.z, o.w, pol);
+              if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;   // shipped to dz by the store warp
+              else st_global_v4_hint(dst + off, o.x, o.y, o.z, o.w, pol);          // last job: nobody reads it on chip
             }
             if (cc < 3) tmem_ld_wait();
           }
           if (b == kNumBwdJobs - 1) {
             const int ntile = tile_of(it + 1, t, rank);
-            if (ntile < nt) { prologue(t, ntile); publish(t); }
+            if (ntile < nt) { const float ds = prologue(t, ntile); if (t) ds1 = ds; else ds0 = ds; publish(t); }
           } else {
             publish(t);
           }
         }
+#ifdef DFN_FWD_STATS
+    if (blockIdx.x < 2 && ew == 0 && lane == 0)
+      printf("dgrad stats (CTA %d epilogue warp 0, cycles): total %lld wait_accfull %lld wait_stored %lld\n", blockIdx.x, clock64() - e_start, e_wait, e_stored);
+#endif
   }
 
   tc_fence_before();

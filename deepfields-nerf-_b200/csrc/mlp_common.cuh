@@ -126,7 +126,13 @@ __device__ __forceinline__ uint32_t relu_bits16(const uint32_t* pk) {
   return m;
 }
 // the 0xFFFF-per-half AND mask of packed pair i from such a word
-__device__ __forceinline__ uint32_t relu_bits_expand(uint32_t m, int i) { return ((m >> i) & 0x00010001u) * 0xFFFFu; }
+// (bit i -> bit 7, bit 16+i -> bit 23, then a byte permute in sign-replicate mode: 3 instructions with the AND)
+__device__ __forceinline__ uint32_t relu_bits_expand(uint32_t m, int i) {
+  const uint32_t t = i <= 7 ? m << (7 - i) : m >> (i - 7);
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %1, 0xAA88;" : "=r"(r) : "r"(t));
+  return r;
+}
 
 // how a tile's points are produced: the public dfn_point_source (include/deepfields_b200.h)
 using PointSource = dfn_point_source;
