@@ -11,6 +11,8 @@
 // column sums of tiles that are already in shared memory, done by the worker warps on the CUDA cores.
 // Operand tiles stream through shared memory rings with 1-D bulk async copies (TMA engine).
 #include "mlp_common.cuh"
+#include <stdio.h>
+#include <stdlib.h>
 
 namespace mlp {
 __host__ __device__ inline size_t dz_off_h(int l, int nt, int tile) { return (static_cast<size_t>(l) * nt + tile) << 16; }
@@ -34,7 +36,7 @@ constexpr uint32_t kOffDz = kOffIn + 2 * kInBytes;     // 2 x 32 KB
 constexpr uint32_t kOffPe = kOffDz + 2 * kDzBytes;     // 2 x 8 KB (dir-PE tiles, colour job)
 constexpr uint32_t kOffSmall = kOffPe + 2 * kPeBytes;  // 2 x [128][4] f32
 constexpr uint32_t kOffBars = kOffSmall + 2 * 2048;
-constexpr uint32_t kOffTmemPtr = kOffBars + 16 * 8;
+constexpr uint32_t kOffTmemPtr = kOffBars + 20 * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
 
@@ -97,8 +99,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
   const uint32_t bar0 = sbase + kOffBars;
   auto bar_in_full = [&](int s) { return bar0 + 8u * s; };
   auto bar_in_empty = [&](int s) { return bar0 + 8u * (2 + s); };
-  auto bar_dz_full = [&](int s) { return bar0 + 8u * (4 + s); };
-  auto bar_dz_empty = [&](int s) { return bar0 + 8u * (6 + s); };
+  auto bar_dz_full = [&](int s) { return bar0 + 8u * (s < 2 ? 4 + s : 11 + s); };    // stages 2, 3: barriers 13, 14
+  auto bar_dz_empty = [&](int s) { return bar0 + 8u * (s < 2 ? 6 + s : 13 + s); };   // stages 2, 3: barriers 15, 16
   auto bar_pe_full = [&](int s) { return bar0 + 8u * (8 + s); };
   auto bar_pe_empty = [&](int s) { return bar0 + 8u * (10 + s); };
   const uint32_t bar_done = bar0 + 8u * 12;
@@ -120,6 +122,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
   const int big_in = job < 7 ? big_layer - 1 : 7;  // stash_h index of the input activation
 
   if (threadIdx.x == 0) {
+    for (int s = 2; s < 4; ++s) { mbar_init(bar_dz_full(s), 1); mbar_init(bar_dz_empty(s), 1 + kWorkers); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_in_full(s), type == TYPE_PE ? kWorkThreads : 1);
       mbar_init(bar_in_empty(s), type == TYPE_PE ? 1 : 1 + kWorkers);
@@ -152,6 +155,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
                   : a.stash + (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(tile) << 15);  // c tile
   };
   const int n_dz = type == TYPE_PE ? 4 : 2;
+  // dz ring: two 32 KB stages; the PE unit's input tiles are computed, not loaded, and fill only 16 KB of each 64 KB
+  // input slot, so it parks two more dz stages there and keeps a whole tile (128 KB) of loads in flight
+  const int n_dzs = type == TYPE_PE ? 4 : 2;
+  auto dz_off = [&](int s) -> uint32_t { return s < 2 ? kOffDz + s * kDzBytes : kOffIn + (s - 2) * kInBytes + 16384u; };
 
   if (warp == 0) {
     if (lane == 0) {  // ================= producer =================
@@ -168,8 +175,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
         for (int i = 0; i < n_dz; ++i) {
           mbar_wait(bar_dz_empty(sd), pd ^ 1);
           mbar_arrive_expect_tx(bar_dz_full(sd), kDzBytes);
-          bulk_g2s_hint(sbase + kOffDz + sd * kDzBytes, dz_src(tile, i), kDzBytes, bar_dz_full(sd), pol);
-          if (++sd == 2) { sd = 0; pd ^= 1; }
+          bulk_g2s_hint(sbase + dz_off(sd), dz_src(tile, i), kDzBytes, bar_dz_full(sd), pol);
+          if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         }
       }
     }
@@ -192,32 +199,32 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
           for (int h = 0; h < 2; ++h) {
             mbar_wait(bar_dz_full(sd), pd);
             tc_fence_after();
-            mma_block(sbase + kOffDz + sd * kDzBytes, in_addr, h * 256, 256, first);
+            mma_block(sbase + dz_off(sd), in_addr, h * 256, 256, first);
             mma_commit(bar_dz_empty(sd));
-            if (++sd == 2) { sd = 0; pd ^= 1; }
+            if (++sd == n_dzs) { sd = 0; pd ^= 1; }
           }
         } else if (type == TYPE_PE) {
           for (int i = 0; i < 4; ++i) {
             mbar_wait(bar_dz_full(sd), pd);
             tc_fence_after();
-            mma_block(sbase + kOffDz + sd * kDzBytes, in_addr, i * 64, 64, first);
+            mma_block(sbase + dz_off(sd), in_addr, i * 64, 64, first);
             mma_commit(bar_dz_empty(sd));
-            if (++sd == 2) { sd = 0; pd ^= 1; }
+            if (++sd == n_dzs) { sd = 0; pd ^= 1; }
           }
         } else {
           mbar_wait(bar_dz_full(sd), pd);
           mbar_wait(bar_pe_full(sp), pp);
           tc_fence_after();
-          mma_block(sbase + kOffDz + sd * kDzBytes, in_addr, 0, 256, first);
-          mma_block(sbase + kOffDz + sd * kDzBytes, sbase + kOffPe + sp * kPeBytes, 256, 32, first);
+          mma_block(sbase + dz_off(sd), in_addr, 0, 256, first);
+          mma_block(sbase + dz_off(sd), sbase + kOffPe + sp * kPeBytes, 256, 32, first);
           mma_commit(bar_dz_empty(sd));
           mma_commit(bar_pe_empty(sp));
-          if (++sd == 2) { sd = 0; pd ^= 1; }
+          if (++sd == n_dzs) { sd = 0; pd ^= 1; }
           if (++sp == 2) { sp = 0; pp ^= 1; }
           // the c tile is consumed by the workers only: account for the MMA side of its empty barrier
           mbar_wait(bar_dz_full(sd), pd);
           mbar_arrive(bar_dz_empty(sd));
-          if (++sd == 2) { sd = 0; pd ^= 1; }
+          if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         }
         mma_commit(bar_in_empty(si));
         if (++si == 2) { si = 0; pi ^= 1; }
@@ -236,11 +243,31 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
     float* s_small = reinterpret_cast<float*>(smem + kOffSmall);
     const bool need_small = (type == TYPE_BIG && job == 7) || type == TYPE_COLOR;
 
-    for (int tile = tile_begin; tile < tile_end; ++tile) {
-      float* small = s_small + (tile & 1) * 512;
+    // global inputs of a tile (the small fp32 grads, the points whose encodings are recomputed) are fetched one tile
+    // ahead: their latency is otherwise paid once per tile, in series with the encoding and the column sums
+    static_assert(kWorkThreads == 256, "two small-grad floats per worker");
+    const bool need_point = type == TYPE_PE || type == TYPE_COLOR;
+    float gn[2] = {0.f, 0.f}, xn[3] = {0.f, 0.f, 0.f}, dn[3] = {0.f, 0.f, 0.f};
+    auto fetch_tile = [&](int tile) {
       if (need_small) {
         const float* g = reinterpret_cast<const float*>(a.dz + dz_off_small(nt, tile));
-        for (int i = wt; i < 512; i += kWorkThreads) small[i] = g[i];
+        gn[0] = g[wt]; gn[1] = g[wt + kWorkThreads];
+      }
+      if (need_point) {
+        long long p = static_cast<long long>(tile) * kTile + (wt & 127);
+        if (p >= a.P) p = a.P - 1;
+        load_point(a.src, p, xn, dn);
+      }
+    };
+    if (tile_begin < tile_end) fetch_tile(tile_begin);
+
+    for (int tile = tile_begin; tile < tile_end; ++tile) {
+      float* small = s_small + (tile & 1) * 512;
+      const float g0 = gn[0], g1 = gn[1];
+      const float x[3] = {xn[0], xn[1], xn[2]}, d[3] = {dn[0], dn[1], dn[2]};
+      if (tile + 1 < tile_end) fetch_tile(tile + 1);
+      if (need_small) {
+        small[wt] = g0; small[wt + kWorkThreads] = g1;
         named_bar_sync(2, kWorkThreads);
         if (wt < 128) {
           const float4 v = reinterpret_cast<const float4*>(small)[wt];
@@ -250,10 +277,6 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
       if (type == TYPE_PE || type == TYPE_COLOR) {
         // recompute the encodings of this tile's points (2 threads per row)
         const int row = wt & 127, hh = wt >> 7;
-        long long p = static_cast<long long>(tile) * kTile + row;
-        if (p >= a.P) p = a.P - 1;
-        float x[3], d[3];
-        load_point(a.src, p, x, d);
         if (type == TYPE_PE) {
           mbar_wait(bar_in_empty(si), pi ^ 1);
           write_pe_row(smem + kOffIn + si * kInBytes, nullptr, row, hh, x, d);
@@ -271,10 +294,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           mbar_wait(bar_dz_full(sd), pd);
-          wcolsum<16, 1>(smem + kOffDz + sd * kDzBytes, nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[h]), wt);
+          wcolsum<16, 1>(smem + dz_off(sd), nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[h]), wt);
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_dz_empty(sd));
-          if (++sd == 2) { sd = 0; pd ^= 1; }
+          if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         }
         mbar_wait(bar_in_full(si), pi);
         if (job == 7) {  // density_layer.weight grad: sum_p d sigma_pre[p] * h8[p,:]
@@ -291,22 +314,22 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           mbar_wait(bar_dz_full(sd), pd);
-          if (i < 2) wcolsum<16, 1>(smem + kOffDz + sd * kDzBytes, nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[i]), wt);
+          if (i < 2) wcolsum<16, 1>(smem + dz_off(sd), nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[i]), wt);
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_dz_empty(sd));
-          if (++sd == 2) { sd = 0; pd ^= 1; }
+          if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         }
       } else {
         mbar_wait(bar_dz_full(sd), pd);  // dZ_c0 -> color_layer.0.bias grad
-        wcolsum<16, 1>(smem + kOffDz + sd * kDzBytes, nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[0]), wt);
+        wcolsum<16, 1>(smem + dz_off(sd), nullptr, reinterpret_cast<float(&)[1][8]>(bias_acc[0]), wt);
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_dz_empty(sd));
-        if (++sd == 2) { sd = 0; pd ^= 1; }
+        if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         mbar_wait(bar_dz_full(sd), pd);  // c tile -> color_layer.2.weight grad (3 weighted column sums)
-        wcolsum<16, 3>(smem + kOffDz + sd * kDzBytes, small, extra, wt);
+        wcolsum<16, 3>(smem + dz_off(sd), small, extra, wt);
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_dz_empty(sd));
-        if (++sd == 2) { sd = 0; pd ^= 1; }
+        if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         mbar_wait(bar_in_full(si), pi);
         if (lane == 0) mbar_arrive(bar_in_empty(si));
       }
@@ -394,6 +417,14 @@ int dfn_launch_wgrad(const dfn_point_source* src, long long P, int n_tiles, cons
   if (per < n_tiles && rest > 0) { a.big_split = per; a.pe_split = per + rest / 2; a.col_split = per + (rest - rest / 2); }
   if (a.pe_split > n_tiles) a.pe_split = n_tiles;
   if (a.col_split > n_tiles) a.col_split = n_tiles;
+  // bring-up override of the split: DFN_WGRAD_SPLIT="big,pe,col"
+  static const char* split_env = getenv("DFN_WGRAD_SPLIT");
+  if (split_env) {
+    int b = 0, p = 0, c = 0;
+    if (sscanf(split_env, "%d,%d,%d", &b, &p, &c) == 3 && b > 0 && p > 0 && c > 0 && b <= n_tiles && p <= n_tiles && c <= n_tiles) {
+      a.big_split = b; a.pe_split = p; a.col_split = c;
+    }
+  }
   const int grid = 8 * a.big_split + a.pe_split + a.col_split;
   DFN_CUDA(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward");
   mlp_wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
