@@ -142,7 +142,8 @@ __device__ __forceinline__ void load_point(const PointSource& s, long long p, fl
 #pragma unroll
     for (int c = 0; c < 3; ++c) { x[c] = s.pos[p * 3 + c]; d[c] = s.view[p * 3 + c]; }
   } else if (s.mode == 1) {
-    const long long ray = p / s.S;
+    // (a 64-bit division costs ~100 instructions on the epilogue's critical path; indices almost always fit 32 bits)
+    const long long ray = (p >> 32) == 0 ? static_cast<long long>(static_cast<uint32_t>(p) / static_cast<uint32_t>(s.S)) : p / s.S;
     const float zz = s.z[p];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -152,7 +153,14 @@ __device__ __forceinline__ void load_point(const PointSource& s, long long p, fl
   } else {
     const long long g = s.p_offset + p;
     const long long RR = static_cast<long long>(s.R) * s.R;
-    x[0] = s.lin[g / RR]; x[1] = s.lin[(g / s.R) % s.R]; x[2] = s.lin[g % s.R];
+    if (((g | RR) >> 32) == 0) {
+      const uint32_t g32 = static_cast<uint32_t>(g), R32 = static_cast<uint32_t>(s.R);
+      const uint32_t i0 = g32 / static_cast<uint32_t>(RR), rem = g32 - i0 * static_cast<uint32_t>(RR);
+      const uint32_t i1 = rem / R32;
+      x[0] = s.lin[i0]; x[1] = s.lin[i1]; x[2] = s.lin[rem - i1 * R32];
+    } else {
+      x[0] = s.lin[g / RR]; x[1] = s.lin[(g / s.R) % s.R]; x[2] = s.lin[g % s.R];
+    }
 #pragma unroll
     for (int c = 0; c < 3; ++c) d[c] = s.view[c];
   }

@@ -265,6 +265,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
             else if (j == 8) st = a.stash_f + (static_cast<size_t>(tile) << 16);
             else st = a.stash_c + (static_cast<size_t>(tile) << 15);
           }
+          // global inputs of the encodings this epilogue writes (view direction at job 4, the slot's next tile at job 9)
+          // are fetched before waiting for the accumulator: their latency would otherwise sit between two jobs
+          float xe[3] = {0.f, 0.f, 0.f}, de[3] = {0.f, 0.f, 0.f};
+          const int ntile = tile_of(it + 1, t, rank);
+          if (j == 4) load_point(a.src, p < a.P ? p : a.P - 1, xe, de);
+          else if (j == kNumJobs - 1 && ntile < a.n_tiles) load_point(a.src, point_of(ntile), xe, de);
           mbar_wait(bar_accfull(t), pf[t]);
           pf[t] ^= 1;
           tc_fence_after();
@@ -294,12 +300,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               }
               if (cc < 3) tmem_ld_wait();
             }
-            if (j == 4) {  // pos-PE is dead once job 4's MMAs finished: overlay the dir-PE
-              float x[3], d[3];
-              load_point(a.src, p < a.P ? p : a.P - 1, x, d);
-              write_pe_row(nullptr, aux, row, hh, x, d);
-            }
             publish(t);
+            // pos-PE is dead once job 4's MMAs finished: overlay the dir-PE (job 9 reads it; the publish of job 5's
+            // epilogue orders it)
+            if (j == 4) write_pe_row(nullptr, aux, row, hh, xe, de);
             if (TRAIN) {
               stash_row<4>(st, c0, row, keep, pol);
               if (j < 8)   // ReLU bit mask for the data-gradient kernel: 16 B per thread instead of re-reading the tile
@@ -340,11 +344,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               }
             }
             // next tile of this slot: its pos-PE goes into aux (dir-PE was consumed by job 9's MMAs)
-            const int ntile = tile_of(it + 1, t, rank);
             if (ntile < a.n_tiles) {
-              float x[3], d[3];
-              load_point(a.src, point_of(ntile), x, d);
-              write_pe_row(aux, nullptr, row, hh, x, d);
+              write_pe_row(aux, nullptr, row, hh, xe, de);
               publish(t);   // (no publish after the slot's last tile: nobody waits for it)
             }
             if (TRAIN) stash_row<2>(st, c0, row, keep, pol);
