@@ -32,6 +32,9 @@ constexpr int kStages = 3;
 constexpr uint32_t kBwdStageBytes = 32768;   // 16 K-chunks = 8 MMAs of this CTA's half of W^T per stage
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
+#ifndef DFN_DZ_STORE_PIECES
+#define DFN_DZ_STORE_PIECES 1
+#endif
 constexpr int kStoreWarp = 2 + kEpiWarps;     // ships published dZ tiles to the dz scratch (bulk shared -> global)
 constexpr int kThreads = 64 + kEpiThreads + 32;   // producer, issuer, 8 epilogue warps, dz store warp
 
@@ -168,9 +171,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
             pa[t] ^= 1;
             if (b >= 1) {
               uint8_t* dst = b == 1 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(9 - b, nt, tile);
-              bulk_s2g_hint(dst, sbase + kOffAct + t * kActBytes, kActBytes, pol);
-              bulk_commit();
-              bulk_wait_read_all();
+              // (the forward ships its tiles in 8 KB pieces so as not to hold up the weight loads queued behind them; with
+              // this kernel's 96 KB ring one 64 KB copy measured faster: 1.01 ms vs 1.07 ms in 8 pieces)
+              constexpr uint32_t kPiece = kActBytes / DFN_DZ_STORE_PIECES;
+#pragma unroll 1
+              for (int i = 0; i < DFN_DZ_STORE_PIECES; ++i) {
+                bulk_s2g_hint(dst + i * kPiece, sbase + kOffAct + t * kActBytes + i * kPiece, kPiece, pol);
+                bulk_commit();
+                bulk_wait_read_all();
+              }
             }
             mbar_arrive(bar_stored(t));
           }

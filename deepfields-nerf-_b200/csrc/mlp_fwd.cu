@@ -39,7 +39,18 @@ constexpr int kFwdCPS = 8;
 constexpr uint32_t kFwdStageBytes = 16384;
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;   // producer, issuer / relay, 8 epilogue warps
+#ifndef DFN_FWD_STORE_WARP
+#define DFN_FWD_STORE_WARP 1
+#endif
+#ifndef DFN_STORE_PIECES
+#define DFN_STORE_PIECES 8
+#endif
+#ifndef DFN_STORE_GAP_NS
+#define DFN_STORE_GAP_NS -1
+#endif
+constexpr bool kUseStoreWarp = DFN_FWD_STORE_WARP != 0;
+constexpr int kStoreWarp = 2 + kEpiWarps;     // TRAIN: ships published activation tiles to the stash (bulk shared -> global)
+constexpr int kThreads = 64 + kEpiThreads + (kUseStoreWarp ? 32 : 0);   // producer, issuer / relay, 8 epilogue warps, stash store warp
 
 // shared memory map (bytes), identical in both CTAs of a pair (the MMA addresses the peer's tiles by the same offsets)
 constexpr uint32_t kOffAct = 0;                                  // 2 x 64 KB
@@ -54,11 +65,12 @@ constexpr uint32_t kOffPart = kOffConst + kConstBytes;
 constexpr uint32_t kOffBars = kOffPart + 2 * 128 * 3 * 4;
 // barriers: full[slot][stage], empty[slot][stage] (one set per slot: a parity wait can only tell adjacent phases
 // apart), accfull[slot], aready[slot] (leader only)
-constexpr uint32_t kNumBars = 4 * kStages + 4;
+constexpr uint32_t kNumBars = 4 * kStages + 6;
 __host__ __device__ constexpr uint32_t bar_full_i(int t, int s) { return t * kStages + s; }
 __host__ __device__ constexpr uint32_t bar_empty_i(int t, int s) { return 2 * kStages + t * kStages + s; }
 __host__ __device__ constexpr uint32_t bar_accfull_i(int t) { return 4 * kStages + t; }
 __host__ __device__ constexpr uint32_t bar_aready_i(int t) { return 4 * kStages + 2 + t; }
+__host__ __device__ constexpr uint32_t bar_stored_i(int t) { return 4 * kStages + 4 + t; }   // act tile of slot t may be overwritten
 constexpr uint32_t kOffTmemPtr = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemPtr + 16;
 static_assert(kSmemBytes <= 232448, "shared memory budget exceeded");
@@ -152,6 +164,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
   const uint32_t bar0 = sbase + kOffBars;
   auto bar_accfull = [&](int t) { return bar0 + 8u * bar_accfull_i(t); };
   auto bar_aready = [&](int t) { return bar0 + 8u * bar_aready_i(t); };
+  auto bar_stored = [&](int t) { return bar0 + 8u * bar_stored_i(t); };
   float* consts = reinterpret_cast<float*>(smem + kOffConst);
 
   if (threadIdx.x == 0) {
@@ -161,7 +174,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
         mbar_init(bar0 + 8u * bar_full_i(t, s), 1);
         mbar_init(bar0 + 8u * bar_empty_i(t, s), 1);
       }
-    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); }   // + the peer's relay
+    for (int t = 0; t < 2; ++t) { mbar_init(bar_accfull(t), 1); mbar_init(bar_aready(t), kEpiWarps + (rank == 0 ? 1 : 0)); mbar_init(bar_stored(t), 1); }   // aready: + the peer's relay
     fence_mbar_init();
   }
   if (warp == 1) {   // one warp per CTA allocates all 512 TMEM columns of the pair
@@ -215,6 +228,41 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
       printf("fwd stats (leader of pair 0, cycles): issuer total %lld wait_aready %lld wait_weights %lld\n", clock64() - t_start,
              c.w_aready, c.w_full);
 #endif
+  } else if (kUseStoreWarp && warp == kStoreWarp) {
+    // ================= TRAIN: stash store (one thread) =================
+    // The activation tile a job's epilogue publishes (h1..h8, features) is exactly the stash tile (same chunk layout), so
+    // it leaves the SM as bulk copies while the tensor cores read it; the epilogue warps issue no global stores for it.
+    // The copy goes out in 8 KB pieces, each after the previous one has been read out of shared memory: one 64 KB copy
+    // holds up the weight loads queued behind it in the TMA unit (measured: fine pass 1.18 ms vs 1.07 ms in pieces).
+    // `stored` tells the epilogues the tile may be overwritten; one arrive per (job, slot) keeps the aready phases
+    // this thread has to observe in lockstep with them.
+    if (TRAIN && lane == 0) {
+      uint32_t pa[2] = {0, 0};
+      const uint64_t pol = make_evict_first_policy();
+      for (int it = 0; it < n_it; ++it)
+        for (int j = 0; j < kNumJobs; ++j)
+          for (int t = 0; t < 2; ++t) {
+            const int tile = tile_of(it, t, rank);
+            if (tile >= a.n_tiles) continue;
+            mbar_wait(bar_aready(t), pa[t]);   // the A operand of job j: encodings (j = 0) or the output of job j-1
+            pa[t] ^= 1;
+            if (j >= 1) {
+              uint8_t* dst = j <= 8 ? a.stash_h + ((static_cast<size_t>(j - 1) * a.n_tiles + tile) << 16)
+                                    : a.stash_f + (static_cast<size_t>(tile) << 16);
+              constexpr uint32_t kPiece = kActBytes / DFN_STORE_PIECES;
+#pragma unroll 1
+              for (int i = 0; i < DFN_STORE_PIECES; ++i) {
+                bulk_s2g_hint(dst + i * kPiece, sbase + kOffAct + t * kActBytes + i * kPiece, kPiece, pol);
+                bulk_commit();
+                if (DFN_STORE_GAP_NS > 0 && i + 1 < DFN_STORE_PIECES) __nanosleep(DFN_STORE_GAP_NS);
+                if (DFN_STORE_GAP_NS < 0 && i + 1 < DFN_STORE_PIECES) bulk_wait_read_all();
+              }
+              bulk_wait_read_all();
+            }
+            mbar_arrive(bar_stored(t));
+          }
+      bulk_wait_all();
+    }
   } else {
     // ================= epilogue / PE warps =================
     const int ew = warp - 2;
@@ -223,7 +271,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     const int row = q * 32 + lane;  // row of the tile == TMEM lane
     const uint32_t lane_sel = static_cast<uint32_t>(q * 32) << 16;
     float* part = reinterpret_cast<float*>(smem + kOffPart);
-    uint32_t pf[2] = {0, 0};
+    uint32_t pf[2] = {0, 0}, pst[2] = {0, 0};
     const uint64_t pol = make_evict_first_policy();
 
     auto point_of = [&](int tile) {
@@ -274,6 +322,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
           mbar_wait(bar_accfull(t), pf[t]);
           pf[t] ^= 1;
           tc_fence_after();
+          if (TRAIN && kUseStoreWarp) { mbar_wait(bar_stored(t), pst[t]); pst[t] ^= 1; }   // the store warp has read the previous tile out of act
 
           if (j < 9) {
             float sdot = 0.f;
@@ -305,7 +354,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
             // epilogue orders it)
             if (j == 4) write_pe_row(nullptr, aux, row, hh, xe, de);
             if (TRAIN) {
-              stash_row<4>(st, c0, row, keep, pol);
+              if (!kUseStoreWarp) stash_row<4>(st, c0, row, keep, pol);
               if (j < 8)   // ReLU bit mask for the data-gradient kernel: 16 B per thread instead of re-reading the tile
                 st_global_v4_hint(a.stash_m + ((static_cast<size_t>(j) * a.n_tiles + tile) << 12) + (hh * 128 + row) * 16, relu_bits16(keep),
                                   relu_bits16(keep + 16), relu_bits16(keep + 32), relu_bits16(keep + 48), pol);
