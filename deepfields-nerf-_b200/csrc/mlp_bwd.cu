@@ -11,6 +11,7 @@
 // job's A operand and stored to the dz scratch (chunk layout) for the weight-gradient kernel.  ReLU masks come
 // from the bit tiles the forward wrote beside its activation stash (32 B per point and layer instead of 512 B).
 #include "mlp_pipe.cuh"
+#include <type_traits>
 
 namespace mlp {
 // dz scratch layout (per n_tiles): [8][nt][64K] dZ_1..dZ_8 | [nt][64K] dZ_f | [nt][32K] dZ_c0 | [nt][128][4] f32
@@ -30,7 +31,14 @@ using namespace mlp_pipe;
 
 constexpr int kStages = 3;
 constexpr uint32_t kBwdStageBytes = 32768;   // 16 K-chunks = 8 MMAs of this CTA's half of W^T per stage
-constexpr int kEpiWarps = 8;
+#ifndef DFN_DGRAD_EPI_WARPS
+#define DFN_DGRAD_EPI_WARPS 16
+#endif
+constexpr int kEpiWarps = DFN_DGRAD_EPI_WARPS;   // 4 TMEM lane quadrants x kColParts column parts
+constexpr int kColParts = kEpiWarps / 4;
+constexpr int kGroups = 8 / kColParts;           // 32-column groups per epilogue thread
+constexpr int kProChunks = 16 / kColParts;       // dZ_c0 chunks per thread in the prologue
+static_assert(kEpiWarps == 8 || kEpiWarps == 16, "epilogue warps");
 constexpr int kEpiThreads = kEpiWarps * 32;
 #ifndef DFN_DZ_STORE_PIECES
 #define DFN_DZ_STORE_PIECES 1
@@ -223,8 +231,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
       uint8_t* dzc0 = a.dz + dz_off_c0(nt, tile);
       const float* w2 = consts + kConstWc2;
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
-        const int chunk = hh * 8 + ch;
+      for (int ch = 0; ch < kProChunks; ++ch) {
+        const int chunk = hh * kProChunks + ch;
         const uint32_t off = chunk * kChunkBytes + row * 16;
         const uint4 cv = *reinterpret_cast<const uint4*>(cst + off);
         const uint32_t cw[4] = {cv.x, cv.y, cv.z, cv.w};
@@ -248,7 +256,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
       const uint8_t* cst = a.stash + (static_cast<size_t>(9) * nt << 16) + (static_cast<size_t>(tile) << 15);
       if ((lane & 7) == 0) {
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) prefetch_l2(cst + (hh * 8 + ch) * kChunkBytes + row * 16);
+        for (int ch = 0; ch < kProChunks; ++ch) prefetch_l2(cst + (hh * kProChunks + ch) * kChunkBytes + row * 16);
       }
       if (hh == 0 && p < a.P && (lane & 3) == 0) {
         prefetch_l2(a.rgb + p * 3);
@@ -257,7 +265,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
       }
     };
     float ds0 = 0.f, ds1 = 0.f;          // d sigma_pre of the slot's current tile (job 1 adds it into d h8)
-    uint4 mk_next = make_uint4(0, 0, 0, 0);   // ReLU bit mask for the NEXT epilogue in program order, loaded one epilogue ahead
+    uint32_t mk_next[kGroups];   // ReLU bit masks (one word per 32-column group) for the NEXT epilogue in program order
+#pragma unroll
+    for (int i = 0; i < kGroups; ++i) mk_next[i] = 0;
+    const int ec0 = hh * (256 / kColParts);   // first column this thread handles
+    auto load_mask = [&](const uint8_t* tile_masks) {
+      const uint8_t* pm = tile_masks + ((ec0 >> 7) * 128 + row) * 16 + ((ec0 & 127) >> 5) * 4;
+      if constexpr (kGroups == 4) {
+        const uint4 v = *reinterpret_cast<const uint4*>(pm);
+        mk_next[0] = v.x; mk_next[1] = v.y; mk_next[2] = v.z; mk_next[3] = v.w;
+      } else {
+        const uint2 v = *reinterpret_cast<const uint2*>(pm);
+        mk_next[0] = v.x; mk_next[1] = v.y;
+      }
+    };
 
     for (int t = 0; t < 2; ++t) {
       const int tile = tile_of(0, t, rank);
@@ -276,19 +297,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
           if (tile >= nt) continue;
           uint8_t* act = smem + kOffAct + t * kActBytes;
           const uint32_t tacc = tmem_base + t * 256 + lane_sel;
-          const int c0 = hh * 128;
+          const int c0 = ec0;
           // ReLU mask of h_{l+1} (bit tile written by the forward, 16 B per thread): loaded during the previous epilogue;
           // now fetch the one the next epilogue in program order needs - (b, slot 1) or (b+1, slot 0)
           const int l = 8 - b;  // b >= 1
-          const uint4 mk = mk_next;
+          uint32_t mk[kGroups];
+#pragma unroll
+          for (int i = 0; i < kGroups; ++i) mk[i] = mk_next[i];
           {
             const int tile1 = tile_of(it, 1, rank);
             const bool other = t == 0 && tile1 < nt;
             const int nb = other ? b : b + 1;
             const int ntl = other ? tile1 : tile_of(it, 0, rank);
             if (nb >= 1 && nb < kNumBwdJobs)
-              mk_next = *reinterpret_cast<const uint4*>(a.stash + stash_off_mask(nt) + ((static_cast<size_t>(8 - nb) * nt + ntl) << 12) +
-                                                        (hh * 128 + row) * 16);
+              load_mask(a.stash + stash_off_mask(nt) + ((static_cast<size_t>(8 - nb) * nt + ntl) << 12));
           }
           uint8_t* dst = b == 0 ? a.dz + dz_off_f(nt, tile) : a.dz + dz_off_h(l, nt, tile);
           const float dsig = t ? ds1 : ds0;
@@ -311,39 +333,49 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
 #ifdef DFN_FWD_STATS
           e_stored += clock64() - ts0;
 #endif
-          uint32_t v0[32], v1[32];
-          tmem_ld32(tacc + c0, v0);
-          tmem_ld_wait();
+          // drain the accumulator: one instantiation per kind of job so that nothing job-dependent is tested per group
+          //   0: b = 0 (no mask)   1: b = 1 (+ d sigma_pre * density weights, mask)   2: b = 2..7 (mask)   3: b = 8 (mask, to global)
+          auto drain = [&](auto kind_c) {
+            constexpr int KIND = decltype(kind_c)::value;
+            uint8_t* out_row = (KIND == 3 ? dst : act) + static_cast<uint32_t>(c0 / 8) * kChunkBytes + row * 16;
+            uint32_t v0[32], v1[32];
+            tmem_ld32(tacc + c0, v0);
+            tmem_ld_wait();
 #pragma unroll
-          for (int cc = 0; cc < 4; ++cc) {
-            uint32_t (&cur)[32] = (cc & 1) ? v1 : v0;
-            uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
-            const int col0 = c0 + cc * 32;
-            if (cc < 3) tmem_ld32(tacc + col0 + 32, nxt);
-            const uint32_t mw = cc == 0 ? mk.x : (cc == 1 ? mk.y : (cc == 2 ? mk.z : mk.w));
+            for (int cc = 0; cc < kGroups; ++cc) {
+              uint32_t (&cur)[32] = (cc & 1) ? v1 : v0;
+              uint32_t (&nxt)[32] = (cc & 1) ? v0 : v1;
+              const int col0 = c0 + cc * 32;
+              if (cc < kGroups - 1) tmem_ld32(tacc + col0 + 32, nxt);
+              const uint32_t mw = mk[cc];
 #pragma unroll
-            for (int g4 = 0; g4 < 4; ++g4) {
-              float x[8];
+              for (int g4 = 0; g4 < 4; ++g4) {
+                float x[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(cur[g4 * 8 + i]);
-              if (b == 1) {
-                const float* ws = consts + kConstWsig + col0 + g4 * 8;
+                for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(cur[g4 * 8 + i]);
+                if constexpr (KIND == 1) {
+                  const float* ws = consts + kConstWsig + col0 + g4 * 8;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) x[i] += dsig * ws[i];
+                  for (int i = 0; i < 8; ++i) x[i] += dsig * ws[i];
+                }
+                uint4 o;
+                o.x = pack_bf16x2(x[0], x[1]); o.y = pack_bf16x2(x[2], x[3]);
+                o.z = pack_bf16x2(x[4], x[5]); o.w = pack_bf16x2(x[6], x[7]);
+                if constexpr (KIND >= 1) {
+                  o.x &= relu_bits_expand(mw, g4 * 4); o.y &= relu_bits_expand(mw, g4 * 4 + 1);
+                  o.z &= relu_bits_expand(mw, g4 * 4 + 2); o.w &= relu_bits_expand(mw, g4 * 4 + 3);
+                }
+                uint8_t* po = out_row + (cc * 4 + g4) * kChunkBytes;
+                if constexpr (KIND < 3) *reinterpret_cast<uint4*>(po) = o;   // next job's A operand; shipped to dz by the store warp
+                else st_global_v4_hint(po, o.x, o.y, o.z, o.w, pol);         // last job: nobody reads it on chip
               }
-              uint4 o;
-              o.x = pack_bf16x2(x[0], x[1]); o.y = pack_bf16x2(x[2], x[3]);
-              o.z = pack_bf16x2(x[4], x[5]); o.w = pack_bf16x2(x[6], x[7]);
-              if (b >= 1) {
-                o.x &= relu_bits_expand(mw, g4 * 4); o.y &= relu_bits_expand(mw, g4 * 4 + 1);
-                o.z &= relu_bits_expand(mw, g4 * 4 + 2); o.w &= relu_bits_expand(mw, g4 * 4 + 3);
-              }
-              const uint32_t off = static_cast<uint32_t>(col0 / 8 + g4) * kChunkBytes + row * 16;
-              if (b < kNumBwdJobs - 1) *reinterpret_cast<uint4*>(act + off) = o;   // shipped to dz by the store warp
-              else st_global_v4_hint(dst + off, o.x, o.y, o.z, o.w, pol);          // last job: nobody reads it on chip
+              if (cc < kGroups - 1) tmem_ld_wait();
             }
-            if (cc < 3) tmem_ld_wait();
-          }
+          };
+          if (b == 0) drain(std::integral_constant<int, 0>{});
+          else if (b == 1) drain(std::integral_constant<int, 1>{});
+          else if (b < kNumBwdJobs - 1) drain(std::integral_constant<int, 2>{});
+          else drain(std::integral_constant<int, 3>{});
           if (b == kNumBwdJobs - 1) {
             const int ntile = tile_of(it + 1, t, rank);
             if (ntile < nt) { const float ds = prologue(t, ntile); if (t) ds1 = ds; else ds0 = ds; publish(t); }
