@@ -3,7 +3,7 @@ allocator) and launch on torch's current CUDA stream.  No op has a CPU path."""
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Tuple
+from typing import Dict, Optional, Tuple
 
 import torch
 
@@ -290,6 +290,80 @@ def pack_volume(sigma: Tensor, rgb: Tensor, thr: float) -> Tuple[Tensor, Tensor]
     col = torch.empty(n, 3, device=sigma.device, dtype=torch.uint8)
     _lib.call("dfn_pack_volume", sigma.data_ptr(), rgb.data_ptr(), n, float(thr), occ.data_ptr(), col.data_ptr(), _stream())
     return occ, col
+
+
+# ---- ray generation (scripts/precompute_rays.py) ---------------------------------------------------
+def _camera_args(K, poses, device):
+    import ctypes
+    import numpy as np
+    kinv = np.ascontiguousarray(np.linalg.inv(np.asarray(K, dtype=np.float64)))   # precompute_rays.py:80 (host, 3x3)
+    if kinv.shape != (3, 3):
+        raise ValueError("K must be 3x3")
+    poses = torch.as_tensor(np.asarray(poses, dtype=np.float64) if not isinstance(poses, Tensor) else poses)
+    poses = poses.to(device=device, dtype=torch.float64).contiguous()
+    if poses.dim() != 3 or tuple(poses.shape[1:]) != (4, 4):
+        raise ValueError("camera_poses must be [M,4,4]")
+    return kinv, kinv.ctypes.data_as(ctypes.c_void_p), poses
+
+
+def generate_rays(H: int, W: int, K, poses, colmap: bool = True, normalize: bool = True, device="cuda") -> Tuple[Tensor, Tensor]:
+    """get_rays: fp32 [M,H,W,3] origins and directions on the device."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("deepfields_nerf_b200: generate_rays needs a CUDA device (there is no CPU fallback)")
+    kinv, kptr, poses = _camera_args(K, poses, device)
+    M = poses.shape[0]
+    o = torch.empty(M, H, W, 3, device=device, dtype=torch.float32)
+    d = torch.empty_like(o)
+    with torch.cuda.device(device):
+        _lib.call("dfn_generate_rays", kptr, poses.data_ptr(), M, int(H), int(W), int(bool(colmap)), int(bool(normalize)),
+                  o.data_ptr(), d.data_ptr(), _stream())
+    return o, d
+
+
+def ray_cube_intersect(rays_o: Tensor, rays_d: Tensor, cube_min: float = -1.0, cube_max: float = 1.0):
+    rays_o, rays_d = _f32(rays_o.reshape(-1, 3), "ray_origins"), _f32(rays_d.reshape(-1, 3), "ray_directions")
+    n = rays_o.shape[0]
+    if rays_d.shape[0] != n:
+        raise ValueError("ray_origins and ray_directions differ in length")
+    hit = torch.empty(n, device=rays_o.device, dtype=torch.uint8)
+    t_near = torch.empty(n, device=rays_o.device, dtype=torch.float32)
+    t_far = torch.empty_like(t_near)
+    _lib.call("dfn_ray_cube_intersect", rays_o.data_ptr(), rays_d.data_ptr(), n, float(cube_min), float(cube_max), hit.data_ptr(),
+              t_near.data_ptr(), t_far.data_ptr(), _stream())
+    return hit.bool(), t_near, t_far
+
+
+def precompute_rays(H: int, W: int, K, poses, images: Optional[Tensor] = None, cube_min: float = -1.0, cube_max: float = 1.0,
+                    colmap: bool = True, normalize: bool = True, device="cuda") -> Dict[str, Tensor]:
+    """Generate + intersect + keep the hits in order (one pass over HBM); images = u8 [M,H,W,3] on the device or None."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("deepfields_nerf_b200: precompute_rays needs a CUDA device (there is no CPU fallback)")
+    kinv, kptr, poses = _camera_args(K, poses, device)
+    M = poses.shape[0]
+    n = M * int(H) * int(W)
+    if images is not None:
+        if images.dtype != torch.uint8 or images.numel() != n * 3:
+            raise ValueError("images must be uint8 [M,H,W,3]")
+        images = images.to(device).contiguous()
+    o = torch.empty(n, 3, device=device, dtype=torch.float32)
+    d = torch.empty_like(o)
+    rgb = torch.empty_like(o) if images is not None else None
+    t_near = torch.empty(n, device=device, dtype=torch.float32)
+    t_far = torch.empty_like(t_near)
+    count = torch.zeros(1, device=device, dtype=torch.int64)
+    ws = torch.empty(int(_lib.load().dfn_precompute_rays_workspace_bytes(n)), device=device, dtype=torch.uint8)
+    with torch.cuda.device(device):
+        _lib.call("dfn_precompute_rays", kptr, poses.data_ptr(), M, int(H), int(W), int(bool(colmap)), int(bool(normalize)),
+                  images.data_ptr() if images is not None else None, float(cube_min), float(cube_max), o.data_ptr(), d.data_ptr(),
+                  rgb.data_ptr() if rgb is not None else None, t_near.data_ptr(), t_far.data_ptr(), count.data_ptr(), ws.data_ptr(),
+                  _stream())
+    k = int(count.item())
+    out = {"rays_o": o[:k], "rays_d": d[:k], "t_near": t_near[:k], "t_far": t_far[:k]}
+    if rgb is not None:
+        out["rgbs"] = rgb[:k]
+    return out
 
 
 # ---- optimiser -------------------------------------------------------------------------------------

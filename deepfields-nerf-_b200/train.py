@@ -311,6 +311,16 @@ class RayStore:
         self.near, self.far = f("t_near").reshape(-1), f("t_far").reshape(-1)
         self.n, self.rank, self.world = self.rgb.shape[0], rank, world
 
+    @classmethod
+    def from_tensors(cls, rays, rank=0, world=1):
+        """Build the store from device tensors (precompute_rays.precompute_rays_on_device) instead of an .npz file."""
+        self = cls.__new__(cls)
+        f = lambda k: rays[k].float().contiguous()  # noqa: E731
+        self.rgb, self.o, self.d = f("rgbs"), f("rays_o"), f("rays_d")
+        self.near, self.far = f("t_near").reshape(-1), f("t_far").reshape(-1)
+        self.n, self.rank, self.world = self.rgb.shape[0], rank, world
+        return self
+
     def batches(self, batch_size, generator=None):
         perm = torch.randperm(self.n, device=self.rgb.device, generator=generator)
         sl = shard_slice(batch_size, self.rank, self.world)

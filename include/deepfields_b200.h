@@ -125,6 +125,24 @@ int dfn_histogram(const float* v, long long n, float lo, float hi, int nbins, un
 int dfn_pack_volume(const float* sigma, const float* rgb, long long n, float thr, unsigned char* occ, unsigned char* col,
                     void* stream);
 
+/* ---- ray generation in front of the path (scripts/precompute_rays.py) ---------------------------- */
+/* get_rays (precompute_rays.py:67-119): every pixel ray of M cameras in the flattened [M,H,W] order.  kinv = HOST pointer
+ * to the 9 doubles of inv(K) (row-major); poses = DEVICE [M][4][4] doubles (camera-to-world, row-major); colmap applies
+ * F = diag(1,-1,-1); fp64 arithmetic like the reference, fp32 results ([M*H*W,3] each). */
+int dfn_generate_rays(const double* kinv, const double* poses, int M, int H, int W, int colmap, int normalize,
+                      float* rays_o, float* rays_d, void* stream);
+/* ray_cube_intersection_numpy (precompute_rays.py:10-64) on fp32 rays: intersects [N] u8 (taken before t_near is
+ * clamped to 0), t_near, t_far [N]; numpy's NaN-propagating minimum / maximum. */
+int dfn_ray_cube_intersect(const float* rays_o, const float* rays_d, long long n_rays, float cube_min, float cube_max,
+                           unsigned char* intersects, float* t_near, float* t_far, void* stream);
+/* precompute_save_ray (precompute_rays.py:206-228) without the .npz round trip: generate, intersect, keep the hits in
+ * order.  images = DEVICE [M,H,W,3] u8 or null (then rgbs must be null); outputs sized for M*H*W rays; *count
+ * (device int64) receives the number kept; workspace of dfn_precompute_rays_workspace_bytes(M*H*W) bytes. */
+long long dfn_precompute_rays_workspace_bytes(long long n_rays);
+int dfn_precompute_rays(const double* kinv, const double* poses, int M, int H, int W, int colmap, int normalize,
+                        const unsigned char* images, float cube_min, float cube_max, float* rays_o, float* rays_d,
+                        float* rgbs, float* t_near, float* t_far, long long* count, void* workspace, void* stream);
+
 /* ---- optimiser (scripts/train.py:244-259, :321-322) ---------------------------------------------- */
 /* AdamW on a flat buffer; lr_table/beta1_table [table_len] hold the OneCycleLR schedule, *step_ptr (device int,
  * 0-based) selects the entry and is incremented. */

@@ -296,3 +296,56 @@ def adamw_step(p, g, m, v, step, lr, b1=0.9, b2=0.999, eps=1e-8, wd=1e-6):
     denom = (v.sqrt() / math.sqrt(bc2)) + eps
     p = p - (lr / bc1) * m / denom
     return p, m, v
+
+
+# ----------------------------------------------------------------------------------------------
+# (f4) ray generation + ray / cube intersection -- scripts/precompute_rays.py
+# (numpy like the reference: fp64 rays, fp32 intersection)
+# ----------------------------------------------------------------------------------------------
+def camera_rays(H: int, W: int, K, poses, colmap: bool = True, normalize: bool = True):
+    """All pixel rays of M cameras, fp64, shape [M,H,W,3] each.  precompute_rays.py:79-80 (axis flip, inverse
+    intrinsics), :81-87 (pixel grid, x fastest), :89-92 (back-projection, flip), :94-98 (unit length, norm clipped
+    at 1e-8), :103-119 (rotate into the world, origin = camera position)."""
+    import numpy as np
+    K = np.asarray(K, dtype=np.float64)
+    poses = np.asarray(poses, dtype=np.float64)
+    flip = np.array([1.0, -1.0, -1.0]) if colmap else np.ones(3)
+    rows, cols = np.divmod(np.arange(H * W), W)
+    pix = np.stack([cols, rows, np.ones(H * W, dtype=np.int64)])          # [3, H*W]
+    cam = flip[:, None] * (np.linalg.inv(K) @ pix)
+    if normalize:
+        cam = cam / np.maximum(np.sqrt((cam * cam).sum(axis=0, keepdims=True)), 1e-8)
+    d = (poses[:, :3, :3] @ cam).transpose(0, 2, 1).reshape(-1, H, W, 3)
+    o = np.broadcast_to(poses[:, None, None, :3, 3], d.shape)
+    return o, d
+
+
+def ray_cube_hits(rays_o, rays_d, cube_min: float = -1.0, cube_max: float = 1.0):
+    """Slab test in fp32.  precompute_rays.py:28-29 (fp32 cast), :32-37 (|d| < 1e-8 -> sign(d) * 1e-8), :40-52
+    (per-axis entry / exit, sorted), :55-56 (interval), :59 (hit flag, BEFORE the clamp), :62 (t_near >= 0).
+    numpy's minimum / maximum propagate NaN (0/0 when an origin lies on a slab plane of a zero direction component)."""
+    import numpy as np
+    o = np.asarray(rays_o, dtype=np.float32)
+    d = np.asarray(rays_d, dtype=np.float32)
+    eps = np.float32(1e-8)
+    d = np.where(np.abs(d) < eps, np.sign(d) * eps, d).astype(np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ta = (np.float32(cube_min) - o) / d
+        tb = (np.float32(cube_max) - o) / d
+    lo, hi = np.minimum(ta, tb), np.maximum(ta, tb)
+    t_near = lo.max(axis=1)   # ndarray.max propagates NaN like np.maximum
+    t_far = hi.min(axis=1)
+    with np.errstate(invalid="ignore"):
+        hits = (t_near <= t_far) & (t_far >= 0)
+    return hits, np.maximum(t_near, np.float32(0.0)), t_far
+
+
+def precompute_rays(H: int, W: int, K, poses, images_u8, cube_min: float = -1.0, cube_max: float = 1.0):
+    """precompute_rays.py:206-228: rays of every pixel, the hits kept in order; colours are u8 / 255 in fp32
+    (:131-132).  Returns the dict the reference writes to the .npz (rays fp64 there; fp32 after dataset.py:52-53)."""
+    import numpy as np
+    o, d = camera_rays(H, W, K, poses)
+    o, d = o.reshape(-1, 3), d.reshape(-1, 3)
+    hits, t_near, t_far = ray_cube_hits(o, d, cube_min, cube_max)
+    rgb = np.asarray(images_u8).reshape(-1, 3).astype(np.float32) / np.float32(255.0)
+    return {"rays_o": o[hits], "rays_d": d[hits], "rgbs": rgb[hits], "t_near": t_near[hits], "t_far": t_far[hits]}

@@ -85,3 +85,40 @@ def make_draws(seed: int, B: int, S: int, I: int):
 def make_noise(seed: int, n: int):
     rs = np.random.RandomState(seed)
     return torch.from_numpy(rs.normal(size=(n, 1)).astype(np.float32))
+
+
+def make_cameras(seed: int, M: int, H: int, W: int, focal: float = None):
+    """Deterministic pinhole cameras for the ray-generation tests: intrinsics K (3x3, fp64), camera-to-world poses
+    [M,4,4] fp64 on a shell of radius 2.5-4 around the origin, looking roughly (not exactly) at it so that part of every
+    image misses the [-1,1]^3 cube, and u8 images [M,H,W,3]."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    f = float(focal) if focal is not None else 0.9 * W
+    K = np.array([[f, 0.0, W / 2.0 - 0.25], [0.0, f * 1.01, H / 2.0 + 0.5], [0.0, 0.0, 1.0]], dtype=np.float64)
+    poses = np.zeros((M, 4, 4), dtype=np.float64)
+    for m in range(M):
+        c = rng.normal(size=3)
+        c = c / np.linalg.norm(c) * rng.uniform(2.5, 4.0)
+        target = rng.uniform(-0.9, 0.9, size=3)
+        back = c - target
+        back /= np.linalg.norm(back)                     # camera +z points away from the scene (OpenGL convention)
+        up = np.array([0.0, 0.0, 1.0]) if abs(back[2]) < 0.95 else np.array([0.0, 1.0, 0.0])
+        right = np.cross(up, back)
+        right /= np.linalg.norm(right)
+        poses[m, :3, 0], poses[m, :3, 1], poses[m, :3, 2], poses[m, :3, 3] = right, np.cross(back, right), back, c
+        poses[m, 3, 3] = 1.0
+    images = rng.integers(0, 256, size=(M, H, W, 3), dtype=np.uint8)
+    return H, W, K, poses, images
+
+
+def edge_case_rays():
+    """fp32 rays that exercise the special cases of the slab test: zero / tiny / negative-zero direction components,
+    origins inside the cube, on a slab plane (0/0 -> NaN in numpy), behind the cube, grazing an edge."""
+    import numpy as np
+    o = np.array([[0.0, 0.0, 0.0], [2.0, 0.1, -0.2], [2.0, 0.1, -0.2], [0.75, 0.0, 0.0], [-0.5, 0.2, 0.3],
+                  [0.1, 0.2, 3.0], [0.1, 0.2, 3.0], [3.0, 3.0, 3.0], [0.0, 0.74, -2.0], [0.2, -0.1, 0.3],
+                  [5.0, 0.0, 0.0], [0.3, 0.3, 0.3]], dtype=np.float32)
+    d = np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [-0.0, -1.0, 0.0],
+                  [0.0, 0.0, -1.0], [1e-9, -1e-9, -1.0], [-0.577, -0.577, -0.577], [0.0, 1e-3, 1.0], [1e-9, 1e-12, -1e-9],
+                  [-1.0, 0.2, 0.0], [0.0, 0.0, 0.0]], dtype=np.float32)
+    return o, d

@@ -330,3 +330,102 @@ def test_errors_are_loud(D):
     with pytest.raises(NotImplementedError):
         m = D.OptimizedVanillaNeRF(hidden_dim=64).cuda()
         m(torch.zeros(4, 3, device="cuda"), torch.zeros(4, 3, device="cuda"))
+
+
+# ---- ray generation / cube intersection (scripts/precompute_rays.py) ---------------------------------
+def _rays_golden():
+    import os
+    return dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "rays_golden.npz")))
+
+
+def test_generate_rays_golden(D):
+    from common import make_cameras
+    g = _rays_golden()
+    H, W, K, poses, _ = make_cameras(7, M=3, H=12, W=16)
+    o, d = D.get_rays(H, W, K, poses)
+    assert o.shape == (3, H, W, 3) and o.dtype == torch.float32
+    assert np.array_equal(o.cpu().numpy(), g["rays_o"].astype(np.float32))
+    want = g["rays_d"].astype(np.float32)
+    got = d.cpu().numpy()
+    # fp64 arithmetic in another association than numpy's BLAS: equal after the fp32 cast up to a rare 1-ulp tie
+    assert np.abs(got - want).max() <= 6e-8 and (got == want).mean() > 0.99
+    o2, d2 = O.camera_rays(H, W, K, poses, colmap=False, normalize=False)
+    o3, d3 = D.get_rays(H, W, K, poses, colmap=False, normalize_directions=False)
+    assert np.allclose(d3.cpu().numpy(), d2.astype(np.float32), rtol=2e-7, atol=0)
+
+
+def test_ray_cube_intersection_bit_exact(D):
+    from common import edge_case_rays
+    g = _rays_golden()
+    o32, d32 = g["rays_o"].reshape(-1, 3).astype(np.float32), g["rays_d"].reshape(-1, 3).astype(np.float32)
+    hits, t_near, t_far = D.ray_cube_intersection_numpy(T(o32).cuda(), T(d32).cuda())
+    assert np.array_equal(hits.cpu().numpy(), g["hits"])
+    assert np.array_equal(t_near.cpu().numpy(), g["t_near"], equal_nan=True)
+    assert np.array_equal(t_far.cpu().numpy(), g["t_far"], equal_nan=True)
+    eo, ed = edge_case_rays()
+    hits, t_near, t_far = D.ray_cube_intersection(T(eo).cuda(), T(ed).cuda(), -0.5, 0.75)
+    assert np.array_equal(hits.cpu().numpy(), g["edge_hits"])
+    assert np.array_equal(t_near.cpu().numpy(), g["edge_near"], equal_nan=True)
+    assert np.array_equal(t_far.cpu().numpy(), g["edge_far"], equal_nan=True)
+    # random rays against the oracle, bit for bit
+    rng = np.random.default_rng(5)
+    o = rng.uniform(-3, 3, size=(100003, 3)).astype(np.float32)
+    dd = rng.normal(size=(100003, 3)).astype(np.float32)
+    dd[::7, 1] = 0.0
+    dd[::11, 0] = 1e-9
+    oh, on, of = O.ray_cube_hits(o, dd)
+    hits, t_near, t_far = D.ray_cube_intersection(T(o).cuda(), T(dd).cuda())
+    assert np.array_equal(hits.cpu().numpy(), oh)
+    assert np.array_equal(t_near.cpu().numpy(), on, equal_nan=True) and np.array_equal(t_far.cpu().numpy(), of, equal_nan=True)
+
+
+def test_precompute_rays_fused(D):
+    from common import make_cameras
+    g = _rays_golden()
+    H, W, K, poses, images = make_cameras(7, M=3, H=12, W=16)
+    out = D.precompute_rays_on_device(H, W, K, poses, T(images).cuda())
+    k = int(g["hits"].sum())
+    assert out["rays_o"].shape == (k, 3) and out["t_near"].shape == (k,)
+    assert np.array_equal(out["rays_o"].cpu().numpy(), g["kept_o"].astype(np.float32))
+    assert np.abs(out["rays_d"].cpu().numpy() - g["kept_d"].astype(np.float32)).max() <= 6e-8
+    assert np.array_equal(out["rgbs"].cpu().numpy(), g["kept_rgb"])
+    assert np.allclose(out["t_near"].cpu().numpy(), g["kept_near"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(out["t_far"].cpu().numpy(), g["kept_far"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("M,H,W", [(1, 1, 1), (2, 31, 33), (3, 1080, 1920)])
+def test_precompute_rays_equals_unfused_path(D, M, H, W):
+    """Size-independent property at full size: the fused generate + intersect + compaction equals generating every ray,
+    intersecting it and boolean-masking, bit for bit and in order (ragged chunk tails, multi-tile scan of the counts)."""
+    from common import make_cameras
+    _, _, K, poses, images = make_cameras(3 + M, M=M, H=H, W=W, focal=0.45 * W)
+    img = T(images).cuda()
+    o, d = D.get_rays(H, W, K, poses)
+    hits, t_near, t_far = D.ray_cube_intersection(o, d)
+    out = D.precompute_rays_on_device(H, W, K, poses, img)
+    k = int(hits.sum())
+    assert out["rays_o"].shape[0] == k
+    if M > 1:
+        assert 0 < k < M * H * W
+    assert torch.equal(out["rays_o"], o.reshape(-1, 3)[hits]) and torch.equal(out["rays_d"], d.reshape(-1, 3)[hits])
+    assert torch.equal(out["t_near"], t_near[hits]) and torch.equal(out["t_far"], t_far[hits])
+    want_rgb = (images.reshape(-1, 3).astype(np.float32) / np.float32(255.0))[hits.cpu().numpy()]   # IEEE division, as numpy does
+    assert np.array_equal(out["rgbs"].cpu().numpy(), want_rgb)
+    assert bool((out["t_near"] >= 0).all()) and bool((out["t_near"] <= out["t_far"]).all())
+
+
+def test_precompute_rays_no_hits_and_store(D):
+    from common import make_cameras
+    H, W, K, poses, images = make_cameras(9, M=2, H=8, W=8)
+    away = poses.copy()
+    away[:, :3, 2] *= -1.0   # look the other way: nothing hits the cube
+    away[:, :3, 0] *= -1.0
+    out = D.precompute_rays_on_device(H, W, K, away, T(images).cuda())
+    assert out["rays_o"].shape == (0, 3) and out["rgbs"].shape == (0, 3)
+    out = D.precompute_rays_on_device(H, W, K, poses, T(images).cuda())
+    store = D.RayStore.from_tensors(out)
+    assert len(store) == out["rays_o"].shape[0] > 0
+    with pytest.raises(ValueError):
+        D.precompute_rays_on_device(H, W, K, poses, T(images).cuda().float())
+    with pytest.raises(RuntimeError):
+        D.get_rays(H, W, K, poses, device="cpu")

@@ -119,3 +119,43 @@ def test_adamw_onecycle(golden):
         assert abs(lr - golden["adamw_lrs"][s]) <= 1e-12 + 1e-9 * lr, (s, lr, golden["adamw_lrs"][s])
         p, m, v = O.adamw_step(p, T(golden["adamw_grads"][s]), m, v, s + 1, lr, b1=b1)
         np.testing.assert_allclose(p.numpy(), golden["adamw_params"][s], rtol=2e-6, atol=1e-7)
+
+
+# ---- ray generation / cube intersection (scripts/precompute_rays.py) ---------------------------------
+def _rays_golden():
+    import os
+    return dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "rays_golden.npz")))
+
+
+def test_camera_rays_match_reference():
+    from common import make_cameras
+    g = _rays_golden()
+    H, W, K, poses, _ = make_cameras(7, M=3, H=12, W=16)
+    o, d = O.camera_rays(H, W, K, poses)
+    assert np.array_equal(o, g["rays_o"])
+    # fp64 sums in a different association than numpy's einsum: a few ulp of fp64, nothing after the fp32 cast
+    assert np.allclose(d, g["rays_d"], rtol=0, atol=4e-16)
+    assert np.array_equal(d.astype(np.float32), g["rays_d"].astype(np.float32))
+
+
+def test_ray_cube_hits_bit_exact():
+    from common import edge_case_rays
+    g = _rays_golden()
+    hits, t_near, t_far = O.ray_cube_hits(g["rays_o"].reshape(-1, 3), g["rays_d"].reshape(-1, 3))
+    assert np.array_equal(hits, g["hits"])
+    assert np.array_equal(t_near, g["t_near"], equal_nan=True) and np.array_equal(t_far, g["t_far"], equal_nan=True)
+    eo, ed = edge_case_rays()
+    hits, t_near, t_far = O.ray_cube_hits(eo, ed, -0.5, 0.75)
+    assert np.array_equal(hits, g["edge_hits"])
+    assert np.array_equal(t_near, g["edge_near"], equal_nan=True) and np.array_equal(t_far, g["edge_far"], equal_nan=True)
+    assert np.isnan(g["edge_near"]).any() and g["edge_hits"].any() and not g["edge_hits"].all()   # the fixture covers the cases
+
+
+def test_precompute_rays_keeps_hits_in_order():
+    from common import make_cameras
+    g = _rays_golden()
+    H, W, K, poses, images = make_cameras(7, M=3, H=12, W=16)
+    out = O.precompute_rays(H, W, K, poses, images)
+    assert np.array_equal(out["rays_o"], g["kept_o"]) and np.array_equal(out["rgbs"], g["kept_rgb"])
+    assert np.array_equal(out["rays_d"].astype(np.float32), g["kept_d"].astype(np.float32))
+    assert np.array_equal(out["t_near"], g["kept_near"]) and np.array_equal(out["t_far"], g["kept_far"])
