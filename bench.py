@@ -324,6 +324,39 @@ def run_ours(args):
                    "tflops": tf, "frac_of_sustained_tensor_peak": tf / (pk["tensor_sustained"] * world)}
         del out
 
+    # ---- ray generation + cube intersection + compaction (scripts/precompute_rays.py), the step in front of the path ----
+    raygen = None
+    if rank == 0 and not args.no_extract:
+        import numpy as np
+        sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+        from common import make_cameras
+        Mc, Hc, Wc = 8, 1080, 1920
+        _, _, Kc, poses_c, _ = make_cameras(21, M=Mc, H=2, W=2, focal=0.45 * Wc)
+        Kc[0, 2], Kc[1, 2] = Wc / 2.0, Hc / 2.0
+        img = torch.randint(0, 256, (Mc, Hc, Wc, 3), device=dev, dtype=torch.uint8)
+        res = D.precompute_rays_on_device(Hc, Wc, Kc, poses_c, img)
+        torch.cuda.synchronize()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        for _ in range(3):
+            res = D.precompute_rays_on_device(Hc, Wc, Kc, poses_c, img)
+        r1.record()
+        torch.cuda.synchronize()
+        ms_r = r0.elapsed_time(r1) / 3
+        n_all, n_kept = Mc * Hc * Wc, res["rays_o"].shape[0]
+        algo_bytes = 3 * n_all + 56 * n_kept     # u8 image in; o, d, rgb (12 B each) + t_near, t_far out per kept ray
+        raygen = {"metric": "precompute_rays_per_s", "value": n_all / (ms_r * 1e-3), "unit": "rays/s", "cameras": Mc, "H": Hc, "W": Wc,
+                  "kept_fraction": n_kept / n_all, "ms": ms_r, "hbm_gbs": algo_bytes / (ms_r * 1e-3) / 1e9,
+                  "frac_of_hbm_peak": algo_bytes / (ms_r * 1e-3) / 1e9 / pk["hbm"],
+                  "includes": "generate + intersect + ordered compaction + 8-byte count read-back, through the public API"}
+        if not args.no_cpu:
+            from oracle import nerf_oracle as O
+            t0 = time.perf_counter()
+            O.precompute_rays(Hc, Wc, Kc, poses_c[:1], np.zeros((1, Hc, Wc, 3), dtype=np.uint8))
+            raygen["cpu_port_rays_per_s"] = Hc * Wc / (time.perf_counter() - t0)
+            raygen["cpu_sample"] = "1 camera of 1080x1920, numpy oracle port, 1 thread"
+        del img, res
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, sample, cores = cpu_rate(args.cpu_budget)
@@ -348,6 +381,7 @@ def run_ours(args):
             "step_tflops": step_tflops, "step_frac_of_sustained_tensor_peak": step_tflops / (pk["tensor_sustained"] * world),
             "stages": stage_report,
             "extract_vol": extract,
+            "precompute_rays": raygen,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -93,7 +93,10 @@ __global__ void cube_intersect_kernel(const float* __restrict__ rays_o, const fl
 }
 
 // pass 1: hits per chunk
-__global__ void __launch_bounds__(kChunk) count_hits_kernel(const RayGenArgs a, unsigned int* __restrict__ counts) {
+// (also keeps the per-warp hit ballots: pass 2 recomputes only the rays it keeps - the fp64 arithmetic, not HBM, is what
+// this path costs)
+__global__ void __launch_bounds__(kChunk) count_hits_kernel(const RayGenArgs a, unsigned int* __restrict__ counts,
+                                                            unsigned int* __restrict__ ballots) {
   const long long n = static_cast<long long>(blockIdx.x) * kChunk + threadIdx.x;
   bool hit = false;
   if (n < a.n_rays) {
@@ -101,6 +104,8 @@ __global__ void __launch_bounds__(kChunk) count_hits_kernel(const RayGenArgs a, 
     make_ray(a, n, o, d);
     hit = cube_hit(o, d, a.cube_min, a.cube_max, tn, tf);
   }
+  const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
+  if ((threadIdx.x & 31) == 0) ballots[n >> 5] = ballot;
   const int c = __syncthreads_count(hit);
   if (threadIdx.x == 0) counts[blockIdx.x] = static_cast<unsigned int>(c);
 }
@@ -145,19 +150,15 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(const unsigned int* _
 
 // pass 2: recompute, keep the hits in order
 __global__ void __launch_bounds__(kChunk) compact_rays_kernel(const RayGenArgs a, const uint8_t* __restrict__ images,
-                                                              const long long* __restrict__ offsets, float* __restrict__ rays_o,
+                                                              const long long* __restrict__ offsets,
+                                                              const unsigned int* __restrict__ ballots, float* __restrict__ rays_o,
                                                               float* __restrict__ rays_d, float* __restrict__ rgbs,
                                                               float* __restrict__ t_near, float* __restrict__ t_far) {
   __shared__ int warp_counts[kChunk / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long n = static_cast<long long>(blockIdx.x) * kChunk + threadIdx.x;
-  bool hit = false;
-  float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f}, tn = 0.f, tf = 0.f;
-  if (n < a.n_rays) {
-    make_ray(a, n, o, d);
-    hit = cube_hit(o, d, a.cube_min, a.cube_max, tn, tf);
-  }
-  const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
+  const unsigned int ballot = ballots[n >> 5];   // (the ballot array is padded to whole chunks)
+  const bool hit = (ballot >> lane) & 1u;
   if (lane == 0) warp_counts[warp] = __popc(ballot);
   __syncthreads();
   if (warp == 0) {
@@ -171,6 +172,9 @@ __global__ void __launch_bounds__(kChunk) compact_rays_kernel(const RayGenArgs a
   }
   __syncthreads();
   if (hit) {
+    float o[3], d[3], tn, tf;
+    make_ray(a, n, o, d);
+    cube_hit(o, d, a.cube_min, a.cube_max, tn, tf);
     const long long dst = offsets[blockIdx.x] + (warp > 0 ? warp_counts[warp - 1] : 0) + __popc(ballot & ((1u << lane) - 1u));
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -225,7 +229,7 @@ extern "C" int dfn_ray_cube_intersect(const float* rays_o, const float* rays_d, 
 
 extern "C" long long dfn_precompute_rays_workspace_bytes(long long n_rays) {
   const long long chunks = (n_rays + kChunk - 1) / kChunk;
-  return chunks * 4 + 16 + chunks * 8 + 16;   // counts (u32) | offsets (i64), each padded to 16 bytes
+  return chunks * 4 + 16 + chunks * 8 + 16 + chunks * (kChunk / 8);   // counts (u32) | offsets (i64), each padded to 16 bytes | ballots
 }
 
 extern "C" int dfn_precompute_rays(const double* kinv_host, const double* poses, int M, int H, int W, int colmap, int normalize,
@@ -239,12 +243,13 @@ extern "C" int dfn_precompute_rays(const double* kinv_host, const double* poses,
   DFN_CHECK_ARG(chunks < (1LL << 31), "precompute_rays: too many rays for one launch");
   unsigned int* counts = static_cast<unsigned int*>(workspace);
   long long* offsets = reinterpret_cast<long long*>(static_cast<uint8_t*>(workspace) + ((chunks * 4 + 15) / 16) * 16);
+  unsigned int* ballots = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(offsets) + ((chunks * 8 + 15) / 16) * 16);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  count_hits_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(a, counts);
+  count_hits_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(a, counts, ballots);
   DFN_CHECK_LAUNCH("precompute_rays(count)");
   scan_counts_kernel<<<1, 1024, 0, st>>>(counts, chunks, offsets, count);
   DFN_CHECK_LAUNCH("precompute_rays(scan)");
-  compact_rays_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(a, images, offsets, rays_o, rays_d, rgbs, t_near, t_far);
+  compact_rays_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(a, images, offsets, ballots, rays_o, rays_d, rgbs, t_near, t_far);
   DFN_CHECK_LAUNCH("precompute_rays(compact)");
   return DFN_OK;
 }
