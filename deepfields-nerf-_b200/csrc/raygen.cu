@@ -5,10 +5,12 @@
 // pass recomputes the rays (cheap) and writes the kept ones in order.  Nothing but the outputs touches HBM:
 // 56 B per kept ray + 3 B of image per generated ray.
 #include "dfn_common.cuh"
+#include "compact.cuh"
 
 namespace {
 
-constexpr int kChunk = 1024;   // rays per CTA
+using dfn_compact::kChunk;   // rays per CTA
+using dfn_compact::scan_counts_kernel;
 
 struct RayGenArgs {
   double kinv[9];          // inverse intrinsics, row-major (np.linalg.inv(K), precompute_rays.py:80)
@@ -110,44 +112,6 @@ __global__ void __launch_bounds__(kChunk) count_hits_kernel(const RayGenArgs a, 
   if (threadIdx.x == 0) counts[blockIdx.x] = static_cast<unsigned int>(c);
 }
 
-// exclusive scan of the chunk counts (one block; the carry runs through the 1024-wide tiles), total -> *total_out
-__global__ void __launch_bounds__(1024) scan_counts_kernel(const unsigned int* __restrict__ counts, long long n_chunks,
-                                                            long long* __restrict__ offsets, long long* __restrict__ total_out) {
-  __shared__ long long warp_sums[32];
-  __shared__ long long carry;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry = 0;
-  __syncthreads();
-  for (long long base = 0; base < n_chunks; base += 1024) {
-    const long long i = base + threadIdx.x;
-    const long long x = i < n_chunks ? counts[i] : 0;
-    long long s = x;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const long long y = __shfl_up_sync(0xffffffffu, s, off);
-      if (lane >= off) s += y;
-    }
-    if (lane == 31) warp_sums[warp] = s;
-    __syncthreads();
-    if (warp == 0) {
-      long long w = warp_sums[lane];
-#pragma unroll
-      for (int off = 1; off < 32; off <<= 1) {
-        const long long y = __shfl_up_sync(0xffffffffu, w, off);
-        if (lane >= off) w += y;
-      }
-      warp_sums[lane] = w;   // inclusive
-    }
-    __syncthreads();
-    const long long before = carry + (warp > 0 ? warp_sums[warp - 1] : 0) + (s - x);
-    if (i < n_chunks) offsets[i] = before;
-    __syncthreads();
-    if (threadIdx.x == 1023) carry = before + x;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) *total_out = carry;
-}
-
 // pass 2: recompute, keep the hits in order
 __global__ void __launch_bounds__(kChunk) compact_rays_kernel(const RayGenArgs a, const uint8_t* __restrict__ images,
                                                               const long long* __restrict__ offsets,
@@ -155,27 +119,16 @@ __global__ void __launch_bounds__(kChunk) compact_rays_kernel(const RayGenArgs a
                                                               float* __restrict__ rays_d, float* __restrict__ rgbs,
                                                               float* __restrict__ t_near, float* __restrict__ t_far) {
   __shared__ int warp_counts[kChunk / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
   const long long n = static_cast<long long>(blockIdx.x) * kChunk + threadIdx.x;
   const unsigned int ballot = ballots[n >> 5];   // (the ballot array is padded to whole chunks)
   const bool hit = (ballot >> lane) & 1u;
-  if (lane == 0) warp_counts[warp] = __popc(ballot);
-  __syncthreads();
-  if (warp == 0) {
-    int w = warp_counts[lane];
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, w, off);
-      if (lane >= off) w += y;
-    }
-    warp_counts[lane] = w;   // inclusive
-  }
-  __syncthreads();
+  const int rank = dfn_compact::rank_in_chunk(ballot, warp_counts);
   if (hit) {
     float o[3], d[3], tn, tf;
     make_ray(a, n, o, d);
     cube_hit(o, d, a.cube_min, a.cube_max, tn, tf);
-    const long long dst = offsets[blockIdx.x] + (warp > 0 ? warp_counts[warp - 1] : 0) + __popc(ballot & ((1u << lane) - 1u));
+    const long long dst = offsets[blockIdx.x] + rank;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       rays_o[dst * 3 + i] = o[i];
@@ -227,10 +180,7 @@ extern "C" int dfn_ray_cube_intersect(const float* rays_o, const float* rays_d, 
   return DFN_OK;
 }
 
-extern "C" long long dfn_precompute_rays_workspace_bytes(long long n_rays) {
-  const long long chunks = (n_rays + kChunk - 1) / kChunk;
-  return chunks * 4 + 16 + chunks * 8 + 16 + chunks * (kChunk / 8);   // counts (u32) | offsets (i64), each padded to 16 bytes | ballots
-}
+extern "C" long long dfn_precompute_rays_workspace_bytes(long long n_rays) { return dfn_compact::workspace_bytes(n_rays); }
 
 extern "C" int dfn_precompute_rays(const double* kinv_host, const double* poses, int M, int H, int W, int colmap, int normalize,
                                    const unsigned char* images, float cube_min, float cube_max, float* rays_o, float* rays_d,
@@ -241,9 +191,10 @@ extern "C" int dfn_precompute_rays(const double* kinv_host, const double* poses,
   DFN_CHECK_ARG((rgbs == nullptr) == (images == nullptr), "precompute_rays: images and rgbs go together");
   const long long chunks = (a.n_rays + kChunk - 1) / kChunk;
   DFN_CHECK_ARG(chunks < (1LL << 31), "precompute_rays: too many rays for one launch");
-  unsigned int* counts = static_cast<unsigned int*>(workspace);
-  long long* offsets = reinterpret_cast<long long*>(static_cast<uint8_t*>(workspace) + ((chunks * 4 + 15) / 16) * 16);
-  unsigned int* ballots = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(offsets) + ((chunks * 8 + 15) / 16) * 16);
+  const dfn_compact::Workspace w = dfn_compact::carve(workspace, a.n_rays);
+  unsigned int* counts = w.counts;
+  long long* offsets = w.offsets;
+  unsigned int* ballots = w.ballots;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   count_hits_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(a, counts, ballots);
   DFN_CHECK_LAUNCH("precompute_rays(count)");

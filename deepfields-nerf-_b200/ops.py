@@ -366,6 +366,41 @@ def precompute_rays(H: int, W: int, K, poses, images: Optional[Tensor] = None, c
     return out
 
 
+# ---- occupied voxels as points (scripts/post_process_vol.py) -----------------------------------------
+def volume_points(occupancy: Tensor, rgb_volume: Tensor, aabb_min=None, aabb_max=None) -> Tuple[Tensor, Tensor]:
+    """argwhere + colour gather + normalised coordinates (+ closed AABB slice): points [N,3] fp64, rgbs [N,3] fp32."""
+    import ctypes
+    import numpy as np
+    if not occupancy.is_cuda or not rgb_volume.is_cuda:
+        raise RuntimeError("deepfields_nerf_b200: volume_points needs CUDA tensors (there is no CPU fallback)")
+    if occupancy.dim() != 3 or len(set(occupancy.shape)) != 1:
+        raise ValueError("occupancy_volume must be [R,R,R]")
+    R = occupancy.shape[0]
+    if tuple(rgb_volume.shape) != (R, R, R, 3) or rgb_volume.dtype != torch.uint8:
+        raise ValueError("rgb_volume must be uint8 [R,R,R,3]")
+    occ = occupancy.to(torch.uint8).contiguous()
+    rgb = rgb_volume.contiguous()
+    n = R ** 3
+    lo = hi = None
+    if (aabb_min is None) != (aabb_max is None):
+        raise ValueError("aabb_min and aabb_max go together")
+    if aabb_min is not None:
+        lo = np.ascontiguousarray(np.asarray(aabb_min, dtype=np.float64).reshape(3))
+        hi = np.ascontiguousarray(np.asarray(aabb_max, dtype=np.float64).reshape(3))
+    dev = occ.device
+    points = torch.empty(n, 3, device=dev, dtype=torch.float64)
+    rgbs = torch.empty(n, 3, device=dev, dtype=torch.float32)
+    count = torch.zeros(1, device=dev, dtype=torch.int64)
+    ws = torch.empty(int(_lib.load().dfn_volume_points_workspace_bytes(n)), device=dev, dtype=torch.uint8)
+    with torch.cuda.device(dev):
+        _lib.call("dfn_volume_points", occ.data_ptr(), rgb.data_ptr(), R,
+                  lo.ctypes.data_as(ctypes.c_void_p) if lo is not None else None,
+                  hi.ctypes.data_as(ctypes.c_void_p) if hi is not None else None,
+                  points.data_ptr(), rgbs.data_ptr(), count.data_ptr(), ws.data_ptr(), _stream())
+    k = int(count.item())
+    return points[:k], rgbs[:k]
+
+
 # ---- optimiser -------------------------------------------------------------------------------------
 def adamw_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, beta1_table: Tensor, step: Tensor,
                beta2=0.999, eps=1e-8, weight_decay=1e-6, grad_scale=1.0) -> None:

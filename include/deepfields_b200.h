@@ -143,6 +143,15 @@ int dfn_precompute_rays(const double* kinv, const double* poses, int M, int H, i
                         const unsigned char* images, float cube_min, float cube_max, float* rays_o, float* rays_d,
                         float* rgbs, float* t_near, float* t_far, long long* count, void* workspace, void* stream);
 
+/* ---- occupied voxels as a point set, the step after extract_vol (scripts/post_process_vol.py:37-50, :77-107) ---- */
+/* argwhere(occupancy) in C order -> points [N,3] fp64 = (index / (R-1)) * 2 - 1, rgbs [N,3] fp32 = rgb_volume / max(rgb_volume)
+ * gathered at those voxels; aabb_min / aabb_max = HOST pointers to 3 doubles (closed box, slice_aabb) or both null.
+ * occupancy [R^3] u8, rgb_volume [R^3,3] u8 on the device; outputs sized for R^3 points; *count (device int64) = N;
+ * workspace of dfn_volume_points_workspace_bytes(R^3) bytes. */
+long long dfn_volume_points_workspace_bytes(long long n_voxels);
+int dfn_volume_points(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
+                      const double* aabb_max, double* points, float* rgbs, long long* count, void* workspace, void* stream);
+
 /* ---- optimiser (scripts/train.py:244-259, :321-322) ---------------------------------------------- */
 /* AdamW on a flat buffer; lr_table/beta1_table [table_len] hold the OneCycleLR schedule, *step_ptr (device int,
  * 0-based) selects the entry and is incremented. */

@@ -349,3 +349,23 @@ def precompute_rays(H: int, W: int, K, poses, images_u8, cube_min: float = -1.0,
     hits, t_near, t_far = ray_cube_hits(o, d, cube_min, cube_max)
     rgb = np.asarray(images_u8).reshape(-1, 3).astype(np.float32) / np.float32(255.0)
     return {"rays_o": o[hits], "rays_d": d[hits], "rgbs": rgb[hits], "t_near": t_near[hits], "t_far": t_far[hits]}
+
+
+# ----------------------------------------------------------------------------------------------
+# (f5) occupied voxels as a point set -- scripts/post_process_vol.py
+# ----------------------------------------------------------------------------------------------
+def volume_points(occupancy, rgb_volume, aabb_min=None, aabb_max=None):
+    """post_process_vol.py:82 (colours = u8 volume / its maximum, fp32), :89 (argwhere in C order), :90 (gather),
+    :94-95 (index / (R-1) * 2 - 1, fp64), :37-50 (closed-box slice).  occupancy [R,R,R] u8, rgb_volume [R,R,R,3] u8."""
+    import numpy as np
+    occ = np.asarray(occupancy)
+    rgb = np.asarray(rgb_volume)
+    R = occ.shape[0]
+    idx = np.stack(np.nonzero(occ), axis=1)                       # C order == argwhere
+    cols = rgb[idx[:, 0], idx[:, 1], idx[:, 2]].astype(np.float32) / np.float32(rgb.max())
+    pts = (idx / (R - 1)) * 2 - 1
+    if aabb_min is not None:
+        lo, hi = np.asarray(aabb_min, dtype=np.float64), np.asarray(aabb_max, dtype=np.float64)
+        keep = np.all((pts >= lo) & (pts <= hi), axis=1)
+        pts, cols = pts[keep], cols[keep]
+    return pts, cols

@@ -122,3 +122,14 @@ def edge_case_rays():
                   [0.0, 0.0, -1.0], [1e-9, -1e-9, -1.0], [-0.577, -0.577, -0.577], [0.0, 1e-3, 1.0], [1e-9, 1e-12, -1e-9],
                   [-1.0, 0.2, 0.0], [0.0, 0.0, 0.0]], dtype=np.float32)
     return o, d
+
+
+def make_volume(seed: int, R: int):
+    """Deterministic u8 occupancy [R,R,R] (a blob plus speckle, ~20 % set) and u8 colours [R,R,R,3] (maximum < 255)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    g = np.linspace(-1, 1, R)
+    x, y, z = np.meshgrid(g, g, g, indexing="ij")
+    occ = ((x * x + 0.6 * y * y + 1.4 * z * z < 0.35) | (rng.random((R, R, R)) < 0.03)).astype(np.uint8)
+    rgb = rng.integers(0, 241, size=(R, R, R, 3), dtype=np.uint8)
+    return occ, rgb

@@ -429,3 +429,62 @@ def test_precompute_rays_no_hits_and_store(D):
         D.precompute_rays_on_device(H, W, K, poses, T(images).cuda().float())
     with pytest.raises(RuntimeError):
         D.get_rays(H, W, K, poses, device="cpu")
+
+
+# ---- occupied voxels as points (scripts/post_process_vol.py) -----------------------------------------
+VOL_AABB = {"aabb_min": [-0.55, -0.4, -0.7], "aabb_max": [0.6, 1.0, 0.22580645161290325]}
+
+
+def test_volume_points_golden_bit_exact(D):
+    import os
+    from common import make_volume
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "volume_points_golden.npz")))
+    occ, rgb = make_volume(5, 32)
+    pts, cols = D.volume_points(T(occ).cuda(), T(rgb).cuda())
+    assert pts.dtype == torch.float64 and cols.dtype == torch.float32
+    assert np.array_equal(pts.cpu().numpy(), g["points"]) and np.array_equal(cols.cpu().numpy(), g["rgbs"])
+    pts, cols = D.volume_points(T(occ).cuda(), T(rgb).cuda(), VOL_AABB)
+    assert np.array_equal(pts.cpu().numpy(), g["sliced_points"]) and np.array_equal(cols.cpu().numpy(), g["sliced_rgbs"])
+    p2, c2 = D.slice_aabb(T(g["points"]).cuda(), T(g["rgbs"]).cuda(), VOL_AABB)
+    assert np.array_equal(p2.cpu().numpy(), g["sliced_points"]) and np.array_equal(c2.cpu().numpy(), g["sliced_rgbs"])
+
+
+@pytest.mark.parametrize("R", [2, 33, 160])
+def test_volume_points_vs_oracle_and_edges(D, R):
+    from common import make_volume
+    occ, rgb = make_volume(40 + R, R)
+    box = ([-0.3, -1.0, -0.25], [0.9, 0.5, 1.0])
+    for lo, hi in ((None, None), box):
+        want_p, want_c = O.volume_points(occ, rgb, lo, hi)
+        meta = None if lo is None else {"aabb_min": lo, "aabb_max": hi}
+        pts, cols = D.volume_points(T(occ).cuda(), T(rgb).cuda(), meta)
+        assert np.array_equal(pts.cpu().numpy(), want_p) and np.array_equal(cols.cpu().numpy(), want_c)
+    empty = np.zeros_like(occ)
+    pts, cols = D.volume_points(T(empty).cuda(), T(rgb).cuda())
+    assert pts.shape == (0, 3) and cols.shape == (0, 3)
+    full = np.ones_like(occ)
+    pts, cols = D.volume_points(T(full).cuda(), T(rgb).cuda())
+    assert pts.shape == (R ** 3, 3) and float(pts.min()) == -1.0 and float(pts.max()) == 1.0
+    assert bool((pts[1:, 0] >= pts[:-1, 0]).all())   # C order: x slowest
+    with pytest.raises(ValueError):
+        D.volume_points(T(occ).cuda(), T(rgb).cuda().float())
+
+
+def test_volume_points_full_size_properties(D):
+    """512^3 (BASELINE config 4 size): count, order and values against torch.nonzero on the device; the sliced set is the
+    masked raw set."""
+    R = 512
+    g = torch.Generator(device="cuda").manual_seed(3)
+    occ = (torch.rand(R, R, R, device="cuda", generator=g) < 0.07).to(torch.uint8)
+    rgb = torch.randint(0, 256, (R, R, R, 3), device="cuda", dtype=torch.uint8, generator=g)
+    pts, cols = D.volume_points(occ, rgb)
+    idx = torch.nonzero(occ)
+    assert pts.shape[0] == idx.shape[0] == int(occ.sum())
+    want = torch.div(idx.double(), torch.full_like(idx, R - 1, dtype=torch.float64)) * 2 - 1
+    assert torch.equal(pts, want)
+    want_c = torch.div(rgb[idx[:, 0], idx[:, 1], idx[:, 2]].float(), torch.full((1,), float(rgb.max()), device="cuda"))
+    assert torch.equal(cols, want_c)
+    meta = {"aabb_min": [-0.5, -0.25, -1.0], "aabb_max": [0.25, 0.75, 0.0]}
+    sp, sc = D.volume_points(occ, rgb, meta)
+    p2, c2 = D.slice_aabb(pts, cols, meta)
+    assert torch.equal(sp, p2) and torch.equal(sc, c2) and 0 < sp.shape[0] < pts.shape[0]

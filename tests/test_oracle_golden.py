@@ -159,3 +159,21 @@ def test_precompute_rays_keeps_hits_in_order():
     assert np.array_equal(out["rays_o"], g["kept_o"]) and np.array_equal(out["rgbs"], g["kept_rgb"])
     assert np.array_equal(out["rays_d"].astype(np.float32), g["kept_d"].astype(np.float32))
     assert np.array_equal(out["t_near"], g["kept_near"]) and np.array_equal(out["t_far"], g["kept_far"])
+
+
+# ---- occupied voxels as points (scripts/post_process_vol.py) -----------------------------------------
+VOL_AABB = {"aabb_min": [-0.55, -0.4, -0.7], "aabb_max": [0.6, 1.0, 0.22580645161290325]}
+
+
+def test_volume_points_bit_exact():
+    import os
+    from common import make_volume
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "volume_points_golden.npz")))
+    occ, rgb = make_volume(5, 32)
+    pts, cols = O.volume_points(occ, rgb)
+    assert pts.dtype == np.float64 and cols.dtype == np.float32
+    assert np.array_equal(pts, g["points"]) and np.array_equal(cols, g["rgbs"])
+    pts, cols = O.volume_points(occ, rgb, VOL_AABB["aabb_min"], VOL_AABB["aabb_max"])
+    assert np.array_equal(pts, g["sliced_points"]) and np.array_equal(cols, g["sliced_rgbs"])
+    assert 0 < len(g["sliced_points"]) < len(g["points"])
+    assert (g["sliced_points"][:, 2] == VOL_AABB["aabb_max"][2]).any()   # the closed upper bound is hit exactly
