@@ -381,6 +381,38 @@ def run_ours(args):
                   "includes": "argwhere + colour max + gather + normalise + AABB slice + 8-byte count read-back, through the public API"}
         del occ, rgbv, pv, cv
 
+    # ---- inference render of a 1920x1080 image, 256 samples/ray, with and without early ray termination (config 5) ----
+    render = None
+    if not args.no_extract:
+        from common import make_cameras, peaked
+        Hr, Wr = 1080, 1920
+        _, _, Kr, poses_r, _ = make_cameras(33, M=1, H=2, W=2, focal=0.9 * Wr)
+        Kr[0, 2], Kr[1, 2] = Wr / 2.0, Hr / 2.0
+        sd_r = peaked(make_state_dict(32, 256))
+        sd_r["density_layer.bias"] = sd_r["density_layer.bias"] + 60.0    # an opaque medium, so that rays do terminate
+        mr_c, mr_f = D.get_nerf_models(device=dev)
+        mr_c.load_state_dict(peaked(make_state_dict(31, 256)))
+        mr_f.load_state_dict(sd_r)
+        rows = D.row_range(Hr, rank, world)
+        kw = dict(rows=rows, N_samples=64, N_importance=192)
+        res_r = {}
+        for tag, eps in (("full", 0.0), ("ert", 1e-3)):
+            D.render_image(mr_c, mr_f, Hr, Wr, Kr, poses_r[0], ert_eps=eps, ert_segments=8, **kw)
+            barrier()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record()
+            _, info_r = D.render_image(mr_c, mr_f, Hr, Wr, Kr, poses_r[0], ert_eps=eps, ert_segments=8, **kw)
+            q1.record()
+            barrier()
+            res_r[tag] = (reduce_max(q0.elapsed_time(q1)), info_r)
+        n_rays = res_r["full"][1]["rays"]
+        render = {"metric": "render_pixels_per_s", "image": [Hr, Wr], "samples_per_ray": 256, "rows_per_rank": rows[1] - rows[0],
+                  "rays_hitting_cube_rank0": n_rays, "ms_full": res_r["full"][0], "ms_ert": res_r["ert"][0],
+                  "ert_eps": 1e-3, "ert_segments": 8, "ert_evaluated_fraction_rank0": res_r["ert"][1]["evaluated_fraction"],
+                  "value": Hr * Wr / (res_r["ert"][0] * 1e-3), "unit": "pixels/s",
+                  "includes": "ray generation, cube test, coarse + fine MLP, resampling, compositing; synthetic opaque medium"}
+        del mr_c, mr_f
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, sample, cores = cpu_rate(args.cpu_budget)
@@ -407,6 +439,7 @@ def run_ours(args):
             "extract_vol": extract,
             "precompute_rays": raygen,
             "volume_points": volpts,
+            "render": render,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -60,6 +60,9 @@ SIGNATURES = {
     "dfn_precompute_rays": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_volume_points_workspace_bytes": (_ll, [_ll]),
     "dfn_volume_points": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p]),
+    "dfn_ert_update": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p, _p]),
+    "dfn_compact_indices_workspace_bytes": (_ll, [_ll]),
+    "dfn_compact_indices": (_i, [_p, _p, _ll, _p, _p, _p, _p]),
     "dfn_adamw_step": (_i, [_p, _p, _p, _p, _ll, _p, _p, _p, _i, _f, _f, _f, _f, _p]),
 }
 

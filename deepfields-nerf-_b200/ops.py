@@ -401,6 +401,39 @@ def volume_points(occupancy: Tensor, rgb_volume: Tensor, aabb_min=None, aabb_max
     return points[:k], rgbs[:k]
 
 
+# ---- early ray termination (inference render) --------------------------------------------------------
+def ert_update(active: Optional[Tensor], seg_rgb: Tensor, seg_sigma: Tensor, z: Tensor, s0: int, rgb_full: Tensor,
+               sigma_full: Tensor, T_run: Tensor, eps: float, dist_last: float = 1e10) -> Tensor:
+    """Scatter one depth segment of the active rays into the full arrays, update their transmittance; returns alive [n] u8."""
+    z = _f32(z, "z_vals")
+    B, S = z.shape
+    n, C = seg_sigma.shape
+    seg_rgb, seg_sigma = _f32(seg_rgb.reshape(n, C, 3), "segment rgb"), _f32(seg_sigma, "segment sigma")
+    if active is not None:
+        active = _chk(active, torch.int32, "active ray list")
+        assert active.numel() == n
+    assert rgb_full.shape == (B, S, 3) and sigma_full.shape == (B, S) and T_run.shape == (B,)
+    alive = torch.empty(n, device=z.device, dtype=torch.uint8)
+    _lib.call("dfn_ert_update", _ptr(active), n, seg_rgb.data_ptr(), seg_sigma.data_ptr(), z.data_ptr(), S, int(s0), C,
+              float(dist_last), float(eps), _f32(rgb_full, "rgb").data_ptr(), _f32(sigma_full, "sigma").data_ptr(),
+              _f32(T_run, "T").data_ptr(), alive.data_ptr(), _stream())
+    return alive
+
+
+def compact_indices(flags: Tensor, idx_in: Optional[Tensor] = None) -> Tensor:
+    """idx_in[flags != 0] in order (idx_in None: the positions), int32."""
+    flags = _chk(flags.reshape(-1), torch.uint8, "flags")
+    n = flags.numel()
+    if idx_in is not None:
+        idx_in = _chk(idx_in, torch.int32, "index list")
+        assert idx_in.numel() == n
+    out = torch.empty(n, device=flags.device, dtype=torch.int32)
+    count = torch.zeros(1, device=flags.device, dtype=torch.int64)
+    ws = torch.empty(max(int(_lib.load().dfn_compact_indices_workspace_bytes(n)), 16), device=flags.device, dtype=torch.uint8)
+    _lib.call("dfn_compact_indices", flags.data_ptr(), _ptr(idx_in), n, out.data_ptr(), count.data_ptr(), ws.data_ptr(), _stream())
+    return out[:int(count.item())]
+
+
 # ---- optimiser -------------------------------------------------------------------------------------
 def adamw_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, beta1_table: Tensor, step: Tensor,
                beta2=0.999, eps=1e-8, weight_decay=1e-6, grad_scale=1.0) -> None:

@@ -152,6 +152,18 @@ long long dfn_volume_points_workspace_bytes(long long n_voxels);
 int dfn_volume_points(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
                       const double* aabb_max, double* points, float* rgbs, long long* count, void* workspace, void* stream);
 
+/* ---- early ray termination for the inference render (BASELINE config 5; compositing = scripts/train.py:78-106) ---- */
+/* After the fine network has been queried on samples [s0, s0+C) of the n active rays (active [n] int32 ray ids or null =
+ * identity; seg_rgb [n,C,3], seg_sigma [n,C] in list order): scatter them into rgb_full [B,S,3] / sigma_full [B,S],
+ * T_run[ray] *= prod(1 - alpha + 1e-10) over the segment (train.py:89-95, last interval dist_last), alive[k] = T > eps. */
+int dfn_ert_update(const int* active, int n, const float* seg_rgb, const float* seg_sigma, const float* z, int S, int s0, int C,
+                   float dist_last, float eps, float* rgb_full, float* sigma_full, float* T_run, unsigned char* alive,
+                   void* stream);
+/* ordered compaction: idx_out = idx_in[flags != 0] (idx_in null = the positions themselves); *count device int64 */
+long long dfn_compact_indices_workspace_bytes(long long n);
+int dfn_compact_indices(const unsigned char* flags, const int* idx_in, long long n, int* idx_out, long long* count,
+                        void* workspace, void* stream);
+
 /* ---- optimiser (scripts/train.py:244-259, :321-322) ---------------------------------------------- */
 /* AdamW on a flat buffer; lr_table/beta1_table [table_len] hold the OneCycleLR schedule, *step_ptr (device int,
  * 0-based) selects the entry and is incremented. */

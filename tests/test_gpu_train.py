@@ -218,3 +218,89 @@ def test_checkpoint_layout_round_trip(D, tmp_path):
     opt = torch.optim.AdamW(ref_params, lr=5e-4, weight_decay=1e-6)
     opt.load_state_dict(ck["optimizer_state_dict"])
     assert len(ck["optimizer_state_dict"]["state"]) == 48
+
+
+# ---- inference render + early ray termination (BASELINE config 5) ------------------------------------
+def _render_setup(D, B, S, I, peak=True):
+    from common import make_draws, make_rays, make_state_dict, peaked
+    o, d, near, far, _ = make_rays(21, B)
+    t_rand, u = make_draws(22, B, S, I)
+    sdc, sdf = make_state_dict(41, 256), make_state_dict(42, 256)
+    if peak:
+        sdc, sdf = peaked(sdc), peaked(sdf)
+        sdf["density_layer.bias"] = sdf["density_layer.bias"] + 60.0   # a dense medium: rays saturate part-way through
+    mc, mf = D.get_nerf_models(device="cuda")
+    mc.load_state_dict(sdc)
+    mf.load_state_dict(sdf)
+    return (o, d, near, far, t_rand, u), (sdc, sdf), (mc.eval(), mf.eval())
+
+
+def test_render_rays_matches_oracle(D):
+    B, S, I = 96, 64, 128
+    (o, d, near, far, t_rand, u), (sdc, sdf), (mc, mf) = _render_setup(D, B, S, I)
+    cu = lambda t: t.cuda()  # noqa: E731
+    out = D.render_rays(mc, mf, cu(o), cu(d), cu(near), cu(far), S, I, t_rand=cu(t_rand), u=cu(u))
+    ref = O.render_losses(sdc, sdf, o, d, near, far, torch.zeros(B, 3), t_rand, u, low=torch.bfloat16)
+    assert out["evaluated_fraction"] == 1.0
+    assert torch.allclose(out["rgb_map_coarse"].cpu(), ref["rgb_map_coarse"].float(), atol=2e-2)   # bf16 MLP tolerance
+    assert torch.allclose(out["rgb_map"].cpu(), ref["rgb_map_fine"].float(), atol=2e-2)
+    assert bool((out["acc"] <= 1.0 + 1e-5).all()) and bool((out["z_vals"][:, 1:] >= out["z_vals"][:, :-1]).all())
+
+
+@pytest.mark.parametrize("segments", [2, 4, 7])
+def test_render_early_ray_termination(D, segments):
+    B, S, I = 3000, 64, 192
+    (o, d, near, far, t_rand, u), _, (mc, mf) = _render_setup(D, B, S, I)
+    cu = lambda t: t.cuda()  # noqa: E731
+    args = (mc, mf, cu(o), cu(d), cu(near), cu(far), S, I)
+    full = D.render_rays(*args, t_rand=cu(t_rand), u=cu(u))
+    eps = 1e-3
+    ert = D.render_rays(*args, t_rand=cu(t_rand), u=cu(u), ert_eps=eps, ert_segments=segments)
+    # the skipped samples carry at most T < eps of weight
+    assert float((ert["rgb_map"] - full["rgb_map"]).abs().max()) <= eps + 1e-6
+    assert torch.equal(ert["rgb_map_coarse"], full["rgb_map_coarse"]) and torch.equal(ert["z_vals"], full["z_vals"])
+    assert ert["evaluated_fraction"] < 1.0
+    # eps at the bottom of the fp32 range: only rays whose transmittance has underflowed leave; same picture
+    same = D.render_rays(*args, t_rand=cu(t_rand), u=cu(u), ert_eps=1e-30, ert_segments=segments)
+    assert same["evaluated_fraction"] > ert["evaluated_fraction"]
+    assert float((same["rgb_map"] - full["rgb_map"]).abs().max()) <= 1e-7
+
+
+def test_ert_update_and_compact_indices(D):
+    g = torch.Generator(device="cuda").manual_seed(1)
+    B, S, C, s0 = 1000, 96, 32, 32
+    z = torch.sort(torch.rand(B, S, device="cuda", generator=g) * 4 + 2, dim=1).values
+    flags = (torch.rand(B, device="cuda", generator=g) < 0.4).to(torch.uint8)
+    active = D.ops.compact_indices(flags)
+    assert torch.equal(active.long(), torch.nonzero(flags).reshape(-1))
+    sub = D.ops.compact_indices((active % 3 == 0).to(torch.uint8), active)
+    assert torch.equal(sub, active[active % 3 == 0])
+    assert D.ops.compact_indices(torch.zeros(5, device="cuda", dtype=torch.uint8)).numel() == 0
+    n = active.numel()
+    seg_rgb = torch.rand(n, C, 3, device="cuda", generator=g)
+    seg_sig = torch.rand(n, C, device="cuda", generator=g) * 3
+    rgb_full = torch.zeros(B, S, 3, device="cuda")
+    sig_full = torch.zeros(B, S, device="cuda")
+    T_run = torch.full((B,), 0.5, device="cuda")
+    alive = D.ops.ert_update(active, seg_rgb, seg_sig, z, s0, rgb_full, sig_full, T_run, eps=0.05)
+    ai = active.long()
+    dist = z[ai, s0 + 1:s0 + C + 1] - z[ai, s0:s0 + C]
+    want_T = 0.5 * torch.prod(1.0 - (1.0 - torch.exp(-seg_sig * dist)) + 1e-10, dim=1)
+    assert torch.allclose(T_run[ai], want_T, rtol=1e-5, atol=1e-7)
+    untouched = torch.ones(B, dtype=torch.bool, device="cuda")
+    untouched[ai] = False
+    assert bool((T_run[untouched] == 0.5).all()) and float(sig_full[untouched].abs().max()) == 0.0
+    assert torch.equal(sig_full[ai, s0:s0 + C], seg_sig) and torch.equal(rgb_full[ai, s0:s0 + C], seg_rgb)
+    assert torch.equal(alive.bool(), T_run[ai] > 0.05)
+
+
+def test_render_image_rows(D):
+    from common import make_cameras
+    (_, _, _, _, _, _), _, (mc, mf) = _render_setup(D, 8, 64, 128)
+    H, W, K, poses, _ = make_cameras(5, M=1, H=24, W=32)
+    img, info = D.render_image(mc, mf, H, W, K, poses[0], N_samples=64, N_importance=128, ert_eps=1e-3)
+    assert img.shape == (H, W, 3) and 0 < info["rays"] < H * W
+    r0, r1 = D.row_range(H, 1, 4)
+    part, _ = D.render_image(mc, mf, H, W, K, poses[0], rows=(r0, r1), N_samples=64, N_importance=128, ert_eps=1e-3)
+    assert part.shape == (r1 - r0, W, 3)
+    assert bool(torch.isfinite(img).all()) and float(img.min()) >= 0.0 and float(img.max()) <= 1.0

@@ -35,8 +35,14 @@ def _worker(rank, world, port, out):
     sl = shard_slice(B, rank, world)
     gsum = (2.0 * x[sl]).mean().reshape(1)                        # d/dw mean((w*x)^2)/... stand-in: per-rank mean
     dist.all_reduce(gsum)
+    # image rows of an inference render: every rank fills its rows of a zero image, a SUM all-reduce assembles the picture
+    H, W = 9, 4
+    r0, r1 = D.row_range(H, rank, world)
+    img = torch.zeros(H, W)
+    img[r0:r1] = torch.arange(H * W, dtype=torch.float32).reshape(H, W)[r0:r1]
+    dist.all_reduce(img)
     out[rank] = {"slab": (x0, x1), "thr": thr, "lo": float(lo), "hi": float(hi), "grad": float(gsum) / world,
-                 "rays": (sl.start, sl.stop)}
+                 "rays": (sl.start, sl.stop), "rows": (r0, r1), "img_ok": bool(torch.equal(img.reshape(-1), torch.arange(float(H * W))))}
     dist.destroy_process_group()
 
 
@@ -56,6 +62,7 @@ def test_two_rank_host_logic():
     assert out[0]["thr"] == X.otsu_from_histogram(hist, float(sigma.min()), float(sigma.max()))   # == single process
     assert out[0]["rays"] == (0, 4) and out[1]["rays"] == (4, 8)
     assert out[0]["grad"] == pytest.approx(float((2.0 * torch.arange(8.0)).mean()))
+    assert out[0]["rows"] == (0, 5) and out[1]["rows"] == (5, 9) and out[0]["img_ok"] and out[1]["img_ok"]
 
 
 def test_slab_ranges_cover_ragged_resolutions():
@@ -64,4 +71,13 @@ def test_slab_ranges_cover_ragged_resolutions():
         for world in (1, 2, 3, 8):
             edges = [X.slab_range(R, r, world) for r in range(world)]
             assert edges[0][0] == 0 and edges[-1][1] == R
+            assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+
+
+def test_row_ranges_cover_ragged_heights():
+    import deepfields_nerf_b200 as D
+    for H in (1, 7, 1080):
+        for world in (1, 2, 3, 8):
+            edges = [D.row_range(H, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == H
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
