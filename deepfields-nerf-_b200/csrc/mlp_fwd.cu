@@ -325,7 +325,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
           if (TRAIN && kUseStoreWarp) { mbar_wait(bar_stored(t), pst[t]); pst[t] ^= 1; }   // the store warp has read the previous tile out of act
 
           if (j < 9) {
-            float sdot = 0.f;
             const int c0 = hh * 128;
             uint32_t v0[32], v1[32], keep[64];
             tmem_ld32(tacc + c0, v0);
@@ -339,14 +338,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               uint32_t* pk = keep + cc * 16;
               if (j == 8) emit32<false>(cur, act, col0, row, pk);
               else emit32<true>(cur, act, col0, row, pk);
-              if (j == 7) {
-                const float* ws = consts + kConstWsig + col0;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                  sdot += bf16lo_to_f32(pk[i]) * ws[2 * i];
-                  sdot += bf16hi_to_f32(pk[i]) * ws[2 * i + 1];
-                }
-              }
               if (cc < 3) tmem_ld_wait();
             }
             publish(t);
@@ -359,7 +350,30 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
                 st_global_v4_hint(a.stash_m + ((static_cast<size_t>(j) * a.n_tiles + tile) << 12) + (hh * 128 + row) * 16, relu_bits16(keep),
                                   relu_bits16(keep + 16), relu_bits16(keep + 32), relu_bits16(keep + 48), pol);
             }
-            if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise))
+            if (j == 7) {  // sigma head: relu(round_bf16(w.h8 + b) (+ noise)), after the publish: the 256 FMAs per thread
+                           // would otherwise make this the longest epilogue of the chain.  Inference re-reads its own h8
+                           // values from the act tile (nobody overwrites them before this thread's next epilogue).
+              float sdot = 0.f;
+#pragma unroll
+              for (int cc = 0; cc < 4; ++cc) {
+                const int col0 = c0 + cc * 32;
+                uint32_t tmp[16];
+                const uint32_t* pk = keep + cc * 16;
+                if (!TRAIN) {
+#pragma unroll
+                  for (int g = 0; g < 4; ++g) {
+                    const uint4 q = *reinterpret_cast<const uint4*>(act + static_cast<uint32_t>(col0 / 8 + g) * kChunkBytes + row * 16);
+                    tmp[g * 4] = q.x; tmp[g * 4 + 1] = q.y; tmp[g * 4 + 2] = q.z; tmp[g * 4 + 3] = q.w;
+                  }
+                  pk = tmp;
+                }
+                const float* ws = consts + kConstWsig + col0;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  sdot += bf16lo_to_f32(pk[i]) * ws[2 * i];
+                  sdot += bf16hi_to_f32(pk[i]) * ws[2 * i + 1];
+                }
+              }
               if (hh == 1) part[(t * 128 + row) * 3] = sdot;
               named_bar_sync(1, kEpiThreads);
               if (hh == 0 && p < a.P) {
@@ -383,7 +397,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
               const int col0 = c0 + cc * 32;
               uint32_t* pk = keep + cc * 16;
               emit32<true>(cur, nullptr, col0, row, pk);
-              const float* w0 = consts + kConstWc2 + col0;
+            }
+            // next tile of this slot first: its pos-PE goes into aux (dir-PE was consumed by job 9's MMAs) and is published
+            // before the colour head is evaluated, which nobody on the chip waits for
+            if (ntile < a.n_tiles) {
+              write_pe_row(aux, nullptr, row, hh, xe, de);
+              publish(t);   // (no publish after the slot's last tile: nobody waits for it)
+            }
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+              const uint32_t* pk = keep + cc * 16;
+              const float* w0 = consts + kConstWc2 + c0 + cc * 32;
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
                 const float lo = bf16lo_to_f32(pk[i]), hi = bf16hi_to_f32(pk[i]);
@@ -391,11 +415,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
                 r1 += lo * w0[128 + 2 * i] + hi * w0[128 + 2 * i + 1];
                 r2 += lo * w0[256 + 2 * i] + hi * w0[256 + 2 * i + 1];
               }
-            }
-            // next tile of this slot: its pos-PE goes into aux (dir-PE was consumed by job 9's MMAs)
-            if (ntile < a.n_tiles) {
-              write_pe_row(aux, nullptr, row, hh, xe, de);
-              publish(t);   // (no publish after the slot's last tile: nobody waits for it)
             }
             if (TRAIN) stash_row<2>(st, c0, row, keep, pol);
             float* pr = part + (t * 128 + row) * 3;
