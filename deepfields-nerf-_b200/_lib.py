@@ -59,6 +59,8 @@ SIGNATURES = {
     "dfn_precompute_rays_workspace_bytes": (_ll, [_ll]),
     "dfn_precompute_rays": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_volume_points_workspace_bytes": (_ll, [_ll]),
+    "dfn_volume_points_count": (_i, [_p, _p, _i, _p, _p, _p, _p, _p]),
+    "dfn_volume_points_emit": (_i, [_p, _p, _i, _p, _p, _p, _p]),
     "dfn_volume_points": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_ert_update": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p, _p]),
     "dfn_compact_indices_workspace_bytes": (_ll, [_ll]),

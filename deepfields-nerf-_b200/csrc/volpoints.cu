@@ -130,26 +130,57 @@ __global__ void __launch_bounds__(kVoxThreads) emit_voxels_kernel(const VolArgs 
 
 extern "C" long long dfn_volume_points_workspace_bytes(long long n_voxels) { return dfn_compact::workspace_bytes(n_voxels) + 16; }
 
-extern "C" int dfn_volume_points(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
-                                 const double* aabb_max, double* points, float* rgbs, long long* count, void* workspace,
-                                 void* stream) {
-  DFN_CHECK_ARG(occupancy && rgb_volume && points && rgbs && count && workspace, "volume_points: null pointer");
+namespace {
+int fill_vol_args(VolArgs& a, const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
+                  const double* aabb_max) {
+  DFN_CHECK_ARG(occupancy && rgb_volume, "volume_points: null pointer");
   DFN_CHECK_ARG(R >= 2 && R <= 2048, "volume_points: resolution must be in [2, 2048]");
   DFN_CHECK_ARG((aabb_min == nullptr) == (aabb_max == nullptr), "volume_points: aabb_min and aabb_max go together");
-  VolArgs a{};
   a.occ = occupancy; a.rgb = rgb_volume; a.R = R; a.n = static_cast<long long>(R) * R * R;
   a.slice = aabb_min != nullptr;
   for (int c = 0; c < 3; ++c) { a.lo[c] = a.slice ? aabb_min[c] : 0.0; a.hi[c] = a.slice ? aabb_max[c] : 0.0; }   // HOST pointers
+  return DFN_OK;
+}
+unsigned int* rgb_max_of(void* workspace, long long n) {
+  return reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(workspace) + dfn_compact::workspace_bytes(n));
+}
+}  // namespace
+
+// pass 1 + scan: *count = number of points pass 2 will write (so that the caller can size its outputs)
+extern "C" int dfn_volume_points_count(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
+                                       const double* aabb_max, long long* count, void* workspace, void* stream) {
+  VolArgs a{};
+  if (int rc = fill_vol_args(a, occupancy, rgb_volume, R, aabb_min, aabb_max)) return rc;
+  DFN_CHECK_ARG(count && workspace, "volume_points: null pointer");
   const long long chunks = (a.n + kChunk - 1) / kChunk;
   const dfn_compact::Workspace w = dfn_compact::carve(workspace, a.n);
-  unsigned int* rgb_max = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(workspace) + dfn_compact::workspace_bytes(a.n));
+  unsigned int* rgb_max = rgb_max_of(workspace, a.n);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DFN_CUDA(cudaMemsetAsync(rgb_max, 0, 4, st), "volume_points");
   count_voxels_kernel<<<static_cast<unsigned int>(chunks), kVoxThreads, 0, st>>>(a, w.counts, w.ballots, rgb_max);
   DFN_CHECK_LAUNCH("volume_points(count)");
   scan_counts_kernel<<<1, 1024, 0, st>>>(w.counts, chunks, w.offsets, count);
   DFN_CHECK_LAUNCH("volume_points(scan)");
-  emit_voxels_kernel<<<static_cast<unsigned int>(chunks), kVoxThreads, 0, st>>>(a, w.offsets, w.ballots, rgb_max, points, rgbs);
+  return DFN_OK;
+}
+
+// pass 2 on the workspace dfn_volume_points_count filled for the same volume
+extern "C" int dfn_volume_points_emit(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, double* points,
+                                      float* rgbs, const void* workspace, void* stream) {
+  VolArgs a{};
+  if (int rc = fill_vol_args(a, occupancy, rgb_volume, R, nullptr, nullptr)) return rc;
+  DFN_CHECK_ARG(points && rgbs && workspace, "volume_points: null pointer");
+  const long long chunks = (a.n + kChunk - 1) / kChunk;
+  const dfn_compact::Workspace w = dfn_compact::carve(const_cast<void*>(workspace), a.n);
+  emit_voxels_kernel<<<static_cast<unsigned int>(chunks), kVoxThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      a, w.offsets, w.ballots, rgb_max_of(const_cast<void*>(workspace), a.n), points, rgbs);
   DFN_CHECK_LAUNCH("volume_points(emit)");
   return DFN_OK;
+}
+
+extern "C" int dfn_volume_points(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
+                                 const double* aabb_max, double* points, float* rgbs, long long* count, void* workspace,
+                                 void* stream) {
+  if (int rc = dfn_volume_points_count(occupancy, rgb_volume, R, aabb_min, aabb_max, count, workspace, stream)) return rc;
+  return dfn_volume_points_emit(occupancy, rgb_volume, R, points, rgbs, workspace, stream);
 }

@@ -388,17 +388,19 @@ def volume_points(occupancy: Tensor, rgb_volume: Tensor, aabb_min=None, aabb_max
         lo = np.ascontiguousarray(np.asarray(aabb_min, dtype=np.float64).reshape(3))
         hi = np.ascontiguousarray(np.asarray(aabb_max, dtype=np.float64).reshape(3))
     dev = occ.device
-    points = torch.empty(n, 3, device=dev, dtype=torch.float64)
-    rgbs = torch.empty(n, 3, device=dev, dtype=torch.float32)
     count = torch.zeros(1, device=dev, dtype=torch.int64)
     ws = torch.empty(int(_lib.load().dfn_volume_points_workspace_bytes(n)), device=dev, dtype=torch.uint8)
     with torch.cuda.device(dev):
-        _lib.call("dfn_volume_points", occ.data_ptr(), rgb.data_ptr(), R,
+        _lib.call("dfn_volume_points_count", occ.data_ptr(), rgb.data_ptr(), R,
                   lo.ctypes.data_as(ctypes.c_void_p) if lo is not None else None,
-                  hi.ctypes.data_as(ctypes.c_void_p) if hi is not None else None,
-                  points.data_ptr(), rgbs.data_ptr(), count.data_ptr(), ws.data_ptr(), _stream())
-    k = int(count.item())
-    return points[:k], rgbs[:k]
+                  hi.ctypes.data_as(ctypes.c_void_p) if hi is not None else None, count.data_ptr(), ws.data_ptr(), _stream())
+        k = int(count.item())                      # the outputs are sized by the count, not by R^3
+        points = torch.empty(k, 3, device=dev, dtype=torch.float64)
+        rgbs = torch.empty(k, 3, device=dev, dtype=torch.float32)
+        if k:
+            _lib.call("dfn_volume_points_emit", occ.data_ptr(), rgb.data_ptr(), R, points.data_ptr(), rgbs.data_ptr(), ws.data_ptr(),
+                      _stream())
+    return points, rgbs
 
 
 # ---- early ray termination (inference render) --------------------------------------------------------

@@ -149,6 +149,12 @@ int dfn_precompute_rays(const double* kinv, const double* poses, int M, int H, i
  * occupancy [R^3] u8, rgb_volume [R^3,3] u8 on the device; outputs sized for R^3 points; *count (device int64) = N;
  * workspace of dfn_volume_points_workspace_bytes(R^3) bytes. */
 long long dfn_volume_points_workspace_bytes(long long n_voxels);
+/* the two halves of dfn_volume_points, for callers that size their outputs by the count: _count fills the workspace and
+ * *count, _emit writes exactly that many points from the same workspace */
+int dfn_volume_points_count(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
+                            const double* aabb_max, long long* count, void* workspace, void* stream);
+int dfn_volume_points_emit(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, double* points, float* rgbs,
+                           const void* workspace, void* stream);
 int dfn_volume_points(const unsigned char* occupancy, const unsigned char* rgb_volume, int R, const double* aabb_min,
                       const double* aabb_max, double* points, float* rgbs, long long* count, void* workspace, void* stream);
 
