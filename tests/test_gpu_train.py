@@ -304,3 +304,39 @@ def test_render_image_rows(D):
     part, _ = D.render_image(mc, mf, H, W, K, poses[0], rows=(r0, r1), N_samples=64, N_importance=128, ert_eps=1e-3)
     assert part.shape == (r1 - r0, W, 3)
     assert bool(torch.isfinite(img).all()) and float(img.min()) >= 0.0 and float(img.max()) <= 1.0
+
+
+def test_mlp_backward_multi_iteration_equals_chunked(D):
+    """Size-independent property at a size where every CTA pair walks several tiles per slot (next-tile prologue, mask /
+    input prefetch across tiles, store-warp lockstep): one forward + backward over P points equals the same points
+    processed in chunks small enough for a single iteration per pair (the path checked against the oracle above) -
+    outputs bit for bit, parameter gradients up to the order of the fp32 atomic accumulation."""
+    P, chunk = 3 * 37888 + 77, 30000
+    sd = peaked(make_state_dict(77, 256), 3.0)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    pos = torch.rand(P, 3, device="cuda", generator=g) * 2 - 1
+    view = torch.nn.functional.normalize(torch.randn(P, 3, device="cuda", generator=g), dim=-1)
+    G_rgb = torch.randn(P, 3, device="cuda", generator=g) * 1e-3
+    G_sig = torch.randn(P, device="cuda", generator=g) * 1e-3
+    noise = torch.randn(P, device="cuda", generator=g)
+    pk = D.ops.PackedMLP("cuda")
+    pk.pack(flat_params(sd).cuda())
+
+    def run(sl):
+        n = sl.stop - sl.start
+        stash = torch.empty(D.ops.mlp_stash_bytes(n), dtype=torch.uint8, device="cuda")
+        dz = torch.empty(D.ops.mlp_dz_bytes(n), dtype=torch.uint8, device="cuda")
+        rgb, sig = D.ops.mlp_forward(pk, pos=pos[sl].contiguous(), view=view[sl].contiguous(), noise=noise[sl].contiguous(), stash=stash)
+        grads = torch.zeros(D.ops.MLP_NUM_PARAMS, device="cuda")
+        D.ops.mlp_backward(pk, rgb, sig, G_rgb[sl].contiguous(), G_sig[sl].contiguous(), stash, dz, grads,
+                           pos=pos[sl].contiguous(), view=view[sl].contiguous())
+        return rgb, sig, grads
+
+    rgb, sig, grads = run(slice(0, P))
+    parts = [run(slice(s, min(s + chunk, P))) for s in range(0, P, chunk)]
+    assert torch.equal(rgb, torch.cat([p[0] for p in parts])) and torch.equal(sig, torch.cat([p[1] for p in parts]))
+    want = torch.stack([p[2] for p in parts]).sum(0)
+    got, ref = split_flat(grads.cpu(), sd), split_flat(want.cpu(), sd)
+    for k in got:
+        assert rel_err(got[k], ref[k]) < 2e-3, (k, rel_err(got[k], ref[k]))
+    assert float(grads.abs().sum()) > 0
