@@ -115,8 +115,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
     else if (u < 8 * a.big_split + a.pe_split) { type = TYPE_PE; part = u - 8 * a.big_split; split = a.pe_split; }
     else { type = TYPE_COLOR; part = u - 8 * a.big_split - a.pe_split; split = a.col_split; }
   }
-  const int tile_begin = static_cast<int>(static_cast<long long>(nt) * part / split);
-  const int tile_end = static_cast<int>(static_cast<long long>(nt) * (part + 1) / split);
+  // tiles part, part + split, ...: all units walk the tile list front to back at about the same pace, so that the dZ5
+  // tiles the layer-4 unit and the PE unit both need are still in L2 for whichever of the two comes second
+  const int tile_begin = part, tile_end = nt, tile_step = split;
   // big job table: layer, input stash index, dz source
   const int big_layer = job < 3 ? job + 1 : (job == 3 ? 4 : (job < 7 ? job + 1 : 9));
   const int big_in = job < 7 ? big_layer - 1 : 7;  // stash_h index of the input activation
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
     if (lane == 0) {  // ================= producer =================
       int si = 0, sd = 0; uint32_t pi = 0, pd = 0;
       const uint64_t pol = make_evict_first_policy();   // stash and dz tiles are read exactly once here
-      for (int tile = tile_begin; tile < tile_end; ++tile) {
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
         if (type != TYPE_PE) {
           mbar_wait(bar_in_empty(si), pi ^ 1);
           mbar_arrive_expect_tx(bar_in_full(si), kInBytes);
@@ -175,7 +176,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
         for (int i = 0; i < n_dz; ++i) {
           mbar_wait(bar_dz_empty(sd), pd ^ 1);
           mbar_arrive_expect_tx(bar_dz_full(sd), kDzBytes);
-          bulk_g2s_hint(sbase + dz_off(sd), dz_src(tile, i), kDzBytes, bar_dz_full(sd), pol);
+          const bool shared_dz = (type == TYPE_BIG && big_layer == 4) || (type == TYPE_PE && i >= 2);   // dZ5: read by two units
+          if (shared_dz) bulk_g2s(sbase + dz_off(sd), dz_src(tile, i), kDzBytes, bar_dz_full(sd));
+          else bulk_g2s_hint(sbase + dz_off(sd), dz_src(tile, i), kDzBytes, bar_dz_full(sd), pol);
           if (++sd == n_dzs) { sd = 0; pd ^= 1; }
         }
       }
@@ -190,7 +193,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
           mma_bf16(tmem_base + tcol, smem_desc(a_addr + k * 256, 128, kChunkBytes), smem_desc(b_addr + k * 256, 128, kChunkBytes),
                    idesc, (first_tile && k == 0) ? 0u : 1u);
       };
-      for (int tile = tile_begin; tile < tile_end; ++tile) {
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
         const bool first = tile == tile_begin;
         const uint32_t in_addr = sbase + kOffIn + si * kInBytes;
         mbar_wait(bar_in_full(si), pi);
@@ -261,11 +264,11 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_wgrad_kernel(const WgradArgs 
     };
     if (tile_begin < tile_end) fetch_tile(tile_begin);
 
-    for (int tile = tile_begin; tile < tile_end; ++tile) {
-      float* small = s_small + (tile & 1) * 512;
+    for (int tile = tile_begin, itn = 0; tile < tile_end; tile += tile_step, ++itn) {
+      float* small = s_small + (itn & 1) * 512;
       const float g0 = gn[0], g1 = gn[1];
       const float x[3] = {xn[0], xn[1], xn[2]}, d[3] = {dn[0], dn[1], dn[2]};
-      if (tile + 1 < tile_end) fetch_tile(tile + 1);
+      if (tile + tile_step < tile_end) fetch_tile(tile + tile_step);
       if (need_small) {
         small[wt] = g0; small[wt + kWorkThreads] = g1;
         named_bar_sync(2, kWorkThreads);
