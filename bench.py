@@ -413,6 +413,51 @@ def run_ours(args):
                   "includes": "ray generation, cube test, coarse + fine MLP, resampling, compositing; synthetic opaque medium"}
         del mr_c, mr_f
 
+    # ---- Instant-NGP variant (config 3, scripts/instantngp.py): fused inference query, hash-grid encode and its backward ----
+    ngp = None
+    if rank == 0 and not args.no_extract:
+        torch.manual_seed(7)
+        net = D.InstantNGP("large").to(dev)
+        with torch.no_grad():
+            net.pos_encoding.params.uniform_(-1.0, 1.0)
+        gen = torch.Generator(device=dev).manual_seed(8)
+        Pn = 1 << 24                                   # 2^18 rays x 64 samples
+        pos_n = torch.rand(Pn, 3, device=dev, generator=gen)
+        dir_n = torch.rand(Pn, 3, device=dev, generator=gen)
+        table16, dw16, cw16 = net._half_params()
+
+        def timed(fn, reps=3):
+            fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) / reps
+
+        ms_q = timed(lambda: D.ops.ngp_forward(pos_n, dir_n, table16, net.grid, dw16, cw16))
+        Pe = 1 << 22
+        enc_holder = {}
+        ms_e = timed(lambda: enc_holder.__setitem__("e", D.ops.hashgrid_forward(pos_n[:Pe], table16, net.grid)))
+        d_enc = (torch.rand(Pe, 32, device=dev, generator=gen) - 0.5).half()
+        d_tab = torch.zeros(2 * net.grid.n_entries, device=dev)
+        ms_b = timed(lambda: D.ops.hashgrid_backward(pos_n[:Pe], d_enc, net.grid, d_table=d_tab))
+        gather = 16 * 8 * 4                            # 512 B of table gathers per point (upper bound)
+        ngp = {"metric": "ngp_query_points_per_s", "value": Pn / (ms_q * 1e-3), "unit": "points/s", "nerf_type": "large",
+               "points": Pn, "ms": ms_q, "table_mb_fp16": 4 * net.grid.n_entries / 1e6,
+               "algorithmic_gather_gbs": Pn * (gather + 24 + 38) / (ms_q * 1e-3) / 1e9,
+               "mlp_tflops": Pn * 2 * 9408 / (ms_q * 1e-3) / 1e12,
+               "hashgrid_forward": {"points": Pe, "ms": ms_e, "points_per_s": Pe / (ms_e * 1e-3),
+                                    "algorithmic_gbs": Pe * (gather + 12 + 64) / (ms_e * 1e-3) / 1e9},
+               "hashgrid_backward": {"points": Pe, "ms": ms_b, "points_per_s": Pe / (ms_b * 1e-3),
+                                     "algorithmic_gbs": Pe * (16 * 8 * 8 + 12 + 64) / (ms_b * 1e-3) / 1e9},
+               "note": "table gathers are served by L2 (26 MB table), so the GB/s are gather throughput, not HBM traffic; "
+                       "uniform random points = worst-case locality; parity unpinned (tiny-cuda-nn absent)",
+               "includes": "hash-grid encode + density MLP + SH4 + colour MLP in one launch, fp16 rgb + features written"}
+        del net, pos_n, dir_n, d_enc, d_tab, enc_holder
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, sample, cores = cpu_rate(args.cpu_budget)
@@ -440,6 +485,7 @@ def run_ours(args):
             "precompute_rays": raygen,
             "volume_points": volpts,
             "render": render,
+            "ngp": ngp,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -26,6 +26,15 @@ class PointSource(C.Structure):
     ]
 
 
+class HashGrid(C.Structure):
+    """struct dfn_hashgrid"""
+
+    _fields_ = [
+        ("scale", _f * 16), ("res", _u * 16), ("size", _u * 16), ("offset", _u * 16), ("n_entries", _ll),
+        ("log2_hashmap_size", _i),
+    ]
+
+
 # name -> (restype, argtypes); mirrors include/deepfields_b200.h one to one
 SIGNATURES = {
     "dfn_last_error": (C.c_char_p, []),
@@ -65,6 +74,11 @@ SIGNATURES = {
     "dfn_ert_update": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p, _p]),
     "dfn_compact_indices_workspace_bytes": (_ll, [_ll]),
     "dfn_compact_indices": (_i, [_p, _p, _ll, _p, _p, _p, _p]),
+    "dfn_hashgrid_init": (_ll, [C.POINTER(HashGrid), _i]),
+    "dfn_hashgrid_forward": (_i, [_p, _ll, _p, C.POINTER(HashGrid), _p, _p]),
+    "dfn_hashgrid_backward": (_i, [_p, _ll, _p, C.POINTER(HashGrid), _f, _p, _p]),
+    "dfn_sh4_encode": (_i, [_p, _ll, _p, _p]),
+    "dfn_ngp_forward": (_i, [_p, _p, _i, _ll, _p, C.POINTER(HashGrid), _p, _p, _p, _p, _p]),
     "dfn_adamw_step": (_i, [_p, _p, _p, _p, _ll, _p, _p, _p, _i, _f, _f, _f, _f, _p]),
 }
 

@@ -1,0 +1,452 @@
+// Instant-NGP variant (scripts/instantngp.py:7-104): multiresolution hash-grid encode + its scatter-add backward,
+// SH degree-4 direction encoding, and the two bias-free tiny MLPs (32->64->16 ReLU/ReLU, 32->64->64->3 ReLU/Sigmoid).
+//
+// The arithmetic the reference delegates to tiny-cuda-nn (un-vendored, commit 74ea173d) is restated from its published
+// algorithm (grid.h / common_device.h / spherical_harmonics.h / fully_fused_mlp.cu): parity is UNPINNED.
+// Documented choices where tcnn cannot be checked: the interpolation and the MLP accumulate in fp32 (tcnn: fp16) and
+// round to fp16 once per level / per layer.
+//
+// Kernels
+//   ngp_forward_kernel     inference: ONE launch, nothing but pos/dir in and rgb/features out touches HBM.  A warp owns
+//                          32 points; lane (g = lane/4, t = lane%4) encodes levels {t, t+4, t+8, t+12} of points
+//                          {g, g+8, g+16, g+24}, which IS the A-fragment layout of mma.m16n8k16, so the encoding never
+//                          leaves registers; each layer's accumulator fragments are re-packed into the next layer's A
+//                          fragments in registers too.  Weights (fp16) and the two smallest dense levels sit in shared
+//                          memory.  These 19 kFLOP/point MLPs are far below the tensor roofline, the kernel is bound by the
+//                          128 table gathers per point; that is why they run on mma.sync here rather than tcgen05.
+//   hashgrid_forward_kernel / hashgrid_backward_kernel   training path: thread per (point, level), level fastest, so the
+//                          [P,32] fp16 rows are written / read fully coalesced; backward = 8 float2 red.add per thread.
+//   sh4_kernel             direction encoding for the training path.
+#include "dfn_common.cuh"
+#include "../../include/deepfields_b200.h"
+#include <cuda_fp16.h>
+#include <math.h>
+
+namespace {
+
+constexpr int kLevels = DFN_NGP_LEVELS;
+constexpr uint32_t kPrimeY = 2654435761u, kPrimeZ = 805459861u;
+
+struct LevelDev {
+  float scale;
+  uint32_t res, size, offset, hashed;
+};
+struct GridDev {
+  LevelDev lv[kLevels];
+};
+
+GridDev to_dev(const dfn_hashgrid* g) {
+  GridDev d;
+  for (int l = 0; l < kLevels; ++l) {
+    d.lv[l].scale = g->scale[l];
+    d.lv[l].res = g->res[l];
+    d.lv[l].size = g->size[l];
+    d.lv[l].offset = g->offset[l];
+    d.lv[l].hashed = ((unsigned long long)g->res[l] * g->res[l] * g->res[l] > g->size[l]) ? 1u : 0u;
+  }
+  return d;
+}
+
+// tcnn grid_index<3>: dense x + y*res + z*res^2 while the stride fits, else the coherent prime hash; then % size
+// (size is a power of two on hashed levels).
+__device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, const LevelDev& L) {
+  if (L.hashed) return (x ^ (y * kPrimeY) ^ (z * kPrimeZ)) & (L.size - 1u);
+  uint32_t i = x + y * L.res + z * L.res * L.res;
+  return i < L.size ? i : i % L.size;
+}
+
+struct Cell {
+  uint32_t gx, gy, gz;
+  float fx, fy, fz;
+};
+// tcnn pos_fract: pos = fma(scale, x, 0.5); cell = floor(pos); frac = pos - cell
+__device__ __forceinline__ Cell locate(float px, float py, float pz, float scale) {
+  Cell c;
+  float x = __fmaf_rn(scale, px, 0.5f), y = __fmaf_rn(scale, py, 0.5f), z = __fmaf_rn(scale, pz, 0.5f);
+  float tx = floorf(x), ty = floorf(y), tz = floorf(z);
+  c.gx = (uint32_t)(int)tx, c.gy = (uint32_t)(int)ty, c.gz = (uint32_t)(int)tz;
+  c.fx = x - tx, c.fy = y - ty, c.fz = z - tz;
+  return c;
+}
+__device__ __forceinline__ float corner_weight(const Cell& c, int idx) {
+  float w = (idx & 1) ? c.fx : 1.0f - c.fx;
+  w = __fmul_rn(w, (idx & 2) ? c.fy : 1.0f - c.fy);
+  return __fmul_rn(w, (idx & 4) ? c.fz : 1.0f - c.fz);
+}
+
+// trilinear interpolation of one level; returns the two features as a packed half2 (low = feature 0)
+__device__ __forceinline__ uint32_t encode_level(const __half2* __restrict__ tab, const LevelDev& L, float px, float py, float pz) {
+  const Cell c = locate(px, py, pz, L.scale);
+  uint32_t raw[8];
+#pragma unroll
+  for (int idx = 0; idx < 8; ++idx) {
+    uint32_t i = grid_index(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
+    raw[idx] = *reinterpret_cast<const uint32_t*>(tab + i);
+  }
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+  for (int idx = 0; idx < 8; ++idx) {
+    const float w = corner_weight(c, idx);
+    const __half2 v = *reinterpret_cast<const __half2*>(&raw[idx]);
+    a0 = __fmaf_rn(w, __low2float(v), a0);
+    a1 = __fmaf_rn(w, __high2float(v), a1);
+  }
+  __half2 r = __floats2half2_rn(a0, a1);
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// ---- training-path kernels -------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hashgrid_forward_kernel(const float* __restrict__ pos, long long P,
+                                                               const __half2* __restrict__ table,
+                                                               const __grid_constant__ GridDev grid, uint32_t* __restrict__ out) {
+  __shared__ LevelDev lv[kLevels];
+  if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
+  __syncthreads();
+  const long long total = P * kLevels;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long p = i / kLevels;
+    const int l = (int)(i % kLevels);
+    const LevelDev L = lv[l];
+    out[i] = encode_level(table + L.offset, L, __ldg(pos + 3 * p), __ldg(pos + 3 * p + 1), __ldg(pos + 3 * p + 2));
+  }
+}
+
+__global__ void __launch_bounds__(256) hashgrid_backward_kernel(const float* __restrict__ pos, long long P,
+                                                                const uint32_t* __restrict__ d_out,
+                                                                const __grid_constant__ GridDev grid, float grad_scale,
+                                                                float2* __restrict__ d_table) {
+  __shared__ LevelDev lv[kLevels];
+  if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
+  __syncthreads();
+  const long long total = P * kLevels;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long p = i / kLevels;
+    const int l = (int)(i % kLevels);
+    const LevelDev L = lv[l];
+    const uint32_t raw = __ldg(d_out + i);
+    const __half2 dv = *reinterpret_cast<const __half2*>(&raw);
+    const float d0 = __low2float(dv) * grad_scale, d1 = __high2float(dv) * grad_scale;
+    if (d0 == 0.f && d1 == 0.f) continue;
+    const Cell c = locate(__ldg(pos + 3 * p), __ldg(pos + 3 * p + 1), __ldg(pos + 3 * p + 2), L.scale);
+#pragma unroll
+    for (int idx = 0; idx < 8; ++idx) {
+      const uint32_t j = grid_index(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
+      const float w = corner_weight(c, idx);
+      atomicAdd(d_table + L.offset + j, make_float2(w * d0, w * d1));  // red.global.add.v2.f32
+    }
+  }
+}
+
+// tcnn spherical_harmonics.h, degree 4; directions arrive in [0,1] and are mapped to [-1,1]
+__device__ __forceinline__ void sh4(float dx, float dy, float dz, float (&o)[16]) {
+  const float x = __fmaf_rn(dx, 2.f, -1.f), y = __fmaf_rn(dy, 2.f, -1.f), z = __fmaf_rn(dz, 2.f, -1.f);
+  const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+  o[0] = 0.28209479177387814f;
+  o[1] = -0.48860251190291987f * y;
+  o[2] = 0.48860251190291987f * z;
+  o[3] = -0.48860251190291987f * x;
+  o[4] = 1.0925484305920792f * xy;
+  o[5] = -1.0925484305920792f * yz;
+  o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+  o[7] = -1.0925484305920792f * xz;
+  o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+  o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+  o[10] = 2.8906114426405538f * xy * z;
+  o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+  o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+  o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+  o[14] = 1.4453057213202769f * z * (x2 - y2);
+  o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+}
+
+__global__ void __launch_bounds__(256) sh4_kernel(const float* __restrict__ dirs, long long P, __half* __restrict__ out) {
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (long long)gridDim.x * blockDim.x) {
+    float o[16];
+    sh4(__ldg(dirs + 3 * p), __ldg(dirs + 3 * p + 1), __ldg(dirs + 3 * p + 2), o);
+    uint32_t w[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      __half2 h = __floats2half2_rn(o[2 * k], o[2 * k + 1]);
+      w[k] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    st_global_v4(out + 16 * p, w[0], w[1], w[2], w[3]);
+    st_global_v4(out + 16 * p + 8, w[4], w[5], w[6], w[7]);
+  }
+}
+
+// ---- fused inference kernel ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t pack_h2_relu(float lo, float hi) { return pack_h2(fmaxf(lo, 0.f), fmaxf(hi, 0.f)); }
+
+// one bias-free layer on a 16-row tile: c[j] = A[16,K] * W[8j..8j+8, K]^T.  W in shared memory, row stride K+8 halves
+// (bank = 4g + t: conflict free).
+template <int K, int NT>
+__device__ __forceinline__ void layer(const uint32_t (&a)[K / 16][4], const __half* W, int g, int t, float (&c)[NT][4]) {
+  constexpr int LD = K + 8;
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    c[j][0] = c[j][1] = c[j][2] = c[j][3] = 0.f;
+#pragma unroll
+    for (int kb = 0; kb < K / 16; ++kb) {
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(W + (8 * j + g) * LD + 16 * kb + 2 * t);
+      mma16816(c[j], a[kb], w[0], w[4]);
+    }
+  }
+}
+// accumulator fragments of 2*KB n-tiles -> ReLU -> fp16 A fragments of the next layer (KB k-blocks)
+template <int KB>
+__device__ __forceinline__ void relu_repack(const float (&c)[2 * KB][4], uint32_t (&a)[KB][4]) {
+#pragma unroll
+  for (int kb = 0; kb < KB; ++kb) {
+    a[kb][0] = pack_h2_relu(c[2 * kb][0], c[2 * kb][1]);
+    a[kb][1] = pack_h2_relu(c[2 * kb][2], c[2 * kb][3]);
+    a[kb][2] = pack_h2_relu(c[2 * kb + 1][0], c[2 * kb + 1][1]);
+    a[kb][3] = pack_h2_relu(c[2 * kb + 1][2], c[2 * kb + 1][3]);
+  }
+}
+
+// shared-memory image of the weights (halves): dmlp W0 [64][40], W1 [16][72]; cmlp W0 [64][40], W1 [64][72], W2 [16][72]
+constexpr int kOffD0 = 0, kOffD1 = kOffD0 + 64 * 40, kOffC0 = kOffD1 + 16 * 72, kOffC1 = kOffC0 + 64 * 40,
+              kOffC2 = kOffC1 + 64 * 72, kWHalves = kOffC2 + 16 * 72;
+
+__device__ __forceinline__ void stage_weights(__half* dst, const __half* __restrict__ src, int rows, int K) {
+  for (int i = threadIdx.x; i < rows * K; i += blockDim.x) dst[(i / K) * (K + 8) + (i % K)] = src[i];
+}
+
+__global__ void __launch_bounds__(256, 2)
+ngp_forward_kernel(const float* __restrict__ pos, const float* __restrict__ dirs, int dirs_stride, long long P,
+                   const __half2* __restrict__ table, const __grid_constant__ GridDev grid,
+                   const __half* __restrict__ dmlp_w, const __half* __restrict__ cmlp_w, int smem_levels,
+                   __half* __restrict__ features, __half* __restrict__ rgb) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __half* W = reinterpret_cast<__half*>(smem_raw);
+  LevelDev* lv = reinterpret_cast<LevelDev*>(smem_raw + kWHalves * 2);
+  uint32_t* coarse = reinterpret_cast<uint32_t*>(smem_raw + kWHalves * 2 + kLevels * sizeof(LevelDev));
+
+  stage_weights(W + kOffD0, dmlp_w, 64, 32);
+  stage_weights(W + kOffD1, dmlp_w + 64 * 32, 16, 64);
+  stage_weights(W + kOffC0, cmlp_w, 64, 32);
+  stage_weights(W + kOffC1, cmlp_w + 64 * 32, 64, 64);
+  stage_weights(W + kOffC2, cmlp_w + 64 * 32 + 64 * 64, 16, 64);
+  if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
+  // the smallest dense levels (level 0: 16 KB, level 1: 54 KB) are gathered from shared memory
+  uint32_t coarse_entries = 0;
+  for (int l = 0; l < smem_levels; ++l) coarse_entries += grid.lv[l].size;
+  for (uint32_t i = threadIdx.x; i < coarse_entries; i += blockDim.x) coarse[i] = reinterpret_cast<const uint32_t*>(table)[i];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const long long n_tiles = (P + 31) / 32;
+  const long long warp_global = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+
+  for (long long tile = warp_global; tile < n_tiles; tile += warp_stride) {
+    const long long p0 = tile * 32;
+    // ---- hash-grid encode straight into A fragments: enc[m][kb][r] ----
+    uint32_t enc[2][2][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {  // rows g (+8)
+        long long p = p0 + 16 * m + 8 * h + g;
+        p = p < P ? p : P - 1;
+        const float px = __ldg(pos + 3 * p), py = __ldg(pos + 3 * p + 1), pz = __ldg(pos + 3 * p + 2);
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {  // levels 8kb + t (+4)
+            const int l = 8 * kb + 4 * q + t;
+            const LevelDev L = lv[l];
+            const __half2* tab = (l < smem_levels) ? reinterpret_cast<const __half2*>(coarse) + L.offset : table + L.offset;
+            enc[m][kb][2 * q + h] = encode_level(tab, L, px, py, pz);
+          }
+      }
+
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const long long pr0 = p0 + 16 * m + g, pr1 = pr0 + 8;
+      uint32_t cin[2][4];  // colour MLP input: k-block 0 = the 16 features, k-block 1 = SH
+      {
+        // ---- density MLP 32 -> 64 -> 16 ----
+        float c1[8][4];
+        layer<32, 8>(enc[m], W + kOffD0, g, t, c1);
+        uint32_t a1[4][4];
+        relu_repack<4>(c1, a1);
+        float c2[2][4];
+        layer<64, 2>(a1, W + kOffD1, g, t, c2);
+        uint32_t f[1][4];
+        relu_repack<1>(c2, f);  // output activation ReLU (instantngp.py:47); sigma = feature 0 (:79)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) cin[0][r] = f[0][r];
+        if (features != nullptr) {
+          if (pr0 < P) {
+            *reinterpret_cast<uint32_t*>(features + 16 * pr0 + 2 * t) = f[0][0];
+            *reinterpret_cast<uint32_t*>(features + 16 * pr0 + 8 + 2 * t) = f[0][2];
+          }
+          if (pr1 < P) {
+            *reinterpret_cast<uint32_t*>(features + 16 * pr1 + 2 * t) = f[0][1];
+            *reinterpret_cast<uint32_t*>(features + 16 * pr1 + 8 + 2 * t) = f[0][3];
+          }
+        }
+      }
+      if (rgb == nullptr) continue;
+      // ---- SH degree 4 of the two rows, columns 2t, 2t+1, 2t+8, 2t+9 ----
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        long long p = (h ? pr1 : pr0);
+        p = p < P ? p : P - 1;
+        const float* d = dirs + (long long)dirs_stride * p;
+        float o[16];
+        sh4(__ldg(d), __ldg(d + 1), __ldg(d + 2), o);
+        float s0 = o[0], s1 = o[1], s2 = o[8], s3 = o[9];
+        if (t == 1) s0 = o[2], s1 = o[3], s2 = o[10], s3 = o[11];
+        if (t == 2) s0 = o[4], s1 = o[5], s2 = o[12], s3 = o[13];
+        if (t == 3) s0 = o[6], s1 = o[7], s2 = o[14], s3 = o[15];
+        cin[1][h] = pack_h2(s0, s1);
+        cin[1][2 + h] = pack_h2(s2, s3);
+      }
+      // ---- colour MLP 32 -> 64 -> 64 -> 3 (padded to 16 rows; only n-tile 0 is needed) ----
+      uint32_t a2[4][4];
+      {
+        float c1[8][4];
+        layer<32, 8>(cin, W + kOffC0, g, t, c1);
+        uint32_t a1[4][4];
+        relu_repack<4>(c1, a1);
+        float c2[8][4];
+        layer<64, 8>(a1, W + kOffC1, g, t, c2);
+        relu_repack<4>(c2, a2);
+      }
+      float c3[1][4];
+      layer<64, 1>(a2, W + kOffC2, g, t, c3);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const long long p = h ? pr1 : pr0;
+        if (p >= P) continue;
+        const float v0 = 1.0f / (1.0f + __expf(-c3[0][2 * h])), v1 = 1.0f / (1.0f + __expf(-c3[0][2 * h + 1]));
+        if (t == 0) {
+          rgb[3 * p] = __float2half_rn(v0);
+          rgb[3 * p + 1] = __float2half_rn(v1);
+        } else if (t == 1) {
+          rgb[3 * p + 2] = __float2half_rn(v0);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+// ---- C ABI -------------------------------------------------------------------------------------------------------------
+extern "C" long long dfn_hashgrid_init(dfn_hashgrid* g, int log2_hashmap_size) {
+  if (g == nullptr || log2_hashmap_size < 4 || log2_hashmap_size > 24) {
+    dfn_set_error("dfn_hashgrid_init: log2_hashmap_size %d outside [4, 24]", log2_hashmap_size);
+    return -1;
+  }
+  // instantngp.py:23-33: 16 levels, 2 features, base resolution 16, per-level scale 1.5
+  // tcnn grid_scale = exp2(level * log2(1.5)) * 16 - 1, evaluated by tcnn with the device's exp2f (not reproducible
+  // offline); 16 * 1.5^level - 1 is exactly representable in fp32 for every level here, so the exact value is used.
+  unsigned long long off = 0;
+  float growth = 1.0f;
+  for (int l = 0; l < kLevels; ++l, growth *= 1.5f) {
+    const float scale = growth * 16.0f - 1.0f;
+    const unsigned res = (unsigned)ceilf(scale) + 1u;                 // tcnn grid_resolution
+    unsigned long long n = (unsigned long long)res * res * res;
+    n = (n + 7ull) / 8ull * 8ull;
+    if (n > (1ull << log2_hashmap_size)) n = 1ull << log2_hashmap_size;
+    g->scale[l] = scale;
+    g->res[l] = res;
+    g->size[l] = (unsigned)n;
+    g->offset[l] = (unsigned)off;
+    off += n;
+  }
+  g->n_entries = (long long)off;
+  g->log2_hashmap_size = log2_hashmap_size;
+  return (long long)off;
+}
+
+static int check_grid(const dfn_hashgrid* g, const char* who) {
+  DFN_CHECK_ARG(g != nullptr && g->n_entries > 0, "%s: grid descriptor not initialised (dfn_hashgrid_init)", who);
+  return DFN_OK;
+}
+static int blocks_for(long long work, int per_sm) {
+  long long b = (work + 255) / 256;
+  long long cap = (long long)dfn_num_sms() * per_sm;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+extern "C" int dfn_hashgrid_forward(const float* pos, long long P, const void* table_f16, const dfn_hashgrid* g, void* out_f16,
+                                    void* stream) {
+  if (int rc = check_grid(g, "dfn_hashgrid_forward")) return rc;
+  DFN_CHECK_ARG(P >= 0, "dfn_hashgrid_forward: P < 0");
+  if (P == 0) return DFN_OK;
+  DFN_CHECK_ARG(pos && table_f16 && out_f16, "dfn_hashgrid_forward: null pointer");
+  hashgrid_forward_kernel<<<blocks_for(P * kLevels, 8), 256, 0, (cudaStream_t)stream>>>(
+      pos, P, (const __half2*)table_f16, to_dev(g), (uint32_t*)out_f16);
+  DFN_CHECK_LAUNCH("dfn_hashgrid_forward");
+  return DFN_OK;
+}
+
+extern "C" int dfn_hashgrid_backward(const float* pos, long long P, const void* d_out_f16, const dfn_hashgrid* g, float grad_scale,
+                                     float* d_table, void* stream) {
+  if (int rc = check_grid(g, "dfn_hashgrid_backward")) return rc;
+  DFN_CHECK_ARG(P >= 0, "dfn_hashgrid_backward: P < 0");
+  if (P == 0) return DFN_OK;
+  DFN_CHECK_ARG(pos && d_out_f16 && d_table, "dfn_hashgrid_backward: null pointer");
+  DFN_CHECK_ARG(((uintptr_t)d_table & 7) == 0, "dfn_hashgrid_backward: d_table must be 8-byte aligned");
+  hashgrid_backward_kernel<<<blocks_for(P * kLevels, 8), 256, 0, (cudaStream_t)stream>>>(
+      pos, P, (const uint32_t*)d_out_f16, to_dev(g), grad_scale, (float2*)d_table);
+  DFN_CHECK_LAUNCH("dfn_hashgrid_backward");
+  return DFN_OK;
+}
+
+extern "C" int dfn_sh4_encode(const float* dirs, long long P, void* out_f16, void* stream) {
+  DFN_CHECK_ARG(P >= 0, "dfn_sh4_encode: P < 0");
+  if (P == 0) return DFN_OK;
+  DFN_CHECK_ARG(dirs && out_f16, "dfn_sh4_encode: null pointer");
+  sh4_kernel<<<blocks_for(P, 8), 256, 0, (cudaStream_t)stream>>>(dirs, P, (__half*)out_f16);
+  DFN_CHECK_LAUNCH("dfn_sh4_encode");
+  return DFN_OK;
+}
+
+extern "C" int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_stride, long long P, const void* table_f16,
+                               const dfn_hashgrid* g, const void* dmlp_w_f16, const void* cmlp_w_f16, void* features_f16,
+                               void* rgb_f16, void* stream) {
+  if (int rc = check_grid(g, "dfn_ngp_forward")) return rc;
+  DFN_CHECK_ARG(P >= 0, "dfn_ngp_forward: P < 0");
+  if (P == 0) return DFN_OK;
+  DFN_CHECK_ARG(pos && table_f16 && dmlp_w_f16 && cmlp_w_f16, "dfn_ngp_forward: null pointer");
+  DFN_CHECK_ARG(rgb_f16 == nullptr || dirs != nullptr, "dfn_ngp_forward: rgb requested without view directions");
+  DFN_CHECK_ARG(dirs_stride == 0 || dirs_stride == 3, "dfn_ngp_forward: dirs_stride must be 3 (per point) or 0 (one view)");
+  DFN_CHECK_ARG(features_f16 || rgb_f16, "dfn_ngp_forward: no output requested");
+  // dense levels that fit the shared-memory budget (two CTAs per SM): level 0 and 1 of the reference configuration
+  int smem_levels = 0;
+  size_t coarse_bytes = 0;
+  while (smem_levels < kLevels && (unsigned long long)g->res[smem_levels] * g->res[smem_levels] * g->res[smem_levels] <= g->size[smem_levels] &&
+         coarse_bytes + 4ull * g->size[smem_levels] <= 80 * 1024)
+    coarse_bytes += 4ull * g->size[smem_levels++];
+  const size_t smem = kWHalves * 2 + kLevels * sizeof(LevelDev) + coarse_bytes;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DFN_CUDA(cudaFuncSetAttribute(ngp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024), "dfn_ngp_forward");
+    attr_set = true;
+  }
+  const long long tiles = (P + 31) / 32;
+  long long blocks = (tiles + 7) / 8;
+  const long long cap = 2ll * dfn_num_sms();
+  if (blocks > cap) blocks = cap;
+  ngp_forward_kernel<<<(int)blocks, 256, smem, (cudaStream_t)stream>>>(pos, dirs, dirs_stride, P, (const __half2*)table_f16,
+                                                                        to_dev(g), (const __half*)dmlp_w_f16,
+                                                                        (const __half*)cmlp_w_f16, smem_levels,
+                                                                        (__half*)features_f16, (__half*)rgb_f16);
+  DFN_CHECK_LAUNCH("dfn_ngp_forward");
+  return DFN_OK;
+}

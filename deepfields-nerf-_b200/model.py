@@ -174,13 +174,114 @@ def get_nerf_models(pos_L=10, dir_L=4, hidden_dim=256, include_input_pos=True, i
     return coarse, fine
 
 
-class InstantNGP:
-    """scripts/instantngp.py:7-104.  Same constructor contract (ValueError for an unknown nerf_type, :9-21); the
-    hash-grid / SH / FullyFusedMLP arithmetic lives in tiny-cuda-nn (un-vendored submodule, commit 74ea173d), which
-    cannot be pinned here, so the variant is not built yet."""
+class _TcnnParams(nn.Module):
+    """Stands in for a tcnn.Encoding / tcnn.Network: one flat fp32 `params` tensor (tinycudann/modules.py), so the
+    state_dict keys are `pos_encoding.params`, `dir_encoding.params`, `dmlp.params`, `cmlp.params` like the reference."""
 
-    def __init__(self, nerf_type="large"):
-        if nerf_type not in ("small", "medium", "large"):
-            raise ValueError(f"Unknown nerf_type: {nerf_type}")
-        raise NotImplementedError("InstantNGP (tiny-cuda-nn semantics) is not built in this round: use ngp: false "
-                                  "(OptimizedVanillaNeRF); see DESIGN.md section 7")
+    def __init__(self, n_params, n_output_dims):
+        super().__init__()
+        self.n_output_dims = n_output_dims
+        self.params = nn.Parameter(torch.zeros(n_params, dtype=torch.float32))
+
+
+class _HashGridEncode(torch.autograd.Function):
+    """Hash-grid encode with its scatter-add backward (both hand-written kernels, csrc/ngp.cu)."""
+
+    @staticmethod
+    def forward(ctx, pos, params, grid):
+        ctx.grid = grid
+        ctx.save_for_backward(pos)
+        return ops.hashgrid_forward(pos, params.detach().half(), grid)
+
+    @staticmethod
+    def backward(ctx, d_out):
+        (pos,) = ctx.saved_tensors
+        return None, ops.hashgrid_backward(pos, d_out.contiguous(), ctx.grid), None
+
+
+class InstantNGP(nn.Module):
+    """scripts/instantngp.py:7-104.  Same constructor contract (ValueError for an unknown nerf_type, :9-21), same
+    submodule names, `query_density(pos) -> (sigma, features)` and `forward(pos, viewdirs) -> (rgb, sigma)` returning
+    fp16 like tcnn.  The arithmetic of tiny-cuda-nn (un-vendored, commit 74ea173d) is restated: parity unpinned
+    (DESIGN.md section 2).  Inference (no grad) is ONE fused launch (`dfn_ngp_forward`); with grad enabled the hash-grid
+    encode and its scatter-add backward are the kernels and the two 10 k-parameter MLPs run as plain fp16 library GEMMs
+    under autograd."""
+
+    LOG2_SIZE = {"small": 15, "medium": 17, "large": 19}
+
+    def __init__(self, nerf_type: str = "small"):
+        super().__init__()
+        if nerf_type not in self.LOG2_SIZE:
+            raise ValueError(f"Unkown {nerf_type=}")
+        self.nerf_type = nerf_type
+        self.grid = ops.hashgrid_levels(self.LOG2_SIZE[nerf_type])
+        self.pos_encoding = _TcnnParams(2 * self.grid.n_entries, 32)
+        self.dir_encoding = _TcnnParams(0, 16)
+        self.dmlp = _TcnnParams(ops.NGP_DMLP_PARAMS, 16)
+        self.cmlp = _TcnnParams(ops.NGP_CMLP_PARAMS, 3)
+        with torch.no_grad():  # tcnn initial_params: grid U(-1e-4, 1e-4), MLP layers Xavier-uniform
+            self.pos_encoding.params.uniform_(-1e-4, 1e-4)
+            for mod, shapes in ((self.dmlp, ((64, 32), (16, 64))), (self.cmlp, ((64, 32), (64, 64), (16, 64)))):
+                o = 0
+                for r, c in shapes:
+                    bound = (6.0 / (r + c)) ** 0.5
+                    mod.params[o:o + r * c].uniform_(-bound, bound)
+                    o += r * c
+        self._half = None
+
+    def _half_params(self):
+        """fp16 copies of the flat parameters (tcnn casts per call); rebuilt when a parameter changed."""
+        ps = (self.pos_encoding.params, self.dmlp.params, self.cmlp.params)
+        key = tuple((p.data_ptr(), p._version) for p in ps)
+        if self._half is None or self._half[0] != key:
+            self._half = (key, tuple(p.detach().half() for p in ps))
+        return self._half[1]
+
+    @staticmethod
+    def _flat(x, name):
+        if not x.is_cuda:
+            raise RuntimeError(f"InstantNGP: {name} must be a CUDA tensor (no CPU fallback)")
+        return x.reshape(-1, 3).float()
+
+    def _mlp(self, x, params, shapes, out_act):
+        o = 0
+        for k, (r, c) in enumerate(shapes):
+            w = params[o:o + r * c].view(r, c).half()
+            o += r * c
+            x = x @ w.t()
+            x = torch.relu(x) if k + 1 < len(shapes) else out_act(x)
+        return x
+
+    def _features_autograd(self, pos):
+        enc = _HashGridEncode.apply(pos, self.pos_encoding.params, self.grid)
+        return self._mlp(enc, self.dmlp.params, ((64, 32), (16, 64)), torch.relu)
+
+    def _training_path(self):
+        return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+
+    def query_density(self, pos):
+        """instantngp.py:66-80"""
+        pos = self._flat(pos, "pos")
+        if self._training_path():
+            features = self._features_autograd(pos)
+        else:
+            table, dw, cw = self._half_params()
+            _, features = ops.ngp_forward(pos, None, table, self.grid, dw, cw, want_features=True, want_rgb=False)
+        return features[:, :1], features
+
+    def forward(self, pos, viewdirs):
+        """instantngp.py:82-104"""
+        pos = self._flat(pos, "pos")
+        if self._training_path():
+            features = self._features_autograd(pos)
+            x = torch.cat([features, ops.sh4_encode(self._flat(viewdirs, "viewdirs"))], dim=-1)
+            rgb = self._mlp(x, self.cmlp.params, ((64, 32), (64, 64), (16, 64)), torch.sigmoid)[:, :3]
+            return rgb, features[:, :1]
+        table, dw, cw = self._half_params()
+        view = viewdirs.float()
+        if view.numel() != 3 and not (view.dim() == 2 and view.stride(0) == 0):
+            view = self._flat(view, "viewdirs")
+        else:
+            view = view.reshape(-1, 3)[0]  # an expanded canonical view (extract_vol.py:100) stays one direction
+        rgb, features = ops.ngp_forward(pos, view, table, self.grid, dw, cw)
+        return rgb, features[:, :1]

@@ -444,3 +444,86 @@ def adamw_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, bet
               _f32(v, "v").data_ptr(), p.numel(), _f32(lr_table, "lr_table").data_ptr(),
               _f32(beta1_table, "beta1_table").data_ptr(), step.data_ptr(), lr_table.numel(), float(beta2), float(eps),
               float(weight_decay), float(grad_scale), _stream())
+
+
+# ---- Instant-NGP variant (scripts/instantngp.py) ---------------------------------------------------
+NGP_LEVELS = 16
+NGP_DMLP_PARAMS = 64 * 32 + 16 * 64
+NGP_CMLP_PARAMS = 64 * 32 + 64 * 64 + 16 * 64
+
+
+def hashgrid_levels(log2_hashmap_size: int) -> "_lib.HashGrid":
+    """Level table of the reference's HashGrid config (instantngp.py:23-33).  Host only."""
+    g = _lib.HashGrid()
+    n = _lib.load().dfn_hashgrid_init(C.byref(g), int(log2_hashmap_size))
+    if n < 0:
+        raise ValueError(_lib.load().dfn_last_error().decode())
+    return g
+
+
+def _f16(t: Tensor, name: str) -> Tensor:
+    return _chk(t, torch.float16, name)
+
+
+def _pos(t: Tensor, name: str) -> Tensor:
+    t = _f32(t, name)
+    if t.dim() != 2 or t.shape[1] != 3:
+        raise ValueError(f"{name}: expected [P,3], got {tuple(t.shape)}")
+    return t
+
+
+def hashgrid_forward(pos: Tensor, table: Tensor, grid) -> Tensor:
+    """tcnn HashGrid encode (instantngp.py:77): pos [P,3] fp32, table fp16 [n_entries*2] -> fp16 [P,32]."""
+    pos, table = _pos(pos, "pos"), _f16(table, "table")
+    if table.numel() != 2 * grid.n_entries:
+        raise ValueError(f"table: expected {2 * grid.n_entries} values, got {table.numel()}")
+    out = torch.empty(pos.shape[0], 2 * NGP_LEVELS, device=pos.device, dtype=torch.float16)
+    _lib.call("dfn_hashgrid_forward", pos.data_ptr(), pos.shape[0], table.data_ptr(), C.byref(grid), out.data_ptr(), _stream())
+    return out
+
+
+def hashgrid_backward(pos: Tensor, d_out: Tensor, grid, grad_scale: float = 1.0, d_table: Optional[Tensor] = None) -> Tensor:
+    """Scatter-add backward of the encode: returns fp32 [n_entries*2] (accumulates into d_table when given)."""
+    pos, d_out = _pos(pos, "pos"), _f16(d_out, "d_out")
+    if d_out.shape != (pos.shape[0], 2 * NGP_LEVELS):
+        raise ValueError(f"d_out: expected {(pos.shape[0], 2 * NGP_LEVELS)}, got {tuple(d_out.shape)}")
+    if d_table is None:
+        d_table = torch.zeros(2 * grid.n_entries, device=pos.device, dtype=torch.float32)
+    else:
+        d_table = _f32(d_table, "d_table")
+    _lib.call("dfn_hashgrid_backward", pos.data_ptr(), pos.shape[0], d_out.data_ptr(), C.byref(grid), float(grad_scale),
+              d_table.data_ptr(), _stream())
+    return d_table
+
+
+def sh4_encode(dirs: Tensor) -> Tensor:
+    """tcnn SphericalHarmonics degree 4 (instantngp.py:34-40, :98): dirs [P,3] fp32 in [0,1] -> fp16 [P,16]."""
+    dirs = _pos(dirs, "dirs")
+    out = torch.empty(dirs.shape[0], 16, device=dirs.device, dtype=torch.float16)
+    _lib.call("dfn_sh4_encode", dirs.data_ptr(), dirs.shape[0], out.data_ptr(), _stream())
+    return out
+
+
+def ngp_forward(pos: Tensor, dirs: Optional[Tensor], table: Tensor, grid, dmlp_w: Tensor, cmlp_w: Tensor,
+                want_features: bool = True, want_rgb: bool = True):
+    """InstantNGP.forward / query_density as one launch (inference).  dirs [P,3] or a single [3] / [1,3] view.
+    Returns (rgb fp16 [P,3] | None, features fp16 [P,16] | None)."""
+    pos, table = _pos(pos, "pos"), _f16(table, "table")
+    dmlp_w, cmlp_w = _f16(dmlp_w, "dmlp_w"), _f16(cmlp_w, "cmlp_w")
+    if table.numel() != 2 * grid.n_entries or dmlp_w.numel() != NGP_DMLP_PARAMS or cmlp_w.numel() != NGP_CMLP_PARAMS:
+        raise ValueError("ngp_forward: parameter sizes do not match the reference configuration")
+    P = pos.shape[0]
+    stride = 3
+    if want_rgb:
+        if dirs is None:
+            raise ValueError("ngp_forward: rgb needs view directions")
+        dirs = _f32(dirs, "dirs")
+        if dirs.numel() == 3:
+            stride, dirs = 0, dirs.reshape(3)
+        elif dirs.shape != (P, 3):
+            raise ValueError(f"dirs: expected {(P, 3)} or a single direction, got {tuple(dirs.shape)}")
+    feat = torch.empty(P, 16, device=pos.device, dtype=torch.float16) if want_features else None
+    rgb = torch.empty(P, 3, device=pos.device, dtype=torch.float16) if want_rgb else None
+    _lib.call("dfn_ngp_forward", pos.data_ptr(), _ptr(dirs) if want_rgb else None, stride, P, table.data_ptr(), C.byref(grid),
+              dmlp_w.data_ptr(), cmlp_w.data_ptr(), _ptr(feat), _ptr(rgb), _stream())
+    return rgb, feat

@@ -177,6 +177,36 @@ int dfn_adamw_step(float* p, const float* g, float* m, float* v, long long n, co
                    const float* beta1_table, int* step_ptr, int table_len, float beta2, float eps, float weight_decay,
                    float grad_scale, void* stream);
 
+/* ---- Instant-NGP variant (scripts/instantngp.py:7-104; arithmetic of tiny-cuda-nn 74ea173d restated, parity unpinned) ---- */
+#define DFN_NGP_LEVELS 16
+/* Level table of the reference's HashGrid config (instantngp.py:23-33: 16 levels x 2 features, base resolution 16,
+ * per-level scale 1.5, log2_hashmap_size 15/17/19 for small/medium/large, :13-19).  size/offset count 2-feature entries. */
+typedef struct dfn_hashgrid {
+  float scale[DFN_NGP_LEVELS];
+  unsigned res[DFN_NGP_LEVELS];
+  unsigned size[DFN_NGP_LEVELS];
+  unsigned offset[DFN_NGP_LEVELS];
+  long long n_entries;
+  int log2_hashmap_size;
+} dfn_hashgrid;
+/* host only (no GPU needed): fills *g, returns the total number of entries (params = 2 x entries) or -1 */
+long long dfn_hashgrid_init(dfn_hashgrid* g, int log2_hashmap_size);
+/* self.pos_encoding(pos), instantngp.py:77: pos [P,3] fp32 in [0,1]^3, table fp16 [n_entries,2] -> out fp16 [P,32]
+ * (feature = 2*level + f) */
+int dfn_hashgrid_forward(const float* pos, long long P, const void* table_f16, const dfn_hashgrid* g, void* out_f16, void* stream);
+/* its backward: d_table [n_entries,2] fp32 += grad_scale * scatter(d_out fp16 [P,32]); the caller zeroes d_table */
+int dfn_hashgrid_backward(const float* pos, long long P, const void* d_out_f16, const dfn_hashgrid* g, float grad_scale,
+                          float* d_table, void* stream);
+/* self.dir_encoding(viewdirs), instantngp.py:98: SphericalHarmonics degree 4, dirs [P,3] fp32 in [0,1] -> fp16 [P,16] */
+int dfn_sh4_encode(const float* dirs, long long P, void* out_f16, void* stream);
+/* InstantNGP.forward / query_density in one launch (instantngp.py:66-104), inference: dmlp_w fp16 [64*32 + 16*64],
+ * cmlp_w fp16 [64*32 + 64*64 + 16*64] (tcnn FullyFusedMLP layout: row-major [out,in] per layer, no biases, last layer
+ * padded to 16 rows); dirs_stride 3 = per-point directions, 0 = one canonical view (extract_vol.py:100);
+ * features fp16 [P,16] (sigma = column 0) and/or rgb fp16 [P,3]; either output may be null. */
+int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_stride, long long P, const void* table_f16,
+                    const dfn_hashgrid* g, const void* dmlp_w_f16, const void* cmlp_w_f16, void* features_f16, void* rgb_f16,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif
