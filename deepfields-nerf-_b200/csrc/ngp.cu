@@ -74,15 +74,18 @@ __device__ __forceinline__ float corner_weight(const Cell& c, int idx) {
   return __fmul_rn(w, (idx & 4) ? c.fz : 1.0f - c.fz);
 }
 
-// trilinear interpolation of one level; returns the two features as a packed half2 (low = feature 0)
-__device__ __forceinline__ uint32_t encode_level(const __half2* __restrict__ tab, const LevelDev& L, float px, float py, float pz) {
-  const Cell c = locate(px, py, pz, L.scale);
-  uint32_t raw[8];
+// the 8 corner entries of one level (kGeneric: the table pointer may be shared memory)
+template <bool kGeneric>
+__device__ __forceinline__ void gather_level(const __half2* __restrict__ tab, const LevelDev& L, const Cell& c, uint32_t (&raw)[8]) {
 #pragma unroll
   for (int idx = 0; idx < 8; ++idx) {
-    uint32_t i = grid_index(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
-    raw[idx] = *reinterpret_cast<const uint32_t*>(tab + i);
+    const uint32_t i = grid_index(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(tab + i);
+    raw[idx] = kGeneric ? *p : __ldg(p);
   }
+}
+// trilinear blend, fp32 accumulate in corner order, one rounding to fp16; packed half2 (low = feature 0)
+__device__ __forceinline__ uint32_t blend_level(const Cell& c, const uint32_t (&raw)[8]) {
   float a0 = 0.f, a1 = 0.f;
 #pragma unroll
   for (int idx = 0; idx < 8; ++idx) {
@@ -93,6 +96,12 @@ __device__ __forceinline__ uint32_t encode_level(const __half2* __restrict__ tab
   }
   __half2 r = __floats2half2_rn(a0, a1);
   return *reinterpret_cast<uint32_t*>(&r);
+}
+__device__ __forceinline__ uint32_t encode_level(const __half2* __restrict__ tab, const LevelDev& L, float px, float py, float pz) {
+  const Cell c = locate(px, py, pz, L.scale);
+  uint32_t raw[8];
+  gather_level<false>(tab, L, c, raw);
+  return blend_level(c, raw);
 }
 
 // ---- training-path kernels -------------------------------------------------------------------------------------------
@@ -260,15 +269,23 @@ ngp_forward_kernel(const float* __restrict__ pos, const float* __restrict__ dirs
         long long p = p0 + 16 * m + 8 * h + g;
         p = p < P ? p : P - 1;
         const float px = __ldg(pos + 3 * p), py = __ldg(pos + 3 * p + 1), pz = __ldg(pos + 3 * p + 2);
+        // the lane's four levels 8kb + 4q + t of this point: all 32 gathers are issued before the first blend
+        Cell cell[4];
+        uint32_t raw[4][8];
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb)
-#pragma unroll
-          for (int q = 0; q < 2; ++q) {  // levels 8kb + t (+4)
-            const int l = 8 * kb + 4 * q + t;
-            const LevelDev L = lv[l];
+        for (int j = 0; j < 4; ++j) {
+          const int l = 8 * (j >> 1) + 4 * (j & 1) + t;
+          const LevelDev L = lv[l];
+          cell[j] = locate(px, py, pz, L.scale);
+          if (j == 0) {  // only levels 0..3 can be shared-memory resident
             const __half2* tab = (l < smem_levels) ? reinterpret_cast<const __half2*>(coarse) + L.offset : table + L.offset;
-            enc[m][kb][2 * q + h] = encode_level(tab, L, px, py, pz);
+            gather_level<true>(tab, L, cell[j], raw[j]);
+          } else {
+            gather_level<false>(table + L.offset, L, cell[j], raw[j]);
           }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) enc[m][j >> 1][2 * (j & 1) + h] = blend_level(cell[j], raw[j]);
       }
 
 #pragma unroll

@@ -13,7 +13,7 @@ import torch
 
 from . import ops
 from .config import load_config
-from .model import OptimizedVanillaNeRF
+from .model import InstantNGP, OptimizedVanillaNeRF
 
 
 def generate_3d_grid(bounds: Tuple[float, float], resolution: int, device="cuda") -> torch.Tensor:
@@ -137,6 +137,42 @@ def load_vanilla_model(checkpoint_path: str, cfg, device="cuda") -> OptimizedVan
     return model.eval()
 
 
+def load_instant_ngp_model(checkpoint_path: str, nerf_type: str = "large", device: str = "cuda") -> InstantNGP:
+    """extract_vol.py:20-54: same errors (FileNotFoundError :33-34, KeyError :51), model in eval mode on `device`."""
+    if not Path(checkpoint_path).exists():
+        raise FileNotFoundError(f"Checkpoint not found: {checkpoint_path}")
+    ckpt = torch.load(checkpoint_path, map_location=device, weights_only=False)
+    model = InstantNGP(nerf_type)
+    if "nerf_fine_state_dict" not in ckpt:
+        raise KeyError("Fine model state dict not found in checkpoint")
+    model.load_state_dict(ckpt["nerf_fine_state_dict"])
+    return model.to(device).eval()
+
+
+def extract_volume_ngp(model: InstantNGP, resolution: int, bounds=(-1.0, 1.0), view_direction=(0.0, 0.0, -1.0),
+                       rank: int = 0, world: int = 1, group=None, slab_points: int = 1 << 25):
+    """The slab-sharded dense query of extract_volume_fused for the Instant-NGP variant: grid points are generated on the
+    device in pieces of `slab_points` (never the 1.6 GB grid), each piece is ONE fused launch (extract_vol.py:85-120 with
+    the canonical view as a single direction, :100).  Same return tuple as extract_volume_fused."""
+    dev = next(model.parameters()).device
+    R = resolution
+    x0, x1 = slab_range(R, rank, world)
+    start, count = x0 * R * R, (x1 - x0) * R * R
+    lin = torch.linspace(bounds[0], bounds[1], R, device=dev)
+    view = torch.tensor(view_direction, dtype=torch.float32, device=dev)
+    view = view / torch.norm(view)
+    sigma = torch.empty(count, 1, device=dev, dtype=torch.float32)
+    rgb = torch.empty(count, 3, device=dev, dtype=torch.float32)
+    with torch.no_grad():
+        for s in range(0, count, slab_points):
+            n = min(slab_points, count - s)
+            c, d = model(ops.grid_points(lin, start + s, n), view)
+            sigma[s:s + n], rgb[s:s + n] = d.float(), c.float()
+    occ_b, thr = apply_otsu_threshold(sigma, group=group)
+    occ, col = ops.pack_volume(sigma, rgb, thr)
+    return sigma, rgb, start, thr, occ, col
+
+
 def get_args(argv=None):
     p = argparse.ArgumentParser(description="Dense occupancy / colour volume from a trained NeRF")
     p.add_argument("--cfg_path", type=str, required=True)
@@ -151,13 +187,15 @@ def get_args(argv=None):
 def main(argv=None):
     args = get_args(argv)
     cfg = load_config(args.cfg_path)
-    if getattr(cfg, "ngp", False):
-        raise NotImplementedError("cfg.ngp=true (tiny-cuda-nn) is not available; set ngp: false")
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
-    model = load_vanilla_model(str(cfg.checkpoint), cfg, dev)
     R = int(cfg.volume_resolution)
     with torch.no_grad():
-        sigma, rgb, _, thr, occ, col = extract_volume_fused(model, R, tuple(args.bounds), tuple(args.view_direction))
+        if getattr(cfg, "ngp", False):
+            model = load_instant_ngp_model(str(cfg.checkpoint), getattr(cfg, "nerf_type", "large"), dev)
+            sigma, rgb, _, thr, occ, col = extract_volume_ngp(model, R, tuple(args.bounds), tuple(args.view_direction))
+        else:
+            model = load_vanilla_model(str(cfg.checkpoint), cfg, dev)
+            sigma, rgb, _, thr, occ, col = extract_volume_fused(model, R, tuple(args.bounds), tuple(args.view_direction))
     stats = lambda t: {"min": float(t.min()), "max": float(t.max()), "mean": float(t.mean()), "std": float(t.std())}  # noqa: E731
     meta = {"checkpoint_path": str(cfg.checkpoint), "device_used": str(dev), "batch_size": int(args.batch_size),
             "density_stats": stats(sigma), "view_direction": list(args.view_direction), "rgb_stats": stats(rgb)}

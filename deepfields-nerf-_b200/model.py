@@ -269,8 +269,9 @@ class InstantNGP(nn.Module):
             _, features = ops.ngp_forward(pos, None, table, self.grid, dw, cw, want_features=True, want_rgb=False)
         return features[:, :1], features
 
-    def forward(self, pos, viewdirs):
-        """instantngp.py:82-104"""
+    def forward(self, pos, viewdirs, noise=None):
+        """instantngp.py:82-104.  `noise` (the vanilla model's injected sigma noise) is accepted and ignored: this variant
+        adds none (:77-80)."""
         pos = self._flat(pos, "pos")
         if self._training_path():
             features = self._features_autograd(pos)

@@ -337,8 +337,7 @@ def train(cfg_in):
     global cfg
     cfg = cfg_in
     if getattr(cfg, "ngp", False):
-        raise NotImplementedError("cfg.ngp=true needs tiny-cuda-nn semantics (parity unpinned, see DESIGN.md); "
-                                  "set ngp: false for the vanilla model")
+        return train_ngp(cfg)
     dist_on = "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1
     rank, world = 0, 1
     if dist_on:
@@ -369,6 +368,65 @@ def train(cfg_in):
         tr.save_checkpoint(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
         print(f"Training completed in {time.time() - t0:.2f}s")
     return tr
+
+
+def train_ngp(cfg_in):
+    """scripts/train.py:189-370 with cfg.ngp true (:219-220): ONE InstantNGP serves as coarse and fine model; AdamW +
+    OneCycleLR as :244-259.  The step runs under autograd: sampling, resampling, compositing and the hash-grid encode /
+    scatter-add backward are this library's kernels, the two tiny MLPs are fp16 library GEMMs.  Like the reference, world
+    coordinates and view directions go to the encodings unnormalised.  tiny-cuda-nn parity is unpinned."""
+    global cfg
+    cfg = cfg_in
+    from .model import InstantNGP
+    from .sampling import StratifiedSampler
+    dist_on = "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1
+    rank, world = 0, 1
+    if dist_on:
+        torch.distributed.init_process_group("nccl")
+        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    ckpt_dir = str(cfg.checkpoint_dir)
+    os.makedirs(ckpt_dir, exist_ok=True)
+    store = RayStore(str(cfg.rays_file), dev, rank, world)
+    steps_per_epoch = len(store) // cfg.batch_size
+    torch.manual_seed(0)
+    model = InstantNGP(getattr(cfg, "nerf_type", "large")).to(dev)
+    params = [p for p in model.parameters() if p.numel() > 0]
+    opt = torch.optim.AdamW(params, lr=cfg.lr, betas=(0.9, 0.999), weight_decay=1e-6, eps=1e-8)
+    sched = torch.optim.lr_scheduler.OneCycleLR(opt, max_lr=cfg.lr * 10, total_steps=max(cfg.num_epochs * steps_per_epoch, 1),
+                                                pct_start=0.1, anneal_strategy="cos", div_factor=10.0, final_div_factor=100.0)
+    sampler, criterion = StratifiedSampler(cfg.N_samples, dev), torch.nn.MSELoss()
+    scale = 128.0  # tcnn's default loss_scale for fp16 parameters (tinycudann/modules.py): keeps fp16 gradients normal
+
+    def save(path, epoch):
+        sd = model.state_dict()
+        torch.save({"iteration": epoch, "nerf_coarse_state_dict": sd, "nerf_fine_state_dict": sd,
+                    "optimizer_state_dict": opt.state_dict()}, path)
+
+    t0 = time.time()
+    for epoch in range(1, cfg.num_epochs + 1):
+        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size)):
+            opt.zero_grad(set_to_none=True)
+            total, lc, lf = forward_pass(model, model, o, d, near, far, rgb, sampler, criterion, dev, bool(cfg.white_bg))
+            (total * scale).backward()
+            for p in params:
+                if p.grad is not None:
+                    p.grad.mul_(1.0 / scale)
+                    if dist_on:
+                        torch.distributed.all_reduce(p.grad)
+                        p.grad.mul_(1.0 / world)
+            opt.step()
+            sched.step()
+            if it % 100 == 0 and rank == 0:
+                print(f"epoch {epoch} it {it}/{steps_per_epoch} loss {total.item():.5f} (c {lc.item():.5f} f {lf.item():.5f}) "
+                      f"psnr {-10.0 * math.log10(max(lf.item(), 1e-12)):.2f} {time.time() - t0:.1f}s")
+        if epoch % 2 == 0 and rank == 0:
+            save(os.path.join(ckpt_dir, f"nerf_epoch_{epoch:06d}.pth"), epoch)
+    if rank == 0:
+        save(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
+        print(f"Training completed in {time.time() - t0:.2f}s")
+    return model
 
 
 def main(argv=None):

@@ -75,9 +75,12 @@ def test_hashgrid_backward_is_adjoint_at_scale(D):
     pos = torch.rand(P, 3, device="cuda", generator=gen)
     tab = (torch.rand(2 * g.n_entries, device="cuda", generator=gen) - 0.5).half()
     d = (torch.rand(P, 32, device="cuda", generator=gen) - 0.5).half()
-    lhs = (D.ops.hashgrid_forward(pos, tab, g).double() * d.double()).sum().item()
+    enc = D.ops.hashgrid_forward(pos, tab, g)
+    lhs = (enc.double() * d.double()).sum().item()
     rhs = (D.ops.hashgrid_backward(pos, d, g).double() * tab.double()).sum().item()
-    assert abs(lhs - rhs) <= 1e-3 * max(1.0, abs(lhs))
+    # the two sides differ by the fp16 rounding of enc (2^-11 relative per term, random sign over 33 M terms: ~1e-7 of
+    # the absolute sum) and the fp32 atomics; one wrong corner or weight would show at ~1e-1 of it
+    assert abs(lhs - rhs) <= 1e-6 * (enc.double().abs() * d.double().abs()).sum().item()
 
 
 def test_sh4_matches_oracle(D):
