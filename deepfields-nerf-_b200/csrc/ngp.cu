@@ -30,6 +30,7 @@ constexpr uint32_t kPrimeY = 2654435761u, kPrimeZ = 805459861u;
 struct LevelDev {
   float scale;
   uint32_t res, size, offset, hashed;
+  uint32_t magic;  // floor(2^32 / size): branch-free i % size on the dense levels
 };
 struct GridDev {
   LevelDev lv[kLevels];
@@ -43,16 +44,23 @@ GridDev to_dev(const dfn_hashgrid* g) {
     d.lv[l].size = g->size[l];
     d.lv[l].offset = g->offset[l];
     d.lv[l].hashed = ((unsigned long long)g->res[l] * g->res[l] * g->res[l] > g->size[l]) ? 1u : 0u;
+    d.lv[l].magic = (uint32_t)((1ull << 32) / g->size[l]);
   }
   return d;
 }
 
 // tcnn grid_index<3>: dense x + y*res + z*res^2 while the stride fits, else the coherent prime hash; then % size
-// (size is a power of two on hashed levels).
+// (size is a power of two on hashed levels).  Both forms are branch-free: lanes of one warp work on different levels.
+__device__ __forceinline__ uint32_t index_hashed(uint32_t x, uint32_t y, uint32_t z, const LevelDev& L) {
+  return (x ^ (y * kPrimeY) ^ (z * kPrimeZ)) & (L.size - 1u);
+}
+__device__ __forceinline__ uint32_t index_dense(uint32_t x, uint32_t y, uint32_t z, const LevelDev& L) {
+  const uint32_t i = x + y * L.res + z * L.res * L.res;
+  uint32_t r = i - __umulhi(i, L.magic) * L.size;  // quotient estimate is exact or one short
+  return r >= L.size ? r - L.size : r;
+}
 __device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, const LevelDev& L) {
-  if (L.hashed) return (x ^ (y * kPrimeY) ^ (z * kPrimeZ)) & (L.size - 1u);
-  uint32_t i = x + y * L.res + z * L.res * L.res;
-  return i < L.size ? i : i % L.size;
+  return L.hashed ? index_hashed(x, y, z, L) : index_dense(x, y, z, L);
 }
 
 struct Cell {
@@ -74,22 +82,41 @@ __device__ __forceinline__ float corner_weight(const Cell& c, int idx) {
   return __fmul_rn(w, (idx & 4) ? c.fz : 1.0f - c.fz);
 }
 
-// the 8 corner entries of one level (kGeneric: the table pointer may be shared memory)
-template <bool kGeneric>
+// the 8 corner entries of one level (kGeneric: the table pointer may be shared memory).  kMode 1: the level is hashed for
+// every lane of the warp, 0: dense for every lane, 2: mixed (select).
+template <bool kGeneric, int kMode>
 __device__ __forceinline__ void gather_level(const __half2* __restrict__ tab, const LevelDev& L, const Cell& c, uint32_t (&raw)[8]) {
+  uint32_t hy[2], hz[2];
+  if (kMode == 1) {
+    hy[0] = c.gy * kPrimeY, hy[1] = hy[0] + kPrimeY;
+    hz[0] = c.gz * kPrimeZ, hz[1] = hz[0] + kPrimeZ;
+  }
 #pragma unroll
   for (int idx = 0; idx < 8; ++idx) {
-    const uint32_t i = grid_index(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
+    const uint32_t x = c.gx + (idx & 1), y = c.gy + ((idx >> 1) & 1), z = c.gz + ((idx >> 2) & 1);
+    uint32_t i;
+    if (kMode == 1) i = (x ^ hy[(idx >> 1) & 1] ^ hz[(idx >> 2) & 1]) & (L.size - 1u);
+    else if (kMode == 0) i = index_dense(x, y, z, L);
+    else i = grid_index(x, y, z, L);
     const uint32_t* p = reinterpret_cast<const uint32_t*>(tab + i);
     raw[idx] = kGeneric ? *p : __ldg(p);
   }
 }
+template <bool kGeneric>
+__device__ __forceinline__ void gather_level_uniform(const __half2* __restrict__ tab, const LevelDev& L, const Cell& c, uint32_t (&raw)[8]) {
+  const bool all_hashed = __all_sync(0xffffffffu, L.hashed != 0), all_dense = __all_sync(0xffffffffu, L.hashed == 0);
+  if (all_hashed) gather_level<kGeneric, 1>(tab, L, c, raw);
+  else if (all_dense) gather_level<kGeneric, 0>(tab, L, c, raw);
+  else gather_level<kGeneric, 2>(tab, L, c, raw);
+}
 // trilinear blend, fp32 accumulate in corner order, one rounding to fp16; packed half2 (low = feature 0)
 __device__ __forceinline__ uint32_t blend_level(const Cell& c, const uint32_t (&raw)[8]) {
   float a0 = 0.f, a1 = 0.f;
+  const float wxy[4] = {__fmul_rn(1.0f - c.fx, 1.0f - c.fy), __fmul_rn(c.fx, 1.0f - c.fy), __fmul_rn(1.0f - c.fx, c.fy),
+                        __fmul_rn(c.fx, c.fy)};
 #pragma unroll
   for (int idx = 0; idx < 8; ++idx) {
-    const float w = corner_weight(c, idx);
+    const float w = __fmul_rn(wxy[idx & 3], (idx & 4) ? c.fz : 1.0f - c.fz);  // == corner_weight(c, idx)
     const __half2 v = *reinterpret_cast<const __half2*>(&raw[idx]);
     a0 = __fmaf_rn(w, __low2float(v), a0);
     a1 = __fmaf_rn(w, __high2float(v), a1);
@@ -100,7 +127,7 @@ __device__ __forceinline__ uint32_t blend_level(const Cell& c, const uint32_t (&
 __device__ __forceinline__ uint32_t encode_level(const __half2* __restrict__ tab, const LevelDev& L, float px, float py, float pz) {
   const Cell c = locate(px, py, pz, L.scale);
   uint32_t raw[8];
-  gather_level<false>(tab, L, c, raw);
+  gather_level<false, 2>(tab, L, c, raw);
   return blend_level(c, raw);
 }
 
@@ -279,9 +306,9 @@ ngp_forward_kernel(const float* __restrict__ pos, const float* __restrict__ dirs
           cell[j] = locate(px, py, pz, L.scale);
           if (j == 0) {  // only levels 0..3 can be shared-memory resident
             const __half2* tab = (l < smem_levels) ? reinterpret_cast<const __half2*>(coarse) + L.offset : table + L.offset;
-            gather_level<true>(tab, L, cell[j], raw[j]);
+            gather_level_uniform<true>(tab, L, cell[j], raw[j]);
           } else {
-            gather_level<false>(table + L.offset, L, cell[j], raw[j]);
+            gather_level_uniform<false>(table + L.offset, L, cell[j], raw[j]);
           }
         }
 #pragma unroll
