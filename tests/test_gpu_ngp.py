@@ -142,3 +142,58 @@ def test_module_inference_equals_training_path_and_trains(D):
         a, _ = m(pos, v.expand(3000, 3))
         b, _ = m(pos, v.repeat(3000, 1))
     assert torch.equal(a, b)
+
+
+def test_extract_volume_ngp_matches_pointwise_query(D, tmp_path):
+    """extract_vol.py with cfg.ngp: the slab pieces of the fused path == the model called on the materialised grid
+    (extract_vol.py:57-120), slabs of two ranks concatenate to the single-rank result, checkpoint round trip."""
+    import sys
+    EV = sys.modules["deepfields_nerf_b200.extract_vol"]
+    torch.manual_seed(1)
+    m = D.InstantNGP("small").cuda()
+    with torch.no_grad():
+        m.pos_encoding.params.uniform_(-1.0, 1.0)
+    R = 24
+    sigma, rgb, start, thr, occ, col = EV.extract_volume_ngp(m, R, slab_points=5000)
+    pts = D.generate_3d_grid((-1.0, 1.0), R)
+    view = torch.tensor([0.0, 0.0, -1.0])
+    sig2, rgb2 = D.volume_extraction(m, pts, view, device="cuda")
+    assert start == 0 and sigma.shape == (R ** 3, 1) and rgb.shape == (R ** 3, 3)
+    assert torch.equal(sigma, sig2.float()) and torch.equal(rgb, rgb2.float())
+    assert occ.dtype == torch.uint8 and col.shape == (R ** 3, 3) and 0 < int(occ.sum()) < R ** 3
+    parts = [EV.extract_volume_ngp(m, R, rank=r, world=2) for r in range(2)]
+    assert torch.equal(torch.cat([p[0] for p in parts]), sigma) and parts[1][2] == (R // 2) * R * R
+    ck = tmp_path / "nerf_final.pth"
+    torch.save({"iteration": 3, "nerf_fine_state_dict": m.state_dict()}, ck)
+    m2 = EV.load_instant_ngp_model(str(ck), "small", "cuda")
+    assert not m2.training and torch.equal(m2.pos_encoding.params, m.pos_encoding.params)
+    with pytest.raises(FileNotFoundError):
+        EV.load_instant_ngp_model(str(tmp_path / "missing.pth"))
+    torch.save({"iteration": 3}, ck)
+    with pytest.raises(KeyError):
+        EV.load_instant_ngp_model(str(ck), "small", "cuda")
+
+
+def test_train_ngp_runs_and_learns(D, tmp_path):
+    """scripts/train.py with cfg.ngp true (:219-220): one InstantNGP as coarse and fine model through the reference's
+    forward_pass; the checkpoint has the reference's keys and the loss of a constant-colour scene drops."""
+    from types import SimpleNamespace
+    from common import make_rays
+    import sys
+    TR = sys.modules["deepfields_nerf_b200.train"]      # the package attribute `train` is the function
+    o, d, near, far, _ = make_rays(3, 2048)
+    rgbs = np.tile(np.array([[0.8, 0.3, 0.1]], np.float32), (2048, 1))
+    f = tmp_path / "rays.npz"
+    np.savez(f, rgbs=rgbs, rays_o=o.numpy(), rays_d=d.numpy(), t_near=near.numpy(), t_far=far.numpy())
+    cfg = SimpleNamespace(ngp=True, nerf_type="small", rays_file=str(f), checkpoint_dir=str(tmp_path / "ck"), batch_size=512,
+                          num_epochs=40, lr=1e-3, N_samples=32, N_importance=32, white_bg=False, chunk_size=32768)
+    model = TR.train(cfg)
+    ck = torch.load(tmp_path / "ck" / "nerf_final.pth", map_location="cpu", weights_only=False)
+    assert {"iteration", "nerf_coarse_state_dict", "nerf_fine_state_dict", "optimizer_state_dict"} <= set(ck)
+    assert list(ck["nerf_fine_state_dict"]) == ["pos_encoding.params", "dir_encoding.params", "dmlp.params", "cmlp.params"]
+    sampler = D.StratifiedSampler(32, "cuda")
+    cu = lambda t: t.cuda()  # noqa: E731
+    with torch.no_grad():
+        _, _, lf = TR.forward_pass(model, model, cu(o), cu(d), cu(near), cu(far), torch.from_numpy(rgbs).cuda(), sampler,
+                                   torch.nn.MSELoss(), "cuda", False)
+    assert float(lf) < 0.1, float(lf)      # an untrained model renders black: MSE = mean(target^2) = 0.247
