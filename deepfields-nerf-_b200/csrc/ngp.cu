@@ -91,15 +91,30 @@ __device__ __forceinline__ void gather_level(const __half2* __restrict__ tab, co
     hy[0] = c.gy * kPrimeY, hy[1] = hy[0] + kPrimeY;
     hz[0] = c.gz * kPrimeZ, hz[1] = hz[0] + kPrimeZ;
   }
+  // The corners come in x pairs (x, x+1).  Whenever the two entries are the halves of one aligned 8-byte word (always on
+  // a dense level with even x, and on a hashed level with even x because (x+1)^h == (x^h)^1) one 8-byte load fetches
+  // both: a quarter fewer L1 wavefronts on average, same values, same accumulation order.
 #pragma unroll
-  for (int idx = 0; idx < 8; ++idx) {
-    const uint32_t x = c.gx + (idx & 1), y = c.gy + ((idx >> 1) & 1), z = c.gz + ((idx >> 2) & 1);
-    uint32_t i;
-    if (kMode == 1) i = (x ^ hy[(idx >> 1) & 1] ^ hz[(idx >> 2) & 1]) & (L.size - 1u);
-    else if (kMode == 0) i = index_dense(x, y, z, L);
-    else i = grid_index(x, y, z, L);
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(tab + i);
-    raw[idx] = kGeneric ? *p : __ldg(p);
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t y = c.gy + (k & 1), z = c.gz + (k >> 1);
+    uint32_t i0, i1;
+    if (kMode == 1) {
+      const uint32_t h = hy[k & 1] ^ hz[k >> 1];
+      i0 = (c.gx ^ h) & (L.size - 1u), i1 = ((c.gx + 1u) ^ h) & (L.size - 1u);
+    } else if (kMode == 0) {
+      i0 = index_dense(c.gx, y, z, L), i1 = index_dense(c.gx + 1u, y, z, L);
+    } else {
+      i0 = grid_index(c.gx, y, z, L), i1 = grid_index(c.gx + 1u, y, z, L);
+    }
+    const uint2* p8 = reinterpret_cast<const uint2*>(tab + (i0 & ~1u));
+    const uint2 w = kGeneric ? *p8 : __ldg(p8);
+    raw[2 * k] = (i0 & 1u) ? w.y : w.x;
+    uint32_t other = (i0 & 1u) ? w.x : w.y;
+    if (i1 != (i0 ^ 1u)) {
+      const uint32_t* p4 = reinterpret_cast<const uint32_t*>(tab + i1);
+      other = kGeneric ? *p4 : __ldg(p4);
+    }
+    raw[2 * k + 1] = other;
   }
 }
 template <bool kGeneric>
@@ -258,7 +273,12 @@ __device__ __forceinline__ void stage_weights(__half* dst, const __half* __restr
   for (int i = threadIdx.x; i < rows * K; i += blockDim.x) dst[(i / K) * (K + 8) + (i % K)] = src[i];
 }
 
-__global__ void __launch_bounds__(256, 2)
+#ifndef DFN_NGP_THREADS
+#define DFN_NGP_THREADS 256  // bring-up override: -DDFN_NGP_THREADS=320 trades registers (96) for warps (20 per SM)
+#endif
+constexpr int kNgpThreads = DFN_NGP_THREADS, kNgpWarps = kNgpThreads / 32;
+
+__global__ void __launch_bounds__(kNgpThreads, 2)
 ngp_forward_kernel(const float* __restrict__ pos, const float* __restrict__ dirs, int dirs_stride, long long P,
                    const __half2* __restrict__ table, const __grid_constant__ GridDev grid,
                    const __half* __restrict__ dmlp_w, const __half* __restrict__ cmlp_w, int smem_levels,
@@ -433,6 +453,7 @@ extern "C" int dfn_hashgrid_forward(const float* pos, long long P, const void* t
   DFN_CHECK_ARG(P >= 0, "dfn_hashgrid_forward: P < 0");
   if (P == 0) return DFN_OK;
   DFN_CHECK_ARG(pos && table_f16 && out_f16, "dfn_hashgrid_forward: null pointer");
+  DFN_CHECK_ARG(((uintptr_t)table_f16 & 7) == 0, "dfn_hashgrid_forward: table must be 8-byte aligned");
   hashgrid_forward_kernel<<<blocks_for(P * kLevels, 8), 256, 0, (cudaStream_t)stream>>>(
       pos, P, (const __half2*)table_f16, to_dev(g), (uint32_t*)out_f16);
   DFN_CHECK_LAUNCH("dfn_hashgrid_forward");
@@ -468,6 +489,7 @@ extern "C" int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_str
   DFN_CHECK_ARG(P >= 0, "dfn_ngp_forward: P < 0");
   if (P == 0) return DFN_OK;
   DFN_CHECK_ARG(pos && table_f16 && dmlp_w_f16 && cmlp_w_f16, "dfn_ngp_forward: null pointer");
+  DFN_CHECK_ARG(((uintptr_t)table_f16 & 7) == 0, "dfn_ngp_forward: table must be 8-byte aligned");
   DFN_CHECK_ARG(rgb_f16 == nullptr || dirs != nullptr, "dfn_ngp_forward: rgb requested without view directions");
   DFN_CHECK_ARG(dirs_stride == 0 || dirs_stride == 3, "dfn_ngp_forward: dirs_stride must be 3 (per point) or 0 (one view)");
   DFN_CHECK_ARG(features_f16 || rgb_f16, "dfn_ngp_forward: no output requested");
@@ -484,10 +506,10 @@ extern "C" int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_str
     attr_set = true;
   }
   const long long tiles = (P + 31) / 32;
-  long long blocks = (tiles + 7) / 8;
+  long long blocks = (tiles + kNgpWarps - 1) / kNgpWarps;
   const long long cap = 2ll * dfn_num_sms();
   if (blocks > cap) blocks = cap;
-  ngp_forward_kernel<<<(int)blocks, 256, smem, (cudaStream_t)stream>>>(pos, dirs, dirs_stride, P, (const __half2*)table_f16,
+  ngp_forward_kernel<<<(int)blocks, kNgpThreads, smem, (cudaStream_t)stream>>>(pos, dirs, dirs_stride, P, (const __half2*)table_f16,
                                                                         to_dev(g), (const __half*)dmlp_w_f16,
                                                                         (const __half*)cmlp_w_f16, smem_levels,
                                                                         (__half*)features_f16, (__half*)rgb_f16);
