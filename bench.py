@@ -444,6 +444,39 @@ def run_ours(args):
         d_enc = (torch.rand(Pe, 32, device=dev, generator=gen) - 0.5).half()
         d_tab = torch.zeros(2 * net.grid.n_entries, device=dev)
         ms_b = timed(lambda: D.ops.hashgrid_backward(pos_n[:Pe], d_enc, net.grid, d_table=d_tab))
+        # one training step of the cfg.ngp path (train.train_ngp): ONE InstantNGP as coarse and fine model through the
+        # reference's forward_pass, loss scale 128, AdamW; 2^16 rays x (64 + 192) points (a quarter of config 3's 2^18-ray
+        # batch, to bound the autograd memory); the tiny MLPs of this path are fp16 library GEMMs
+        ngp_train = None
+        try:
+            from types import SimpleNamespace
+            from common import make_rays
+            TRm = sys.modules["deepfields_nerf_b200.train"]
+            cfg_saved = getattr(TRm, "cfg", None)
+            TRm.cfg = SimpleNamespace(N_samples=S_COARSE, N_importance=N_IMPORTANCE, chunk_size=32768)
+            Bn = 1 << 16
+            o_n, d_n, near_n, far_n, tgt_n = (t.to(dev) for t in make_rays(9, Bn))
+            smp, crit = D.StratifiedSampler(S_COARSE, dev), torch.nn.MSELoss()
+            prm = [p_ for p_ in net.parameters() if p_.numel() > 0]
+            opt_n = torch.optim.AdamW(prm, lr=5e-4, weight_decay=1e-6, eps=1e-8)
+
+            def ngp_step():
+                opt_n.zero_grad(set_to_none=True)
+                tot, _, _ = TRm.forward_pass(net, net, o_n, d_n, near_n, far_n, tgt_n, smp, crit, dev, False)
+                (tot * 128.0).backward()
+                for p_ in prm:
+                    p_.grad.mul_(1.0 / 128.0)
+                opt_n.step()
+
+            ms_t = timed(ngp_step, reps=3)
+            TRm.cfg = cfg_saved
+            ngp_train = {"rays": Bn, "points": Bn * (S_COARSE + T_FINE), "ms": ms_t, "rays_per_s": Bn / (ms_t * 1e-3),
+                         "path": "autograd: sampling / encode / scatter-add backward / compositing kernels of this library + "
+                                 "fp16 library GEMMs for the two tiny MLPs + torch AdamW"}
+            del o_n, d_n, near_n, far_n, tgt_n, opt_n, prm
+        except Exception as e:  # an auxiliary measurement must not take the headline line down with it
+            ngp_train = {"error": f"{type(e).__name__}: {e}"[:300]}
+        table16, dw16, cw16 = net._half_params()
         gather = 16 * 8 * 4                            # 512 B of table gathers per point (upper bound)
         ngp = {"metric": "ngp_query_points_per_s", "value": Pn / (ms_q * 1e-3), "unit": "points/s", "nerf_type": "large",
                "points": Pn, "ms": ms_q, "table_mb_fp16": 4 * net.grid.n_entries / 1e6,
@@ -453,6 +486,7 @@ def run_ours(args):
                                     "algorithmic_gbs": Pe * (gather + 12 + 64) / (ms_e * 1e-3) / 1e9},
                "hashgrid_backward": {"points": Pe, "ms": ms_b, "points_per_s": Pe / (ms_b * 1e-3),
                                      "algorithmic_gbs": Pe * (16 * 8 * 8 + 12 + 64) / (ms_b * 1e-3) / 1e9},
+               "train_step": ngp_train,
                "note": "table gathers are served by L2 (26 MB table), so the GB/s are gather throughput, not HBM traffic; "
                        "uniform random points = worst-case locality; parity unpinned (tiny-cuda-nn absent)",
                "includes": "hash-grid encode + density MLP + SH4 + colour MLP in one launch, fp16 rgb + features written"}
