@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) hashgrid_forward_kernel(const float* __re
 __global__ void __launch_bounds__(256) hashgrid_backward_kernel(const float* __restrict__ pos, long long P,
                                                                 const uint32_t* __restrict__ d_out,
                                                                 const __grid_constant__ GridDev grid, float grad_scale,
-                                                                float2* __restrict__ d_table) {
+                                                                int first_level, float2* __restrict__ d_table) {
   __shared__ LevelDev lv[kLevels];
   if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
   __syncthreads();
@@ -173,6 +173,7 @@ __global__ void __launch_bounds__(256) hashgrid_backward_kernel(const float* __r
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long p = i / kLevels;
     const int l = (int)(i % kLevels);
+    if (l < first_level) continue;  // those levels are reduced in shared memory by hashgrid_backward_coarse_kernel
     const LevelDev L = lv[l];
     const uint32_t raw = __ldg(d_out + i);
     const __half2 dv = *reinterpret_cast<const __half2*>(&raw);
@@ -194,6 +195,44 @@ __global__ void __launch_bounds__(256) hashgrid_backward_kernel(const float* __r
         atomicAdd(base + i1, make_float2(w1 * d0, w1 * d1));
       }
     }
+  }
+}
+
+// The smallest dense levels (level 0: 4 096 entries, level 1: 13 824) take 8 atomics per point each: in global memory
+// that is thousands of reductions per address (measured: level 0 alone 17 % of the backward).  One persistent CTA per SM
+// accumulates them in shared memory and flushes once with 16-byte vector reductions.
+__global__ void __launch_bounds__(1024, 1) hashgrid_backward_coarse_kernel(const float* __restrict__ pos, long long P,
+                                                                           const uint32_t* __restrict__ d_out,
+                                                                           const __grid_constant__ GridDev grid, float grad_scale,
+                                                                           int n_lv, uint32_t n_entries, float2* __restrict__ d_table) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* acc = reinterpret_cast<float2*>(smem_raw);
+  __shared__ LevelDev lv[kLevels];
+  if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
+  for (uint32_t i = threadIdx.x; i < n_entries; i += blockDim.x) acc[i] = make_float2(0.f, 0.f);
+  __syncthreads();
+  const long long total = P * n_lv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long p = i / n_lv;
+    const int l = (int)(i % n_lv);
+    const LevelDev L = lv[l];
+    const uint32_t raw = __ldg(d_out + p * kLevels + l);
+    const __half2 dv = *reinterpret_cast<const __half2*>(&raw);
+    const float d0 = __low2float(dv) * grad_scale, d1 = __high2float(dv) * grad_scale;
+    if (d0 == 0.f && d1 == 0.f) continue;
+    const Cell c = locate(__ldg(pos + 3 * p), __ldg(pos + 3 * p + 1), __ldg(pos + 3 * p + 2), L.scale);
+#pragma unroll
+    for (int idx = 0; idx < 8; ++idx) {
+      const uint32_t j = L.offset + index_dense(c.gx + (idx & 1), c.gy + ((idx >> 1) & 1), c.gz + ((idx >> 2) & 1), L);
+      const float w = corner_weight(c, idx);
+      atomicAdd(&acc[j].x, w * d0);
+      atomicAdd(&acc[j].y, w * d1);
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n_entries / 2; i += blockDim.x) {  // level sizes are multiples of 8 entries
+    const float4 v = reinterpret_cast<const float4*>(acc)[i];
+    if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) atomicAdd(reinterpret_cast<float4*>(d_table) + i, v);
   }
 }
 
@@ -476,8 +515,29 @@ extern "C" int dfn_hashgrid_backward(const float* pos, long long P, const void* 
   if (P == 0) return DFN_OK;
   DFN_CHECK_ARG(pos && d_out_f16 && d_table, "dfn_hashgrid_backward: null pointer");
   DFN_CHECK_ARG(((uintptr_t)d_table & 15) == 0, "dfn_hashgrid_backward: d_table must be 16-byte aligned");
+  // dense levels whose fp32 gradient fits one SM's shared memory (level 0 and 1 of the reference configuration)
+  int n_lv = 0;
+  unsigned coarse_entries = 0;
+  while (n_lv < kLevels && (unsigned long long)g->res[n_lv] * g->res[n_lv] * g->res[n_lv] <= g->size[n_lv] &&
+         8ull * (coarse_entries + g->size[n_lv]) <= 160 * 1024)
+    coarse_entries += g->size[n_lv++];
+  if (n_lv > 0 && P >= 4096) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      DFN_CUDA(cudaFuncSetAttribute(hashgrid_backward_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024),
+               "dfn_hashgrid_backward");
+      attr_set = true;
+    }
+    long long nb = (P * n_lv + 1023) / 1024;
+    if (nb > dfn_num_sms()) nb = dfn_num_sms();
+    hashgrid_backward_coarse_kernel<<<(int)nb, 1024, 8ull * coarse_entries, (cudaStream_t)stream>>>(
+        pos, P, (const uint32_t*)d_out_f16, to_dev(g), grad_scale, n_lv, coarse_entries, (float2*)d_table);
+    DFN_CHECK_LAUNCH("dfn_hashgrid_backward (coarse levels)");
+  } else {
+    n_lv = 0;
+  }
   hashgrid_backward_kernel<<<blocks_for(P * kLevels, 8), 256, 0, (cudaStream_t)stream>>>(
-      pos, P, (const uint32_t*)d_out_f16, to_dev(g), grad_scale, (float2*)d_table);
+      pos, P, (const uint32_t*)d_out_f16, to_dev(g), grad_scale, n_lv, (float2*)d_table);
   DFN_CHECK_LAUNCH("dfn_hashgrid_backward");
   return DFN_OK;
 }
