@@ -9,15 +9,16 @@ from .train import (  # noqa: F401
     sample_pdf, raw2outputs, process_rays_in_chunks, forward_pass, FusedTrainer, RayStore, onecycle_tables, train,
 )
 from .extract_vol import (  # noqa: F401
-    generate_3d_grid, volume_extraction, apply_otsu_threshold, save_volume, extract_volume_fused,
+    generate_3d_grid, volume_extraction, apply_otsu_threshold, save_volume, extract_volume_fused, gather_slabs, global_stats,
+    slab_range,
 )
 from .precompute_rays import get_rays, ray_cube_intersection, ray_cube_intersection_numpy, precompute_rays_on_device  # noqa: F401
 from .post_process_vol import volume_points, slice_aabb  # noqa: F401
-from .render import render_rays, render_image, row_range  # noqa: F401
+from .render import render_rays, render_image, row_range, gather_rows  # noqa: F401
 from .config import load_config  # noqa: F401
 
 __all__ = [
     "StratifiedSampler", "OptimizedPositionalEncoding", "OptimizedVanillaNeRF", "get_nerf_models", "InstantNGP", "sample_pdf",
     "raw2outputs", "process_rays_in_chunks", "forward_pass", "FusedTrainer", "RayStore", "onecycle_tables", "train", "generate_3d_grid",
-    "volume_extraction", "apply_otsu_threshold", "save_volume", "extract_volume_fused", "load_config", "ops", "get_rays", "ray_cube_intersection", "ray_cube_intersection_numpy", "precompute_rays_on_device", "volume_points", "slice_aabb", "render_rays", "render_image", "row_range",
+    "volume_extraction", "apply_otsu_threshold", "save_volume", "extract_volume_fused", "load_config", "ops", "get_rays", "ray_cube_intersection", "ray_cube_intersection_numpy", "precompute_rays_on_device", "volume_points", "slice_aabb", "render_rays", "render_image", "row_range", "gather_rows", "gather_slabs", "global_stats", "slab_range",
 ]

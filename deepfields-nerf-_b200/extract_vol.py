@@ -54,15 +54,19 @@ def apply_otsu_threshold(densities: torch.Tensor, fallback_percentile: float = 5
     """scripts/extract_vol.py:123-150 -> (binary occupancy [N] bool, threshold).  Histogram on the GPU; with a
     process group the min/max and the histogram are all-reduced so every rank gets the global threshold."""
     d = densities.reshape(-1).float()
-    lo, hi = d.min(), d.max()
+    if d.numel():
+        lo, hi = d.min(), d.max()
+    else:   # a rank whose slab is empty (more ranks than x-planes) still takes part in the collectives
+        lo, hi = torch.full((), float("inf"), device=d.device), torch.full((), float("-inf"), device=d.device)
     if group is not None:
-        torch.distributed.all_reduce(lo, op=torch.distributed.ReduceOp.MIN, group=group)
-        torch.distributed.all_reduce(hi, op=torch.distributed.ReduceOp.MAX, group=group)
+        lohi = torch.stack([-lo, hi])
+        torch.distributed.all_reduce(lohi, op=torch.distributed.ReduceOp.MAX, group=group)   # one collective for min and max
+        lo, hi = -lohi[0], lohi[1]
     lo, hi = float(lo), float(hi)
     if hi <= lo:
         thr = lo
     else:
-        hist = ops.histogram(d, lo, hi, 256)
+        hist = ops.histogram(d, lo, hi, 256) if d.numel() else torch.zeros(256, dtype=torch.int64, device=d.device)
         if group is not None:
             torch.distributed.all_reduce(hist, group=group)
         thr = otsu_from_histogram(hist, lo, hi)
@@ -107,10 +111,75 @@ def global_otsu(local_hist: torch.Tensor, lo: float, hi: float, group=None) -> f
     return otsu_from_histogram(hist, lo, hi)
 
 
+def default_group(world: int, group=None):
+    """The process group the slab collectives run on: the caller's, else the default group when `world` > 1 ranks are
+    initialised (so that a sharded call can never silently threshold every slab on its own)."""
+    if group is not None or world <= 1:
+        return group
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        return torch.distributed.group.WORLD
+    raise RuntimeError("extract_vol: world > 1 needs an initialised torch.distributed process group (one global Otsu "
+                       "threshold, extract_vol.py:123-150); pass group=False to keep per-slab statistics on purpose")
+
+
+def gather_slabs(occ: torch.Tensor, col: torch.Tensor, resolution: int, rank: int, world: int, group=None, dst: int = 0):
+    """Stitches the ranks' u8 slabs into ONE volume on rank `dst`: x-slabs are contiguous ranges of the flat
+    grid, so rank r's bytes land at [x0*R*R, x1*R*R) of the full arrays.  Returns (occupancy [R^3] u8, rgb [R^3,3] u8) on
+    `dst`, (None, None) elsewhere.  Point-to-point (slabs may be ragged when R % world != 0)."""
+    R = resolution
+    if world == 1:
+        return occ.reshape(-1), col.reshape(-1, 3)
+    dist = torch.distributed
+    if rank == dst:
+        full_o = torch.empty(R * R * R, dtype=torch.uint8, device=occ.device)
+        full_c = torch.empty(R * R * R, 3, dtype=torch.uint8, device=occ.device)
+        reqs = []
+        for r in range(world):
+            x0, x1 = slab_range(R, r, world)
+            a, b = x0 * R * R, x1 * R * R
+            if b == a:
+                continue
+            if r == dst:
+                full_o[a:b].copy_(occ.reshape(-1))
+                full_c[a:b].copy_(col.reshape(-1, 3))
+            else:
+                src = dist.get_global_rank(group, r) if group is not None and group is not dist.group.WORLD else r
+                reqs.append(dist.irecv(full_o[a:b], src=src, group=group))
+                reqs.append(dist.irecv(full_c[a:b], src=src, group=group))
+        for q in reqs:
+            q.wait()
+        return full_o, full_c
+    if occ.numel():
+        g_dst = dist.get_global_rank(group, dst) if group is not None and group is not dist.group.WORLD else dst
+        dist.send(occ.reshape(-1).contiguous(), dst=g_dst, group=group)
+        dist.send(col.reshape(-1, 3).contiguous(), dst=g_dst, group=group)
+    return None, None
+
+
+def global_stats(t: torch.Tensor, group=None) -> dict:
+    """min / max / mean / std (unbiased, like Tensor.std) of a tensor that is sharded over the ranks of `group`
+    (the density_stats / rgb_stats metadata of extract_vol.py:323-340)."""
+    x = t.reshape(-1).double()
+    n = torch.tensor([float(x.numel())], dtype=torch.float64, device=t.device)
+    acc = torch.stack([x.sum(), (x * x).sum()]) if x.numel() else torch.zeros(2, dtype=torch.float64, device=t.device)
+    mm = torch.stack([-x.min(), x.max()]) if x.numel() else torch.full((2,), float("-inf"), dtype=torch.float64, device=t.device)
+    if group is not None:
+        acc = torch.cat([acc, n])
+        torch.distributed.all_reduce(acc, group=group)
+        torch.distributed.all_reduce(mm, op=torch.distributed.ReduceOp.MAX, group=group)
+        n = acc[2:3]
+    cnt, mean = float(n), float(acc[0] / n)
+    var = max(float(acc[1] / n) - mean * mean, 0.0) * (cnt / max(cnt - 1.0, 1.0))
+    return {"min": float(-mm[0]), "max": float(mm[1]), "mean": mean, "std": var ** 0.5}
+
+
 def extract_volume_fused(model: OptimizedVanillaNeRF, resolution: int, bounds=(-1.0, 1.0), view_direction=(0.0, 0.0, -1.0),
                          rank: int = 0, world: int = 1, group=None, out=None):
     """Slab-sharded dense query: rank r owns x-planes [r*R/G,(r+1)*R/G) == a contiguous range of
-    the flat grid.  Returns (sigma [n], rgb [n,3], start, thr, occupancy u8 [n], rgb u8 [n,3]) for this rank's slab."""
+    the flat grid.  Returns (sigma [n], rgb [n,3], start, thr, occupancy u8 [n], rgb u8 [n,3]) for this rank's slab.
+    With world > 1 the min / max and the 256-bin histogram are all-reduced over `group` (default: the initialised
+    default group), so `thr` is the ONE global Otsu threshold of extract_vol.py:123-150 on every rank."""
+    group = None if group is False else default_group(world, group)
     dev = next(model.parameters()).device
     model._sync_packed()
     R = resolution
@@ -119,9 +188,15 @@ def extract_volume_fused(model: OptimizedVanillaNeRF, resolution: int, bounds=(-
     lin = torch.linspace(bounds[0], bounds[1], R, device=dev)
     view = torch.tensor(view_direction, dtype=torch.float32, device=dev)
     view = view / torch.norm(view)
-    rgb, sigma = ops.mlp_forward(model._packed, grid=(lin, view, start, count), out=out)
+    if count:
+        rgb, sigma = ops.mlp_forward(model._packed, grid=(lin, view, start, count), out=out)
+    else:
+        rgb, sigma = torch.empty(0, 3, device=dev), torch.empty(0, device=dev)
     occ_b, thr = apply_otsu_threshold(sigma, group=group)
-    occ, col = ops.pack_volume(sigma, rgb, thr)
+    if count:
+        occ, col = ops.pack_volume(sigma, rgb, thr)
+    else:
+        occ, col = torch.empty(0, dtype=torch.uint8, device=dev), torch.empty(0, 3, dtype=torch.uint8, device=dev)
     return sigma, rgb, start, thr, occ, col
 
 
@@ -154,6 +229,7 @@ def extract_volume_ngp(model: InstantNGP, resolution: int, bounds=(-1.0, 1.0), v
     """The slab-sharded dense query of extract_volume_fused for the Instant-NGP variant: grid points are generated on the
     device in pieces of `slab_points` (never the 1.6 GB grid), each piece is ONE fused launch (extract_vol.py:85-120 with
     the canonical view as a single direction, :100).  Same return tuple as extract_volume_fused."""
+    group = None if group is False else default_group(world, group)
     dev = next(model.parameters()).device
     R = resolution
     x0, x1 = slab_range(R, rank, world)
@@ -169,7 +245,10 @@ def extract_volume_ngp(model: InstantNGP, resolution: int, bounds=(-1.0, 1.0), v
             c, d = model(ops.grid_points(lin, start + s, n), view)
             sigma[s:s + n], rgb[s:s + n] = d.float(), c.float()
     occ_b, thr = apply_otsu_threshold(sigma, group=group)
-    occ, col = ops.pack_volume(sigma, rgb, thr)
+    if count:
+        occ, col = ops.pack_volume(sigma, rgb, thr)
+    else:
+        occ, col = torch.empty(0, dtype=torch.uint8, device=dev), torch.empty(0, 3, dtype=torch.uint8, device=dev)
     return sigma, rgb, start, thr, occ, col
 
 
@@ -185,22 +264,43 @@ def get_args(argv=None):
 
 
 def main(argv=None):
+    """scripts/extract_vol.py:264-357.  Under torchrun (RANK / WORLD_SIZE / LOCAL_RANK) the grid is sharded in x-slabs
+    over the ranks: NCCL all-reduces make the Otsu threshold and the metadata statistics global, the u8 slabs are gathered
+    to rank 0, and rank 0 alone writes ONE volume.pth."""
     args = get_args(argv)
+    if args.resolution <= 0:
+        raise ValueError("Resolution must be positive")
+    if args.bounds[0] >= args.bounds[1]:
+        raise ValueError("Invalid bounds: min must be less than max")
     cfg = load_config(args.cfg_path)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
-    R = int(cfg.volume_resolution)
+    torch.cuda.set_device(dev)   # the ops launch on the current device's stream
+    own_pg = False
+    if world > 1 and not torch.distributed.is_initialized():
+        torch.distributed.init_process_group("nccl", device_id=dev)
+        own_pg = True
+    group = torch.distributed.group.WORLD if world > 1 else None
+    R = int(cfg.volume_resolution)   # --resolution is ignored in favour of the cfg (:283-284, :346-347)
     with torch.no_grad():
         if getattr(cfg, "ngp", False):
             model = load_instant_ngp_model(str(cfg.checkpoint), getattr(cfg, "nerf_type", "large"), dev)
-            sigma, rgb, _, thr, occ, col = extract_volume_ngp(model, R, tuple(args.bounds), tuple(args.view_direction))
+            sigma, rgb, _, thr, occ, col = extract_volume_ngp(model, R, tuple(args.bounds), tuple(args.view_direction),
+                                                              rank=rank, world=world, group=group)
         else:
             model = load_vanilla_model(str(cfg.checkpoint), cfg, dev)
-            sigma, rgb, _, thr, occ, col = extract_volume_fused(model, R, tuple(args.bounds), tuple(args.view_direction))
-    stats = lambda t: {"min": float(t.min()), "max": float(t.max()), "mean": float(t.mean()), "std": float(t.std())}  # noqa: E731
-    meta = {"checkpoint_path": str(cfg.checkpoint), "device_used": str(dev), "batch_size": int(args.batch_size),
-            "density_stats": stats(sigma), "view_direction": list(args.view_direction), "rgb_stats": stats(rgb)}
-    save_volume(occ, col, str(cfg.volume_output_path), R, tuple(args.bounds), thr, meta)
-    print(f"Saved colored occupancy volume with metadata: {cfg.volume_output_path}")
+            sigma, rgb, _, thr, occ, col = extract_volume_fused(model, R, tuple(args.bounds), tuple(args.view_direction),
+                                                                rank=rank, world=world, group=group)
+        meta = {"checkpoint_path": str(cfg.checkpoint), "device_used": str(dev), "batch_size": int(args.batch_size),
+                "density_stats": global_stats(sigma, group), "view_direction": list(args.view_direction),
+                "rgb_stats": global_stats(rgb, group)}
+        occ, col = gather_slabs(occ, col, R, rank, world, group)
+    if rank == 0:
+        save_volume(occ, col, str(cfg.volume_output_path), R, tuple(args.bounds), thr, meta)
+        print(f"Saved colored occupancy volume with metadata: {cfg.volume_output_path}")
+    if own_pg:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":

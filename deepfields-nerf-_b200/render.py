@@ -77,8 +77,10 @@ def render_rays(model_coarse, model_fine, rays_o, rays_d, near, far, N_samples=6
 
 
 @torch.no_grad()
-def render_image(model_coarse, model_fine, H, W, K, pose, rows=None, background=0.0, **kw):
-    """Render rows [rows[0], rows[1]) of one camera: pixels whose ray misses the [-1,1]^3 cube get `background`."""
+def render_image(model_coarse, model_fine, H, W, K, pose, rows=None, background=0.0, draws=None, **kw):
+    """Render rows [rows[0], rows[1]) of one camera: pixels whose ray misses the [-1,1]^3 cube get `background`.
+    `draws` = (t_rand [H*W,S], u [H*W,I]) optionally fixes the jitter / inverse-CDF draws PER PIXEL, so that a row-sharded
+    render reproduces the unsharded image bit for bit."""
     from .precompute_rays import get_rays, ray_cube_intersection
     dev = next(model_fine.parameters()).device
     r0, r1 = rows if rows is not None else (0, H)
@@ -90,7 +92,36 @@ def render_image(model_coarse, model_fine, H, W, K, pose, rows=None, background=
     img = torch.full(((r1 - r0) * W, 3), float(background), device=dev)
     info = {"evaluated_fraction": 0.0, "rays": int(idx.numel())}
     if idx.numel() > 0:
+        if draws is not None:
+            pix = idx + r0 * W
+            kw = dict(kw, t_rand=draws[0][pix].contiguous(), u=draws[1][pix].contiguous())
         out = render_rays(model_coarse, model_fine, o[idx], d[idx], t_near[idx], t_far[idx], **kw)
         img[idx] = out["rgb_map"]
         info["evaluated_fraction"] = out["evaluated_fraction"]
     return img.reshape(r1 - r0, W, 3), info
+
+
+def gather_rows(part: torch.Tensor, H: int, rank: int, world: int, group=None, dst: int = 0):
+    """Assembles the row tiles of a row-sharded render on rank `dst` (gather of rgb tiles): rank r's
+    [rows_r, W, 3] tile lands at rows row_range(H, r, world) of the [H, W, 3] image.  Returns the image on `dst`, None elsewhere."""
+    if world == 1:
+        return part
+    dist = torch.distributed
+    W = part.shape[1]
+    if rank == dst:
+        img = torch.empty(H, W, 3, dtype=part.dtype, device=part.device)
+        reqs = []
+        for r in range(world):
+            r0, r1 = row_range(H, r, world)
+            if r1 == r0:
+                continue
+            if r == dst:
+                img[r0:r1].copy_(part)
+            else:
+                reqs.append(dist.irecv(img[r0:r1], src=r, group=group))
+        for q in reqs:
+            q.wait()
+        return img
+    if part.numel():
+        dist.send(part.contiguous(), dst=dst, group=group)
+    return None

@@ -278,8 +278,13 @@ class FusedTrainer:
                               "exp_avg_sq": self.v[off:off + c].view_as(p).clone()}
                 idx += 1
                 off += c
+        base_lr = float(self.lr_table[0])          # OneCycleLR: initial_lr = max_lr / div_factor = cfg.lr (train.py:250-259)
         group = {"lr": lr_now, "betas": (beta1_now, 0.999), "eps": 1e-8, "weight_decay": self.wd, "amsgrad": False,
                  "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": True,
+                 # the keys OneCycleLR adds to the group, so that the checkpoint resumes with OneCycleLR(last_epoch=k)
+                 "initial_lr": base_lr, "max_lr": base_lr * 10.0, "min_lr": base_lr / 100.0,
+                 "base_momentum": 0.85, "max_momentum": 0.95,
                  "params": list(range(idx))}
         return {"state": state, "param_groups": [group]}
 
@@ -322,51 +327,99 @@ class RayStore:
         return self
 
     def batches(self, batch_size, generator=None):
+        """One shuffled pass (DataLoader(shuffle=True), train.py:209-217).  Like the reference's loader (drop_last=False)
+        the final short batch is yielded too.  Every rank must draw the SAME permutation (pass generators seeded alike);
+        rank r then takes its shard_slice of each global batch."""
         perm = torch.randperm(self.n, device=self.rgb.device, generator=generator)
-        sl = shard_slice(batch_size, self.rank, self.world)
-        for i in range(0, self.n - batch_size + 1, batch_size):
-            idx = perm[i:i + batch_size][sl]
+        for i in range(0, self.n, batch_size):
+            chunk = perm[i:i + batch_size]
+            idx = chunk[shard_slice(chunk.numel(), self.rank, self.world)]
+            if idx.numel() == 0:
+                continue
             yield self.o[idx], self.d[idx], self.near[idx], self.far[idx], self.rgb[idx]
+
+    def steps_per_epoch(self, batch_size):
+        """len(dataloader) of the reference: ceil(n / batch_size)."""
+        return (self.n + batch_size - 1) // batch_size
 
     def __len__(self):
         return self.n
 
 
+def _open_writer(cfg, rank):
+    """SummaryWriter(output_dir / "logs") of scripts/train.py:198-203 (rank 0 only); None when tensorboard is absent."""
+    if rank != 0:
+        return None
+    out_dir = getattr(cfg, "output_dir", None) or os.path.dirname(str(cfg.checkpoint_dir).rstrip("/")) or "."
+    try:
+        from torch.utils.tensorboard import SummaryWriter
+    except ImportError:
+        return None
+    os.makedirs(str(out_dir), exist_ok=True)
+    return SummaryWriter(os.path.join(str(out_dir), "logs"))
+
+
+def _log_scalars(writer, step, loss_c, loss_f, lr_next):
+    """The five scalars of scripts/train.py:333-338, same tags."""
+    if writer is None:
+        return
+    writer.add_scalar("Loss/Coarse", loss_c, step)
+    writer.add_scalar("Loss/Fine", loss_f, step)
+    writer.add_scalar("Loss/Total", loss_c + loss_f, step)
+    writer.add_scalar("PSNR", -10.0 * math.log10(max(loss_f, 1e-12)), step)
+    writer.add_scalar("Scheduler Step", lr_next, step)
+
+
 def train(cfg_in):
-    """scripts/train.py:189-370 for the vanilla model (cfg.ngp false): same cfg keys, same checkpoint files."""
+    """scripts/train.py:189-370 for the vanilla model (cfg.ngp false): same cfg keys, same checkpoint files, same
+    TensorBoard tags and step numbering (step = epoch * steps_per_epoch + idx with epoch starting at 1, :333)."""
     global cfg
     cfg = cfg_in
     if getattr(cfg, "ngp", False):
         return train_ngp(cfg)
     dist_on = "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1
     rank, world = 0, 1
-    if dist_on:
-        torch.distributed.init_process_group("nccl")
-        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
+    if dist_on:
+        if not torch.distributed.is_initialized():
+            torch.distributed.init_process_group("nccl", device_id=dev)
+        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     ckpt_dir = str(cfg.checkpoint_dir)
     os.makedirs(ckpt_dir, exist_ok=True)
+    writer = _open_writer(cfg, rank)
     store = RayStore(str(cfg.rays_file), dev, rank, world)
-    steps_per_epoch = len(store) // cfg.batch_size
-    torch.manual_seed(0)
+    steps_per_epoch = store.steps_per_epoch(cfg.batch_size)          # len(dataloader), drop_last=False
+    torch.manual_seed(0)                                             # identical initial weights on every rank
     mc, mf = get_nerf_models(cfg.pos_L, cfg.dir_L, cfg.hidden_dim, device=dev)
     tr = FusedTrainer(mc, mf, cfg.N_samples, cfg.N_importance, cfg.lr, max(cfg.num_epochs * steps_per_epoch, 1),
                       bool(cfg.white_bg))
+    perm_gen = torch.Generator(device=dev)
+    perm_gen.manual_seed(0)                                          # the SAME shuffle on every rank ...
+    torch.manual_seed(1 + rank)                                      # ... but per-rank jitter / inverse-CDF / noise streams (SURVEY 8e)
     t0 = time.time()
     for epoch in range(1, cfg.num_epochs + 1):
-        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size)):
+        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size, perm_gen)):
             losses = tr.step(o, d, near, far, rgb)
-            if it % 100 == 0 and rank == 0:
-                lc, lf = losses.tolist()
-                psnr = -10.0 * math.log10(max(lf, 1e-12))
-                print(f"epoch {epoch} it {it}/{steps_per_epoch} loss {lc + lf:.5f} (c {lc:.5f} f {lf:.5f}) "
-                      f"psnr {psnr:.2f} {time.time() - t0:.1f}s")
+            if it % 100 == 0:
+                if world > 1:                                         # the global-batch losses (3 floats every 100 steps, SURVEY 8e)
+                    losses = losses.clone()
+                    torch.distributed.all_reduce(losses)
+                    losses /= world
+                if rank == 0:
+                    lc, lf = losses.tolist()
+                    psnr = -10.0 * math.log10(max(lf, 1e-12))
+                    print(f"| Epoch: {epoch} | Iteration: {it} | Loss: {lc + lf:.4f} (Coarse: {lc:.4f}, Fine: {lf:.4f}) | "
+                          f"PSNR: {psnr:.2f} | Time: {time.time() - t0:.2f}s |")
+                    done = min(int(tr.step_dev.item()), tr.total_steps - 1)
+                    _log_scalars(writer, epoch * steps_per_epoch + it, lc, lf, float(tr.lr_table[done]))
         if epoch % 2 == 0 and rank == 0:
             tr.save_checkpoint(os.path.join(ckpt_dir, f"nerf_epoch_{epoch:06d}.pth"), epoch)
     if rank == 0:
         tr.save_checkpoint(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
         print(f"Training completed in {time.time() - t0:.2f}s")
+    if writer is not None:
+        writer.close()
     return tr
 
 

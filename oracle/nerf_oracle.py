@@ -34,7 +34,7 @@ Tensor = torch.Tensor
 def stratified_z(near: Tensor, far: Tensor, t_rand: Tensor) -> Tensor:
     """Jittered depths.  sampling.py:8 (t grid), :13 (lerp), :16-18 (bin edges), :21 (jitter)."""
     S = t_rand.shape[-1]
-    t = torch.linspace(0.0, 1.0, S, dtype=torch.float32)
+    t = torch.linspace(0.0, 1.0, S, dtype=torch.float32, device=near.device)
     z = near * (1.0 - t[None, :]) + far * t[None, :]
     centre = 0.5 * (z[:, 1:] + z[:, :-1])
     hi = torch.cat([centre, z[:, -1:]], dim=1)
@@ -94,7 +94,7 @@ def merge_depths(z_coarse: Tensor, z_fine: Tensor) -> Tensor:
 # ----------------------------------------------------------------------------------------------
 def posenc(x: Tensor, L: int, include_input: bool = True) -> Tensor:
     """[x | sin(x_d * 2^k pi) (d-major, k-minor) | cos(...)]   (model.py:30, :48-53)."""
-    freqs = (2.0 ** torch.arange(L)) * torch.pi                # fp32, as the registered buffer
+    freqs = ((2.0 ** torch.arange(L)) * torch.pi).to(x.device)  # fp32, as the registered buffer
     ang = (x[..., None] * freqs).flatten(-2)                   # [..., 3L]
     parts = ([x] if include_input else []) + [torch.sin(ang), torch.cos(ang)]
     return torch.cat(parts, dim=-1)

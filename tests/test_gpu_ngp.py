@@ -161,7 +161,7 @@ def test_extract_volume_ngp_matches_pointwise_query(D, tmp_path):
     assert start == 0 and sigma.shape == (R ** 3, 1) and rgb.shape == (R ** 3, 3)
     assert torch.equal(sigma, sig2.float()) and torch.equal(rgb, rgb2.float())
     assert occ.dtype == torch.uint8 and col.shape == (R ** 3, 3) and 0 < int(occ.sum()) < R ** 3
-    parts = [EV.extract_volume_ngp(m, R, rank=r, world=2) for r in range(2)]
+    parts = [EV.extract_volume_ngp(m, R, rank=r, world=2, group=False) for r in range(2)]   # per-slab statistics on purpose
     assert torch.equal(torch.cat([p[0] for p in parts]), sigma) and parts[1][2] == (R // 2) * R * R
     ck = tmp_path / "nerf_final.pth"
     torch.save({"iteration": 3, "nerf_fine_state_dict": m.state_dict()}, ck)

@@ -44,7 +44,7 @@ def rel_err(a, b):
     return float((a - b).norm() / b.norm().clamp(min=1e-30))
 
 
-def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35):
+def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35, record=None):
     """The kernels compute in bf16 like the reference under autocast.  Gradients are therefore judged against the
     fp32 oracle with the error the bf16-autocast oracle itself shows as the yardstick: per parameter tensor
     rel_L2(cuda, fp32) <= slack * rel_L2(bf16 oracle, fp32) + floor (and an absolute cap)."""
@@ -57,6 +57,9 @@ def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35):
         # (a sum of cancelling terms, e.g. density_layer in eval mode): there the kernel must be no worse than it
         tol = min(slack * e16 + floor, cap) if e16 <= cap else e16
         rows.append(f"{k:26s} cuda-vs-fp32 {e:.4f}  bf16oracle-vs-fp32 {e16:.4f}  tol {tol:.4f}")
+        if record is not None:
+            record[k] = {"cuda_vs_fp32": round(e, 5), "bf16_oracle_vs_fp32": round(e16, 5), "cuda_vs_bf16_oracle": round(rel_err(got[k], g16), 5),
+                         "tol": round(tol, 5)}
         ok = ok and e <= tol
         worst = max(worst, e)
     assert ok, label + "\n" + "\n".join(rows)
@@ -174,6 +177,70 @@ def test_fused_step_vs_oracle(D, train_mode):
     l2 = tr.forward_backward(cu(o), cu(d), cu(near), cu(far), cu(tgt), t_rand=cu(t_rand), u=cu(u), noise_c=cu(nc),
                              noise_f=cu(nf))
     assert not torch.equal(l2.cpu(), got)
+
+
+def _oracle_step_chunked(sdc, sdf, o, d, near, far, tgt, t_rand, u, nc, nf, low, chunk=512):
+    """O.render_losses + backward over ray chunks (bounds the autograd memory at 4096 rays): MSELoss(mean) over the whole
+    batch is sum of squared errors / (3 B), so per-chunk losses scaled by chunk / B add up to it, gradients included."""
+    B, S = t_rand.shape
+    T = S + u.shape[1]
+    rc, rf = leaf_sd(sdc), leaf_sd(sdf)
+    lc = lf = 0.0
+    extras = []
+    for a in range(0, B, chunk):
+        b = min(a + chunk, B)
+        sl = slice(a, b)
+        out = O.render_losses(rc, rf, o[sl], d[sl], near[sl], far[sl], tgt[sl], t_rand[sl], u[sl],
+                              None if nc is None else nc[a * S:b * S], None if nf is None else nf[a * T:b * T], low=low)
+        w = (b - a) / B
+        ((out["loss_coarse"].float() + out["loss_fine"].float()) * w).backward()
+        lc += float(out["loss_coarse"].detach()) * w
+        lf += float(out["loss_fine"].detach()) * w
+        extras.append((out["z"].detach(), out["rgb_map_coarse"].detach().float(), out["rgb_map_fine"].detach().float()))
+    return rc, rf, lc, lf, extras
+
+
+@pytest.mark.parametrize("B", [1024, 4096])
+def test_fused_step_vs_oracle_at_benchmarked_sizes(D, B):
+    """The step bench.py times -- BASELINE config 1 (1024 rays) and config 2 (4096 rays), 64 + 128 samples, sigma noise on --
+    against the oracle with the same injected draws: losses 2e-2, rendered maps 2e-2, per-tensor gradient errors judged by
+    check_grads and RECORDED (gpurun_out/grad_errors_B*.json; the committed copies live in profiles/)."""
+    import json
+    import os
+    S, I = 64, 128
+    o, d, near, far, tgt = make_rays(1000, B)           # the seed of bench.py's first batch on rank 0
+    t_rand, u = make_draws(12 + B, B, S, I)
+    sdc, sdf = make_state_dict(31, 256), make_state_dict(32, 256)
+    nc, nf = make_noise(41, B * S), make_noise(42, B * (S + I))
+    rc, rf, lc, lf, extras = _oracle_step_chunked(sdc, sdf, o, d, near, far, tgt, t_rand, u, nc, nf, None)
+    rc16, rf16, lc16, lf16, _ = _oracle_step_chunked(sdc, sdf, o, d, near, far, tgt, t_rand, u, nc, nf, torch.bfloat16)
+
+    mc, mf = D.get_nerf_models(device="cuda")
+    mc.load_state_dict(sdc)
+    mf.load_state_dict(sdf)
+    tr = D.FusedTrainer(mc, mf, S, I, lr=5e-4, total_steps=20, train_noise=True)
+    cu = lambda t: t.cuda()  # noqa: E731
+    losses = tr.forward_backward(cu(o), cu(d), cu(near), cu(far), cu(tgt), t_rand=cu(t_rand), u=cu(u),
+                                 noise_c=cu(nc).reshape(-1), noise_f=cu(nf).reshape(-1))
+    got = losses.cpu()
+    want = torch.tensor([lc, lf])
+    assert torch.allclose(got, want, rtol=2e-2, atol=1e-5), (got, want)
+    assert (tr.aux["z"].cpu() - torch.cat([e[0] for e in extras])).abs().max() < 1e-6       # sampler: same jitter, same depths
+    n = D.ops.MLP_NUM_PARAMS
+    rec = {"rays": B, "N_samples": S, "N_importance": I, "losses_cuda": got.tolist(), "losses_fp32_oracle": [lc, lf],
+           "losses_bf16_oracle": [lc16, lf16], "metric": "per-tensor relative L2 error of the parameter gradient",
+           "coarse": {}, "fine": {}}
+    wc = check_grads(tr.grads[:n], rc, rc16, f"coarse B={B}", record=rec["coarse"])
+    wf = check_grads(tr.grads[n:], rf, rf16, f"fine B={B}", floor=0.06, record=rec["fine"])   # fine samples move with the bf16 coarse weights
+    rec["worst"] = {"coarse": wc, "fine": wf}
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out_dir, exist_ok=True)
+        with open(os.path.join(out_dir, f"grad_errors_B{B}.json"), "w") as fh:
+            json.dump(rec, fh, indent=1)
+    except OSError:
+        pass
+    print(f"fused step B={B}: losses {got.tolist()} vs {want.tolist()}; worst grad rel err coarse {wc:.4f} fine {wf:.4f}")
 
 
 def test_reference_signature_forward_pass(D):

@@ -81,3 +81,45 @@ def test_row_ranges_cover_ragged_heights():
             edges = [D.row_range(H, r, world) for r in range(world)]
             assert edges[0][0] == 0 and edges[-1][1] == H
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+
+
+def _gather_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import deepfields_nerf_b200 as D
+    from deepfields_nerf_b200 import extract_vol as X
+    R = 7                                                          # ragged: slabs of 4 and 3 planes (3 ranks: 3, 3, 1)
+    g = torch.Generator().manual_seed(3)
+    occ_full = (torch.rand(R ** 3, generator=g) < 0.3).to(torch.uint8)
+    col_full = torch.randint(0, 256, (R ** 3, 3), generator=g, dtype=torch.uint8)
+    sig_full = torch.rand(R ** 3, generator=g) * 9.0
+    x0, x1 = X.slab_range(R, rank, world)
+    sl = slice(x0 * R * R, x1 * R * R)
+    occ, col = X.gather_slabs(occ_full[sl].clone(), col_full[sl].clone(), R, rank, world, dist.group.WORLD)
+    st = X.global_stats(sig_full[sl], dist.group.WORLD)
+    # the sharded Otsu of apply_otsu_threshold needs the CUDA histogram; its collectives are covered by _worker above
+    H, W = 5, 3
+    img_full = torch.arange(H * W * 3, dtype=torch.float32).reshape(H, W, 3)
+    r0, r1 = D.row_range(H, rank, world)
+    img = D.gather_rows(img_full[r0:r1].clone(), H, rank, world, dist.group.WORLD)
+    out[rank] = {"occ_ok": None if occ is None else bool(torch.equal(occ, occ_full) and torch.equal(col, col_full)),
+                 "stats": st, "img_ok": None if img is None else bool(torch.equal(img, img_full))}
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gather_slabs_rows_and_global_stats(world):
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_gather_worker, args=(world, 29741 + world, out), nprocs=world, join=True)
+    assert out[0]["occ_ok"] is True and out[0]["img_ok"] is True       # rank 0 holds ONE stitched volume / image
+    assert all(out[r]["occ_ok"] is None and out[r]["img_ok"] is None for r in range(1, world))
+    g = torch.Generator().manual_seed(3)
+    R = 7
+    torch.rand(R ** 3, generator=g); torch.randint(0, 256, (R ** 3, 3), generator=g, dtype=torch.uint8)
+    sig = torch.rand(R ** 3, generator=g) * 9.0
+    for r in range(world):                                              # every rank reports the statistics of the whole volume
+        st = out[r]["stats"]
+        assert st["min"] == float(sig.min()) and st["max"] == float(sig.max())
+        assert st["mean"] == pytest.approx(float(sig.double().mean()), rel=1e-12)
+        assert st["std"] == pytest.approx(float(sig.double().std()), rel=1e-9)

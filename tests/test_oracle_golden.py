@@ -177,3 +177,34 @@ def test_volume_points_bit_exact():
     assert np.array_equal(pts, g["sliced_points"]) and np.array_equal(cols, g["sliced_rgbs"])
     assert 0 < len(g["sliced_points"]) < len(g["points"])
     assert (g["sliced_points"][:, 2] == VOL_AABB["aabb_max"][2]).any()   # the closed upper bound is hit exactly
+
+
+def test_dense_query_64_and_packing_vs_reference():
+    """The oracle's dense query (extract_vol.py:85-120) and u8 packing (:142,197-198) against the 64^3 goldens the reference's
+    query_density_and_rgb_batch produced (tests/golden/make_golden_extract.py) -- a strided sample keeps the CPU suite fast."""
+    import os
+    from common import peaked
+    G = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "extract_golden.npz")))
+    sd = peaked(make_state_dict(32, 256), 3.0)
+    pts = O.grid_points((-1.0, 1.0), 64)
+    idx = torch.arange(0, 64 ** 3, 37)
+    with torch.no_grad():
+        dens, cols = O.dense_query(sd, pts[idx], torch.tensor([0.0, 0.0, -1.0]))
+    assert float((dens.reshape(-1) - torch.from_numpy(G["r64_sigma"])[idx]).abs().max()) <= 1e-5
+    assert float((cols - torch.from_numpy(G["r64_rgb_f16"]).float()[idx]).abs().max()) <= 5e-4      # the golden rgb is stored in fp16
+    occ, col = O.pack_volume(torch.from_numpy(G["r64_sigma"]), torch.from_numpy(G["r64_rgb_f16"]).float(), 0.25, 64)
+    assert occ.dtype == torch.uint8 and int(occ.sum()) == int((G["r64_sigma"] > 0.25).sum())
+    # (rgb * 255).byte() truncates: recomputed from the fp16-stored rgb it is within one level of the reference's u8
+    assert int((col.reshape(-1, 3).int() - torch.from_numpy(G["r64_rgb_u8"]).int()).abs().max()) <= 1
+
+
+def test_save_volume_spec_is_the_reference_layout():
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "extract_golden.json")) as fh:
+        spec = json.load(fh)
+    sv = spec["save_volume"]
+    assert sv["top_keys"] == ["occupancy_volume", "rgb_volume", "metadata"]
+    assert sv["metadata_keys"][:7] == ["resolution", "bounds", "threshold", "occupied_ratio", "total_voxels", "occupied_voxels", "timestamp"]
+    # the state-dict spec of model.py:66-137 is what common.make_state_dict builds (key order and shapes)
+    sd = make_state_dict(1, 256)
+    assert [[k, list(v.shape), str(v.dtype)] for k, v in sd.items()] == spec["state_dict"]
