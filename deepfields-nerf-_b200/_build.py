@@ -15,8 +15,9 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libdeepfields_b200.so")
-OBJ = os.path.join(HERE, "build")
+SUFFIX = os.environ.get("DFN_LIB_SUFFIX", "")   # bring-up builds beside the product library, e.g. "_stats"
+LIB = os.path.join(HERE, f"libdeepfields_b200{SUFFIX}.so")
+OBJ = os.path.join(HERE, "build" + SUFFIX)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdeepfields_b200.so")
+LIB_PATH = os.path.join(HERE, "libdeepfields_b200%s.so" % os.environ.get("DFN_LIB_SUFFIX", ""))   # suffix: bring-up builds only
 
 _p = C.c_void_p
 _i = C.c_int
@@ -58,6 +58,8 @@ SIGNATURES = {
     "dfn_mlp_backward": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_mlp_backward_dgrad": (_i, [_ll, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_mlp_backward_wgrad": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p]),
+    "dfn_mlp_bwd_fused_ws_bytes": (_ll, [_ll]),
+    "dfn_mlp_backward_fused": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_umma_selftest": (_i, [_p, _p, _i, _i, _i, _i, _u, _u, _u, _u, _u, _u, _p, _p]),
     "dfn_umma_bench": (_i, [_i, _i, _i, _i, _i, _i, _p, _p]),
     "dfn_grid_points": (_i, [_p, _i, _ll, _ll, _p, _p]),

@@ -92,6 +92,7 @@ struct DgradArgs {
   const uint8_t* stash;  // forward stash
   uint8_t* dz;
   int skew_ns;           // start of pair p is delayed by (p % 8) * skew_ns (see mlp_fwd.cu)
+  int replicas;          // copies of the packed weight image; pair p streams copy p % replicas
 };
 
 __device__ __forceinline__ uint32_t relu_mask2(uint32_t h2) {
@@ -139,6 +140,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
       ps.pol = make_evict_last_policy();
+      ps.row0 = static_cast<uint32_t>((blockIdx.x >> 1) % a.replicas) * (kBwdPackBytes >> 7);
       // de-synchronise the pairs: all of them stream the same weight blocks in the same order, and in lockstep they all
       // hit the same L2 lines at the same moment
       for (int w = (blockIdx.x >> 1) & 7; a.skew_ns > 0 && w > 0; --w) __nanosleep(a.skew_ns);
@@ -423,8 +425,11 @@ extern "C" int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const f
   a.consts = consts; a.rgb = rgb; a.sigma = sigma;
   a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.stash = static_cast<const uint8_t*>(stash); a.dz = static_cast<uint8_t*>(dz);
   WeightMaps maps;
-  if (int rc = make_weight_maps(bwd_pack, kBwdPackBytes, &maps)) return rc;
-  const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  a.replicas = weight_replicas();
+  if (int rc = make_weight_maps(bwd_pack, static_cast<unsigned long long>(kBwdPackBytes) * a.replicas, &maps)) return rc;
+  int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  static const int pairs_env = [] { const char* e = getenv("DFN_DGRAD_PAIRS"); return e ? atoi(e) : 0; }();   // bring-up: per-pair speed on fewer SMs
+  if (pairs_env > 0 && pairs_env < pairs) pairs = pairs_env;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DFN_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes), "mlp_backward_dgrad");
   mlp_dgrad_kernel<<<2 * pairs, kThreads, kSmemBytes, st>>>(a, maps);

@@ -120,6 +120,7 @@ struct FwdArgs {
   uint8_t* stash_c;       // TRAIN: [n_tiles][32 KB]
   uint8_t* stash_m;       // TRAIN: [8][n_tiles][4 KB] ReLU bit masks of h1..h8 (mlp_common.cuh)
   int skew_ns;            // start of pair p is delayed by (p % 8) * skew_ns (see dfn_mlp_forward)
+  int replicas;           // copies of the packed weight image; pair p streams copy p % replicas
 };
 
 // ---- epilogue helpers ------------------------------------------------------------------------------
@@ -204,6 +205,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
 #pragma unroll
       for (int i = 0; i < kStages; ++i) { ps.use[0][i] = ps.use[1][i] = 0; ps.last[i] = -1; }
       ps.pol = make_evict_last_policy();
+      ps.row0 = static_cast<uint32_t>((blockIdx.x >> 1) % a.replicas) * (kFwdPackBytes >> 7);
       // de-synchronise the pairs: all of them stream the same weight blocks in the same order, and in lockstep they all
       // hit the same L2 lines at the same moment
       for (int w = (blockIdx.x >> 1) & 7; a.skew_ns > 0 && w > 0; --w) __nanosleep(a.skew_ns);
@@ -456,7 +458,7 @@ __device__ __forceinline__ float param_w(const float* params, int layer, int o, 
 }
 
 __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ fwd,
-                                    __nv_bfloat16* __restrict__ bwd, float* __restrict__ consts) {
+                                    __nv_bfloat16* __restrict__ bwd, float* __restrict__ consts, int replicas) {
   constexpr ParamOffsets po = param_offsets();
   const int nf = kFwdPackBytes / 2, nb = kBwdPackBytes / 2;
   const int total = nf + nb + kConstFloats;
@@ -478,7 +480,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
       else if (j == 4) { if (k < 256 + 63) v = param_w(params, 4, n, k); }
       else if (j == 9) { if (k < 256 + 27) v = param_w(params, 10, n, k); }
       else v = param_w(params, layer, n, k);
-      fwd[idx] = __float2bfloat16_rn(v);
+      for (int r = 0; r < replicas; ++r) fwd[idx + static_cast<size_t>(r) * nf] = __float2bfloat16_rn(v);
     } else if (idx < nf + nb) {
       const int bi = idx - nf;
       int b = 0;
@@ -488,7 +490,8 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
       const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half of W^T's N rows
       const int kc = e / (128 * 8), i = r * 128 + (e / 8) % 128, o = kc * 8 + (e & 7);
       const int layer_of[kNumBwdJobs] = {10, 9, 7, 6, 5, 4, 3, 2, 1};
-      bwd[bi] = __float2bfloat16_rn(param_w(params, layer_of[b], o, i));
+      const __nv_bfloat16 wv = __float2bfloat16_rn(param_w(params, layer_of[b], o, i));
+      for (int r = 0; r < replicas; ++r) bwd[bi + static_cast<size_t>(r) * nb] = wv;
     } else {
       const int c = idx - nf - nb;
       float v = 0.f;
@@ -503,15 +506,15 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloa
 
 }  // namespace
 
-extern "C" long long dfn_mlp_fwd_pack_bytes(void) { return kFwdPackBytes; }
-extern "C" long long dfn_mlp_bwd_pack_bytes(void) { return kBwdPackBytes; }
+extern "C" long long dfn_mlp_fwd_pack_bytes(void) { return static_cast<long long>(kFwdPackBytes) * weight_replicas(); }
+extern "C" long long dfn_mlp_bwd_pack_bytes(void) { return static_cast<long long>(kBwdPackBytes) * weight_replicas(); }
 extern "C" long long dfn_mlp_consts_bytes(void) { return kConstBytes; }
 extern "C" long long dfn_mlp_stash_bytes(long long P) { return stash_total_bytes(num_tiles(P)); }
 
 extern "C" int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream) {
   DFN_CHECK_ARG(params && fwd_pack && bwd_pack && consts, "mlp_pack_weights: null pointer");
   pack_weights_kernel<<<dfn_num_sms() * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      params, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts);
+      params, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts, weight_replicas());
   DFN_CHECK_LAUNCH("mlp_pack_weights");
   return DFN_OK;
 }
@@ -544,7 +547,8 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
     a.stash_m = s + stash_off_mask(a.n_tiles);
   }
   WeightMaps maps;
-  if (int rc = make_weight_maps(fwd_pack, kFwdPackBytes, &maps)) return rc;
+  a.replicas = weight_replicas();
+  if (int rc = make_weight_maps(fwd_pack, static_cast<unsigned long long>(kFwdPackBytes) * a.replicas, &maps)) return rc;
   // one CTA per SM, paired: grid = 2 * min(#SM / 2, #super-tiles)
   const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
   const int grid = 2 * pairs;

@@ -9,6 +9,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include <utility>
+#include <stdlib.h>
 
 namespace mlp_pipe {
 using namespace mlp;
@@ -85,6 +86,7 @@ struct ProdState {
   uint32_t use[2][PP::kStages];   // parity of the number of fills so far per (slot, stage)
   uint64_t pol;               // L2 evict_last policy for the weight loads (the image is re-read by every tile)
   int last[PP::kStages];          // slot that used the stage last (-1: never)
+  uint32_t row0;              // first 128-byte row of the replica of the weight image this pair streams (weight_replicas())
 };
 
 // tensor-map TMA load of `rows` x 128 bytes starting at row y of the weight image; completion (bytes) is signalled on
@@ -119,7 +121,7 @@ __device__ __forceinline__ void produce_job(const WeightMaps& maps, uint32_t ran
       const uint32_t full = bar0 + 8u * PP::bar_full_i(t, stage);
       const int mi = map_index(nb);
       if (rank == 0) mbar_arrive_expect_tx(full, 2 * nb);
-      tma_load_rows(ring + stage * PP::kRingStageBytes, &maps.m[mi], (src + off) >> 7, rank == 0 ? full : map_to_cta(full, 0), ps.pol);
+      tma_load_rows(ring + stage * PP::kRingStageBytes, &maps.m[mi], ps.row0 + ((src + off) >> 7), rank == 0 ? full : map_to_cta(full, 0), ps.pol);
     }
   }
 }
@@ -304,6 +306,14 @@ __device__ __forceinline__ void issue_job(IssueCtx& c) {
 template <class PP, int... Js>
 __device__ __forceinline__ void issue_all(IssueCtx& c, std::integer_sequence<int, Js...>) {
   ((issue_job<PP, Js, 0>(c), issue_job<PP, Js, 1>(c)), ...);
+}
+
+// All pairs stream the same weight blocks in the same order: with ONE copy of the image every pair asks the same L2 slices
+// for the same lines at about the same time.  The packed images are therefore kept in R identical replicas (different
+// addresses hash to different slices) and pair p streams replica p % R.  DFN_WEIGHT_REPLICAS overrides R.
+static inline int weight_replicas() {
+  static const int r = [] { const char* e = getenv("DFN_WEIGHT_REPLICAS"); int v = e ? atoi(e) : 1; return v < 1 ? 1 : (v > 16 ? 16 : v); }();
+  return r;
 }
 
 // tensor maps over the packed weight image (rebuilt per call: a few hundred ns of host time, no device work)

@@ -3,6 +3,7 @@ allocator) and launch on torch's current CUDA stream.  No op has a CPU path."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -240,6 +241,29 @@ def mlp_forward(packed: PackedMLP, *, pos=None, view=None, rays=None, grid=None,
     _lib.call("dfn_mlp_forward", C.byref(s), P, packed.fwd.data_ptr(), packed.consts.data_ptr(), _ptr(noise),
               rgb.data_ptr(), sigma.data_ptr(), _ptr(stash), _stream())
     return rgb, sigma
+
+
+def mlp_bwd_fused_ws_bytes(P: int) -> int:
+    return _lib.load().dfn_mlp_bwd_fused_ws_bytes(P)
+
+
+def bwd_fused_default() -> bool:
+    """The one-launch backward (csrc/mlp_bwd_fused.cu) is an EXPERIMENT that measured slower than the two launches
+    (DESIGN.md section 5); DFN_BWD_FUSED=1 selects it."""
+    return os.environ.get("DFN_BWD_FUSED", "0") == "1"
+
+
+def mlp_backward_fused(packed: PackedMLP, rgb: Tensor, sigma: Tensor, d_rgb: Tensor, d_sigma: Tensor, stash: Tensor,
+                       ws: Tensor, grads: Tensor, *, pos=None, view=None, rays=None, grid=None) -> None:
+    """mlp_backward as ONE launch: dgrad pairs and wgrad units run concurrently, dZ tiles pass through an L2-resident ring
+    in `ws` (mlp_bwd_fused_ws_bytes(P) bytes) instead of an HBM scratch."""
+    s, P, keep = _source(pos, view, rays, grid)
+    assert grads.numel() == MLP_NUM_PARAMS and grads.dtype == torch.float32 and grads.is_cuda
+    assert ws.is_cuda and ws.dtype == torch.uint8 and ws.numel() >= mlp_bwd_fused_ws_bytes(P)
+    _lib.call("dfn_mlp_backward_fused", C.byref(s), P, packed.bwd.data_ptr(), packed.consts.data_ptr(),
+              _f32(rgb.reshape(-1, 3), "rgb").data_ptr(), _f32(sigma.reshape(-1), "sigma").data_ptr(),
+              _f32(d_rgb.reshape(-1, 3), "d_rgb").data_ptr(), _f32(d_sigma.reshape(-1), "d_sigma").data_ptr(),
+              stash.data_ptr(), ws.data_ptr(), grads.data_ptr(), _stream())
 
 
 def mlp_backward(packed: PackedMLP, rgb: Tensor, sigma: Tensor, d_rgb: Tensor, d_sigma: Tensor, stash: Tensor,

@@ -110,6 +110,15 @@ int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const float* const
 int dfn_mlp_backward_wgrad(const dfn_point_source* src, long long P, const void* stash, const void* dz, float* grads,
                            void* stream);
 
+/* dfn_mlp_backward as ONE launch: the data-gradient pipeline and the weight-gradient units run concurrently on disjoint
+ * SMs and the dZ tiles go from one to the other through a ring that stays resident in L2 (csrc/mlp_bwd_fused.cu), so they
+ * never make the 2 x 4 880 B/point round trip through HBM.  workspace = dfn_mlp_bwd_fused_ws_bytes(P) bytes (ring control
+ * block, ring, 16 B/point of head gradients); same inputs, same accumulation into grads as dfn_mlp_backward. */
+long long dfn_mlp_bwd_fused_ws_bytes(long long P);
+int dfn_mlp_backward_fused(const dfn_point_source* src, long long P, const void* bwd_pack, const float* consts,
+                           const float* rgb, const float* sigma, const float* d_rgb, const float* d_sigma, const void* stash,
+                           void* workspace, float* grads, void* stream);
+
 /* single 128 x N x K tcgen05 GEMM on operand tiles in the chunk layout (bring-up / descriptor self test) */
 int dfn_umma_selftest(const void* a_tile, const void* b_tile, int N, int K, int a_mn_major, int b_mn_major,
                       unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, unsigned a_kstep, unsigned b_kstep,
