@@ -44,6 +44,7 @@ SIGNATURES = {
     "dfn_sample_pdf": (_i, [_p, _i, _p, _ll, _i, _p, _i, _i, _i, _p, _p, _p, _p]),
     "dfn_sample_pdf_with_cdf": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "dfn_merge_sort_z": (_i, [_p, _i, _p, _i, _i, _p, _p]),
+    "dfn_sample_merge": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "dfn_posenc": (_i, [_p, _p, _ll, _i, _i, _p, _p]),
     "dfn_composite_forward": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),
     "dfn_composite_backward": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),

@@ -101,13 +101,23 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) composite_kernel(Composit
         m2 += w[k] * sc[3 * i + 2];
         accv += w[k];
         dep += w[k] * sz[i];
-        if (MODE != 1 && a.weights) a.weights[base + i] = w[k];
       } else {
         w[k] = 0.f;
       }
     }
     m0 = warp_sum(m0); m1 = warp_sum(m1); m2 = warp_sum(m2);
     accv = warp_sum(accv); dep = warp_sum(dep);
+    // Per-sample outputs leave through shared memory: a lane owns a CONTIGUOUS run of samples (that is what makes the
+    // transmittance scan cheap), so direct stores would hit 32 different sectors per instruction.  sz is dead after this
+    // point (depth is summed), ss after the alphas: they stage weights / d_sigma; the colours stay until d_rgb is out.
+    if (MODE != 1 && a.weights) {
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < kMaxPerLane; ++k)
+        if (k < n && i0 + k < S) sz[i0 + k] = w[k];
+      __syncwarp();
+      for (int i = lane; i < S; i += 32) a.weights[base + i] = sz[i];
+    }
     if (a.white_bg) { m0 += 1.0f - accv; m1 += 1.0f - accv; m2 += 1.0f - accv; }
     if (MODE != 1 && lane == 0) {
       if (a.rgb_map) { a.rgb_map[ray * 3] = m0; a.rgb_map[ray * 3 + 1] = m1; a.rgb_map[ray * 3 + 2] = m2; }
@@ -137,10 +147,18 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) composite_kernel(Composit
         if (a.d_weights) g += a.d_weights[base + i];
         gw[k] = g;
         lsum += g * w[k];
-        a.d_rgb[(base + i) * 3] = w[k] * g0;
-        a.d_rgb[(base + i) * 3 + 1] = w[k] * g1;
-        a.d_rgb[(base + i) * 3 + 2] = w[k] * g2;
       }
+    }
+    // d_rgb[i][c] = w[i] * g_c: weights -> shared memory (sz; any staged forward weights have been written out), then one
+    // coalesced pass over the 3S floats
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kMaxPerLane; ++k)
+      if (k < n && i0 + k < S) sz[i0 + k] = w[k];
+    __syncwarp();
+    for (int j = lane; j < 3 * S; j += 32) {
+      const int i = j / 3, c = j - 3 * i;
+      a.d_rgb[base * 3 + j] = sz[i] * (c == 0 ? g0 : (c == 1 ? g1 : g2));
     }
     // exclusive suffix sum over lanes: suffix(lane) = sum over lanes > lane of lsum
     float incl_s = lsum;
@@ -156,10 +174,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) composite_kernel(Composit
       const int i = i0 + k;
       if (k < n && i < S) {
         const float dalpha = gw[k] * T[k] - suf / keep[k];
-        a.d_sigma[base + i] = dalpha * delta[k] * ex[k];
+        ss[i] = dalpha * delta[k] * ex[k];
         suf += gw[k] * w[k];
       }
     }
+    __syncwarp();
+    for (int i = lane; i < S; i += 32) a.d_sigma[base + i] = ss[i];
     __syncwarp();
   }
 }

@@ -6,26 +6,27 @@
 
 namespace {
 
-__global__ void posenc_kernel(const float* __restrict__ x, const float* __restrict__ freqs, long long P, int L,
+// one thread per (point, dimension, frequency): sin and cos of the same angle come from ONE sincosf, and no thread does
+// 64-bit division (the batch is cut into pieces of < 2^31 / D points by the launcher)
+__global__ void posenc_kernel(const float* __restrict__ x, const float* __restrict__ freqs, unsigned P, int L,
                               int include_input, float* __restrict__ out) {
-  const int D = (include_input ? 3 : 0) + 6 * L;
-  const long long total = P * D;
-  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long p = idx / D;
-    int c = static_cast<int>(idx % D);
-    float v;
-    if (include_input && c < 3) {
-      v = x[p * 3 + c];
+  const unsigned per = 3u * L + (include_input ? 3u : 0u);   // work items per point: 3L angles (+ 3 copies)
+  const unsigned D = 6u * L + (include_input ? 3u : 0u);
+  const unsigned total = P * per;
+  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const unsigned p = idx / per, c = idx - p * per;
+    float* o = out + static_cast<size_t>(p) * D;
+    if (include_input && c < 3u) {
+      o[c] = x[static_cast<size_t>(p) * 3 + c];
     } else {
-      if (include_input) c -= 3;
-      const int is_cos = c >= 3 * L;
-      if (is_cos) c -= 3 * L;
-      const int d = c / L, k = c % L;
-      const float ang = __fmul_rn(x[p * 3 + d], freqs[k]);
-      v = is_cos ? cosf(ang) : sinf(ang);
+      const unsigned j = c - (include_input ? 3u : 0u);       // j = d * L + k
+      const unsigned d = j / L, k = j - d * L;
+      float sn, cs;
+      sincosf(__fmul_rn(x[static_cast<size_t>(p) * 3 + d], freqs[k]), &sn, &cs);
+      const unsigned off = include_input ? 3u : 0u;
+      o[off + j] = sn;
+      o[off + 3u * L + j] = cs;
     }
-    out[idx] = v;
   }
 }
 
@@ -120,8 +121,14 @@ extern "C" int dfn_posenc(const float* x, const float* freqs, long long P, int L
   DFN_CHECK_ARG(L >= 0 && L <= 32, "posenc: L=%d out of range", L);
   const int D = (include_input ? 3 : 0) + 6 * L;
   if (P == 0 || D == 0) return DFN_OK;
-  posenc_kernel<<<grid1d(P * D, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, freqs, P, L, include_input, out);
-  DFN_CHECK_LAUNCH("posenc");
+  const long long per = 3LL * L + (include_input ? 3 : 0);
+  const long long piece = (1LL << 31) / per;     // points per launch: the kernel indexes its work items with 32 bits
+  for (long long p0 = 0; p0 < P; p0 += piece) {
+    const long long n = P - p0 < piece ? P - p0 : piece;
+    posenc_kernel<<<grid1d(n * per, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x + p0 * 3, freqs, static_cast<unsigned>(n), L,
+                                                                                         include_input, out + p0 * D);
+    DFN_CHECK_LAUNCH("posenc");
+  }
   return DFN_OK;
 }
 

@@ -15,18 +15,44 @@ __device__ __forceinline__ float lerp_nf(float near, float far, float t) {
   return __fadd_rn(__fmul_rn(near, __fsub_rn(1.0f, t)), __fmul_rn(far, t));
 }
 
-__global__ void stratified_kernel(const float* __restrict__ near, const float* __restrict__ far,
-                                  const float* __restrict__ t_vals, const float* __restrict__ t_rand, int B, int S,
-                                  float* __restrict__ z_out) {
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= static_cast<long long>(B) * S) return;
-  const int ray = static_cast<int>(idx / S), i = static_cast<int>(idx % S);
-  const float n = near[ray], f = far[ray];
+__device__ __forceinline__ float strat_z(float n, float f, const float* __restrict__ t_vals, int i, int S, float tr) {
   const float zi = lerp_nf(n, f, t_vals[i]);
   float lo = zi, hi = zi;
   if (i > 0) lo = __fmul_rn(0.5f, __fadd_rn(zi, lerp_nf(n, f, t_vals[i - 1])));
   if (i + 1 < S) hi = __fmul_rn(0.5f, __fadd_rn(lerp_nf(n, f, t_vals[i + 1]), zi));
-  z_out[idx] = __fadd_rn(lo, __fmul_rn(__fsub_rn(hi, lo), t_rand[idx]));
+  return __fadd_rn(lo, __fmul_rn(__fsub_rn(hi, lo), tr));
+}
+
+// VEC = 4: S % 4 == 0, one thread per four consecutive samples of a ray (16-byte loads / stores)
+template <int VEC>
+__global__ void stratified_kernel(const float* __restrict__ near, const float* __restrict__ far,
+                                  const float* __restrict__ t_vals, const float* __restrict__ t_rand, int B, int S,
+                                  float* __restrict__ z_out) {
+  const long long n_items = static_cast<long long>(B) * S / VEC;
+  const unsigned per_ray = static_cast<unsigned>(S / VEC);
+  for (long long it = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; it < n_items;
+       it += static_cast<long long>(gridDim.x) * blockDim.x) {
+    long long ray;
+    int i0;
+    if ((it >> 32) == 0) {   // a 64-bit division costs ~100 instructions
+      const unsigned r = static_cast<unsigned>(it) / per_ray;
+      ray = r; i0 = static_cast<int>(static_cast<unsigned>(it) - r * per_ray) * VEC;
+    } else {
+      ray = it / per_ray; i0 = static_cast<int>(it % per_ray) * VEC;
+    }
+    const float n = __ldg(near + ray), f = __ldg(far + ray);
+    if (VEC == 4) {
+      const float4 tr = *reinterpret_cast<const float4*>(t_rand + it * 4);
+      float4 z;
+      z.x = strat_z(n, f, t_vals, i0, S, tr.x);
+      z.y = strat_z(n, f, t_vals, i0 + 1, S, tr.y);
+      z.z = strat_z(n, f, t_vals, i0 + 2, S, tr.z);
+      z.w = strat_z(n, f, t_vals, i0 + 3, S, tr.w);
+      *reinterpret_cast<float4*>(z_out + it * 4) = z;
+    } else {
+      z_out[it] = strat_z(n, f, t_vals, i0, S, t_rand[it]);
+    }
+  }
 }
 
 // pts / dirs emission: one thread per point
@@ -49,6 +75,38 @@ __global__ void points_kernel(const float* __restrict__ o, const float* __restri
 // ------------------------------------------------------------------------------------------------
 constexpr int kPdfWarps = 4;
 constexpr int kMaxBins = 256;
+
+// cdf[0] = 0, cdf[i+1] = fl32(sum_{j<=i} pdf[j]) with the running sum kept in double and rounded to fp32 per prefix - the
+// accumulation torch's CPU cumsum performs.  On entry cdf[1..NW] holds the pdf.  The sum runs as a warp
+// scan: every lane adds a contiguous run, the run totals are scanned with shuffles.  The pdf values are fp32 numbers within
+// 2^-17 of each other at most ((w + 1e-5) / sum, at most 255 terms), so every partial sum is EXACT in double whatever the
+// association, and the rounded prefixes are bit-identical to the sequential loop's.
+__device__ __forceinline__ void pdf_to_cdf_warp(float* cdf, int NW, int lane) {
+  const int per = (NW + 31) >> 5;              // <= 8
+  const int i0 = lane * per;
+  double loc[8];
+  double run = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int i = i0 + k;
+    if (k < per && i < NW) run += static_cast<double>(cdf[i + 1]);
+    loc[k] = run;
+  }
+  double incl = run;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  const double excl = incl - run;              // exact: see above
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int i = i0 + k;
+    if (k < per && i < NW) cdf[i + 1] = static_cast<float>(excl + loc[k]);
+  }
+  if (lane == 0) cdf[0] = 0.f;
+}
 
 template <bool HAVE_CDF>
 __global__ void __launch_bounds__(kPdfWarps * 32) sample_pdf_kernel(
@@ -79,14 +137,7 @@ __global__ void __launch_bounds__(kPdfWarps * 32) sample_pdf_kernel(
       const float tot = warp_sum(part);
       for (int i = lane; i < NW; i += 32) cdf[i + 1] = __fdiv_rn(__fadd_rn(wr[i], 1e-5f), tot);
       __syncwarp();
-      if (lane == 0) {
-        double run = 0.0;
-        cdf[0] = 0.f;
-        for (int i = 0; i < NW; ++i) {
-          run += static_cast<double>(cdf[i + 1]);
-          cdf[i + 1] = static_cast<float>(run);
-        }
-      }
+      pdf_to_cdf_warp(cdf, NW, lane);
     }
     __syncwarp();
     if (cdf_out)
@@ -113,39 +164,197 @@ __global__ void __launch_bounds__(kPdfWarps * 32) sample_pdf_kernel(
 }
 
 // ------------------------------------------------------------------------------------------------
-// merge: sort(cat(z_coarse, z_fine)) per ray; bitonic network over 256 padded keys in shared memory
+// sample_pdf + fine_points' sort in ONE kernel (the train step / render path): the NS new depths never leave the SM.
+// One warp per ray: pdf -> cdf (warp scan) -> searchsorted + lerp (KPL draws per lane) -> bitonic sort of the new depths
+// in registers (compare-exchange through shuffles) -> merge with the NA coarse depths by rank (two binary searches; the
+// coarse depths of the stratified sampler are sorted by construction - if a ray's are not, its keys take the generic
+// shared-memory bitonic network instead) -> one coalesced write of the NA + NS merged depths.
+// Values are bit-identical to sample_pdf_kernel followed by merge_sort_kernel: same arithmetic, and a sorted sequence of
+// the same multiset of floats is unique.
 // ------------------------------------------------------------------------------------------------
-constexpr int kSortWarps = 4;
-constexpr int kSortN = 256;
+constexpr int kSmWarps = 4;
+constexpr int kSmMaxNA = 128;
 
-__global__ void __launch_bounds__(kSortWarps * 32) merge_sort_kernel(const float* __restrict__ za, int NA,
-                                                                      const float* __restrict__ zb, int NBn, int B,
-                                                                      float* __restrict__ out) {
-  __shared__ float s_keys[kSortWarps][kSortN];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* k = s_keys[warp];
-  const int N = NA + NBn;
-  for (int ray = blockIdx.x * kSortWarps + warp; ray < B; ray += gridDim.x * kSortWarps) {
-    for (int i = lane; i < kSortN; i += 32) {
-      float v = CUDART_INF_F;
-      if (i < NA) v = za[static_cast<size_t>(ray) * NA + i];
-      else if (i < N) v = zb[static_cast<size_t>(ray) * NBn + (i - NA)];
-      k[i] = v;
-    }
-    __syncwarp();
-    for (int size = 2; size <= kSortN; size <<= 1) {
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        for (int t = lane; t < kSortN / 2; t += 32) {
-          const int i = 2 * t - (t & (stride - 1));
-          const int j = i + stride;
-          const bool up = ((i & size) == 0);
-          const float a = k[i], b = k[j];
-          if ((a > b) == up) { k[i] = b; k[j] = a; }
+template <int KPL>
+__device__ __forceinline__ void bitonic_sort_regs(float (&v)[KPL], int lane) {
+  constexpr int N = 32 * KPL;
+#pragma unroll
+  for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= KPL) {
+        const int lj = j / KPL;
+        const bool lower = (lane & lj) == 0;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) {
+          const float other = __shfl_xor_sync(0xffffffffu, v[i], lj);
+          const bool up = (((lane * KPL + i) & k) == 0);
+          const bool take_min = (up == lower);
+          const bool swap = take_min ? (other < v[i]) : (other > v[i]);
+          v[i] = swap ? other : v[i];
         }
-        __syncwarp();
+      } else {
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) {
+          const int p2 = i ^ j;
+          if (p2 > i) {
+            const bool up = (((lane * KPL + i) & k) == 0);
+            const float a = v[i], b = v[p2];
+            const bool swap = up ? (a > b) : (a < b);
+            v[i] = swap ? b : a;
+            v[p2] = swap ? a : b;
+          }
+        }
       }
     }
-    for (int i = lane; i < N; i += 32) out[static_cast<size_t>(ray) * N + i] = k[i];
+  }
+}
+
+// Sorted union of NA keys in shared memory (zc; `sorted` tells whether they are ascending) and NS keys in registers
+// (v: key lane + 32 j in v[j], +inf beyond NS) -> so[0 .. NA + NS)
+template <int KPL>
+__device__ __forceinline__ void sort_merge_warp(float (&v)[KPL], const float* zc, int NA, int NS, bool sorted, float* sf, float* so,
+                                                int lane) {
+  const int N = NA + NS;
+  if (sorted) {
+      bitonic_sort_regs<KPL>(v, lane);                 // element e = lane * KPL + j, ascending; the +inf padding sorts last
+#pragma unroll
+      for (int j = 0; j < KPL; ++j) sf[lane * KPL + j] = v[j];
+      __syncwarp();
+      // rank merge, coarse first among equal values:  pos(coarse i) = i + #{fine < zc[i]},  pos(fine e) = e + #{coarse <= f}
+#pragma unroll
+      for (int j = 0; j < KPL; ++j) {
+        const int e = lane * KPL + j;
+        if (e < NS) {
+          const float f = v[j];
+          int lo = 0, hi = NA;
+          while (lo < hi) { const int mid = (lo + hi) >> 1; if (zc[mid] <= f) lo = mid + 1; else hi = mid; }
+          so[e + lo] = f;
+        }
+      }
+      for (int i = lane; i < NA; i += 32) {
+        const float c = zc[i];
+        int lo = 0, hi = NS;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sf[mid] < c) lo = mid + 1; else hi = mid; }
+        so[i + lo] = c;
+      }
+    } else {
+      // generic path: bitonic network over all keys in shared memory (padded to a power of two with +inf)
+      int M = 2;
+      while (M < N) M <<= 1;
+      for (int i = lane; i < M; i += 32) so[i] = i < NA ? zc[i] : CUDART_INF_F;
+#pragma unroll
+      for (int j = 0; j < KPL; ++j) if (lane + 32 * j < NS) so[NA + lane + 32 * j] = v[j];
+      __syncwarp();
+      for (int size = 2; size <= M; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+          for (int t = lane; t < M / 2; t += 32) {
+            const int i = 2 * t - (t & (stride - 1));
+            const int jj = i + stride;
+            const bool up = ((i & size) == 0);
+            const float a = so[i], b = so[jj];
+            if ((a > b) == up) { so[i] = b; so[jj] = a; }
+          }
+          __syncwarp();
+        }
+    }
+}
+
+template <int KPL>
+__global__ void __launch_bounds__(kSmWarps * 32) sample_merge_kernel(
+    const float* __restrict__ z, const float* __restrict__ weights, const float* __restrict__ u, int B, int NA, int NS,
+    float* __restrict__ z_all, float* __restrict__ z_new) {
+  constexpr int NF = 32 * KPL;                        // padded number of new depths
+  __shared__ float s_cdf[kSmWarps][kSmMaxNA];
+  __shared__ float s_bins[kSmWarps][kSmMaxNA];
+  __shared__ float s_zc[kSmWarps][kSmMaxNA];
+  __shared__ float s_f[kSmWarps][NF];
+  __shared__ float s_out[kSmWarps][kSmMaxNA + NF];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* cdf = s_cdf[warp];
+  float* bn = s_bins[warp];
+  float* zc = s_zc[warp];
+  float* sf = s_f[warp];
+  float* so = s_out[warp];
+  const int NB = NA - 1, NW = NA - 2, N = NA + NS;
+  for (int ray = blockIdx.x * kSmWarps + warp; ray < B; ray += gridDim.x * kSmWarps) {
+    const float* zr = z + static_cast<size_t>(ray) * NA;
+    const float* wr = weights + static_cast<size_t>(ray) * NA + 1;      // weights[..., 1:-1]  (scripts/train.py:158)
+    for (int i = lane; i < NA; i += 32) zc[i] = zr[i];
+    __syncwarp();
+    for (int i = lane; i < NB; i += 32) bn[i] = __fmul_rn(0.5f, __fadd_rn(zc[i], zc[i + 1]));   // scripts/train.py:157
+    float part = 0.f;
+    for (int i = lane; i < NW; i += 32) part += __fadd_rn(wr[i], 1e-5f);
+    const float tot = warp_sum(part);
+    for (int i = lane; i < NW; i += 32) cdf[i + 1] = __fdiv_rn(__fadd_rn(wr[i], 1e-5f), tot);
+    bool sorted = true;
+    for (int i = lane; i + 1 < NA; i += 32) sorted = sorted && !(zc[i] > zc[i + 1]);
+    sorted = __all_sync(0xffffffffu, sorted);
+    __syncwarp();
+    pdf_to_cdf_warp(cdf, NW, lane);
+    __syncwarp();
+    float v[KPL];
+#pragma unroll
+    for (int j = 0; j < KPL; ++j) {
+      const int sidx = lane + 32 * j;
+      v[j] = CUDART_INF_F;
+      if (sidx < NS) {
+        const float uu = u[static_cast<size_t>(ray) * NS + sidx];
+        int lo = 0, hi = NB;
+        while (lo < hi) {   // searchsorted(right=True): first index with cdf[idx] > u
+          const int mid = (lo + hi) >> 1;
+          if (cdf[mid] <= uu) lo = mid + 1; else hi = mid;
+        }
+        const int below = max(lo - 1, 0), above = min(lo, NB - 1);
+        const float c0 = cdf[below], c1 = cdf[above];
+        float denom = __fsub_rn(c1, c0);
+        if (denom < 1e-5f) denom = 1.0f;
+        const float t = __fdiv_rn(__fsub_rn(uu, c0), denom);
+        const float b0 = bn[below], b1 = bn[above];
+        v[j] = __fadd_rn(b0, __fmul_rn(t, __fsub_rn(b1, b0)));
+        if (z_new) z_new[static_cast<size_t>(ray) * NS + sidx] = v[j];
+      }
+    }
+    sort_merge_warp<KPL>(v, zc, NA, NS, sorted, sf, so, lane);
+    __syncwarp();
+    for (int i = lane; i < N; i += 32) z_all[static_cast<size_t>(ray) * N + i] = so[i];
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// merge: sort(cat(z_coarse, z_fine)) per ray (scripts/sampling.py:40) for any inputs: the second list is sorted in
+// registers, the first one is merged by rank when it is ascending (the stratified depths are) and goes through the generic
+// shared-memory network otherwise
+// ------------------------------------------------------------------------------------------------
+constexpr int kSortN = 256;
+
+template <int KPL>
+__global__ void __launch_bounds__(kSmWarps * 32) merge_sort_kernel(const float* __restrict__ za, int NA,
+                                                                   const float* __restrict__ zb, int NBn, int B,
+                                                                   float* __restrict__ out) {
+  constexpr int NF = 32 * KPL;
+  __shared__ float s_zc[kSmWarps][kSmMaxNA];
+  __shared__ float s_f[kSmWarps][NF];
+  __shared__ float s_out[kSmWarps][kSmMaxNA + NF];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* zc = s_zc[warp];
+  const int N = NA + NBn;
+  for (int ray = blockIdx.x * kSmWarps + warp; ray < B; ray += gridDim.x * kSmWarps) {
+    for (int i = lane; i < NA; i += 32) zc[i] = za[static_cast<size_t>(ray) * NA + i];
+    float v[KPL];
+#pragma unroll
+    for (int j = 0; j < KPL; ++j) {
+      const int i = lane + 32 * j;
+      v[j] = i < NBn ? zb[static_cast<size_t>(ray) * NBn + i] : CUDART_INF_F;
+    }
+    __syncwarp();
+    bool sorted = true;
+    for (int i = lane; i + 1 < NA; i += 32) sorted = sorted && !(zc[i] > zc[i + 1]);
+    sorted = __all_sync(0xffffffffu, sorted);
+    sort_merge_warp<KPL>(v, zc, NA, NBn, sorted, s_f[warp], s_out[warp], lane);
+    __syncwarp();
+    for (int i = lane; i < N; i += 32) out[static_cast<size_t>(ray) * N + i] = s_out[warp][i];
     __syncwarp();
   }
 }
@@ -164,8 +373,9 @@ extern "C" int dfn_stratified_sample(const float* near, const float* far, const 
   DFN_CHECK_ARG(B >= 0 && S >= 1, "stratified_sample: bad shape B=%d S=%d", B, S);
   const long long n = static_cast<long long>(B) * S;
   if (n == 0) return DFN_OK;
-  stratified_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      near, far, t_vals, t_rand, B, S, z_out);
+  const bool vec = (S % 4 == 0) && ((reinterpret_cast<uintptr_t>(t_rand) | reinterpret_cast<uintptr_t>(z_out)) % 16 == 0);
+  if (vec) stratified_kernel<4><<<grid_for(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out);
+  else stratified_kernel<1><<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out);
   DFN_CHECK_LAUNCH("stratified_sample");
   return DFN_OK;
 }
@@ -209,8 +419,29 @@ extern "C" int dfn_merge_sort_z(const float* z_coarse, int NA, const float* z_fi
   DFN_CHECK_ARG((z_coarse || NA == 0) && (z_fine || NBn == 0) && z_out, "merge_sort_z: null pointer");
   DFN_CHECK_ARG(NA >= 0 && NBn >= 0 && NA + NBn <= kSortN, "merge_sort_z: %d+%d keys exceed %d", NA, NBn, kSortN);
   if (B == 0) return DFN_OK;
-  merge_sort_kernel<<<grid_for(B, kSortWarps), kSortWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      z_coarse, NA, z_fine, NBn, B, z_out);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // the list that goes to registers is the longer one (<= 256 keys); the other one must fit the 128-key shared buffer
+  const bool swap = NA > NBn;
+  const float* a = swap ? z_fine : z_coarse;
+  const float* b = swap ? z_coarse : z_fine;
+  const int na = swap ? NBn : NA, nb = swap ? NA : NBn;
+  if (nb <= 128) merge_sort_kernel<4><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(a, na, b, nb, B, z_out);
+  else merge_sort_kernel<8><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(a, na, b, nb, B, z_out);
   DFN_CHECK_LAUNCH("merge_sort_z");
+  return DFN_OK;
+}
+
+// sample_pdf on (mid-points of z, weights[:, 1:-1]) followed by sort(cat(z, samples)) - the two steps between the coarse and
+// the fine network of scripts/train.py:157-163 - as one launch.  z [B,NA], weights [B,NA] (the full coarse weights),
+// u [B,NS]; z_all [B,NA+NS]; z_new [B,NS] or NULL.
+extern "C" int dfn_sample_merge(const float* z, const float* weights, const float* u, int B, int NA, int NS, float* z_all,
+                                float* z_new, void* stream) {
+  DFN_CHECK_ARG(z && weights && u && z_all, "sample_merge: null pointer");
+  DFN_CHECK_ARG(NA >= 3 && NA <= kSmMaxNA && NS >= 1 && NS <= 256, "sample_merge: NA=%d outside [3,%d] or NS=%d outside [1,256]", NA, kSmMaxNA, NS);
+  if (B == 0) return DFN_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (NS <= 128) sample_merge_kernel<4><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new);
+  else sample_merge_kernel<8><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new);
+  DFN_CHECK_LAUNCH("sample_merge");
   return DFN_OK;
 }

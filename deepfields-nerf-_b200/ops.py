@@ -103,6 +103,19 @@ def merge_sort_z(z_coarse: Tensor, z_fine: Tensor) -> Tensor:
     return out
 
 
+def sample_merge(z: Tensor, weights: Tensor, u: Tensor, want_new: bool = False):
+    """sample_pdf(mid-points of z, weights[:, 1:-1], u) + sort(cat(z, samples)) in one launch (scripts/train.py:157-158,
+    scripts/sampling.py:40); the new depths never reach HBM unless `want_new`.  Returns z_all [B,NA+NS] (, z_new [B,NS])."""
+    z, weights, u = _f32(z, "z"), _f32(weights, "weights"), _f32(u, "u")
+    B, NA = z.shape
+    NS = u.shape[1]
+    assert weights.shape == (B, NA) and u.shape[0] == B
+    z_all = torch.empty(B, NA + NS, device=z.device, dtype=torch.float32)
+    z_new = torch.empty(B, NS, device=z.device, dtype=torch.float32) if want_new else None
+    _lib.call("dfn_sample_merge", z.data_ptr(), weights.data_ptr(), u.data_ptr(), B, NA, NS, z_all.data_ptr(), _ptr(z_new), _stream())
+    return (z_all, z_new) if want_new else z_all
+
+
 # ---- encoding ------------------------------------------------------------------------------------
 def posenc(x: Tensor, freq_bands: Tensor, include_input: bool = True) -> Tensor:
     """scripts/model.py:32-53."""

@@ -44,8 +44,7 @@ def render_rays(model_coarse, model_fine, rays_o, rays_d, near, far, N_samples=6
     z_c = ops.stratified_sample(near, far, sampler.t_vals, t_rand)
     rgb_c, sig_c = ops.mlp_forward(model_coarse._packed, rays=(rays_o, rays_d, z_c))
     rgb_map_c, w_c = ops.composite_forward(rgb_c, sig_c, z_c, white_bg, dist_last)
-    z_new = ops.sample_pdf(z_c, w_c[:, 1:-1], u, bins_mid_of_z=True)
-    z_all = ops.merge_sort_z(z_c, z_new)
+    z_all = ops.sample_merge(z_c, w_c, u)
     evaluated = B * T
     if ert_eps <= 0.0 or ert_segments <= 1:
         rgb_f, sig_f = ops.mlp_forward(model_fine._packed, rays=(rays_o, rays_d, z_all))

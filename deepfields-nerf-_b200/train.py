@@ -207,10 +207,8 @@ class FusedTrainer:
         _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg,
                                                    self.dist_last)
         self._mark("render_loss_coarse")
-        z_new = ops.sample_pdf(z_c, w_c[:, 1:-1], u, bins_mid_of_z=True)
-        self._mark("sample_pdf")
-        z_all = ops.merge_sort_z(z_c, z_new)
-        self._mark("merge_sort")
+        z_all = ops.sample_merge(z_c, w_c, u)          # inverse-CDF resampling + sort in one launch; z_new never reaches HBM
+        self._mark("sample_merge")
         rays_f = (rays_o, rays_d, z_all)
         rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f)
         self._mark("mlp_fwd_fine")
@@ -223,7 +221,7 @@ class FusedTrainer:
                          mark=mk_c)
         ops.mlp_backward(mf._packed, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.dz, self.grads[n:], rays=rays_f,
                          mark=mk_f)
-        self.aux = {"z": z_c, "z_all": z_all, "z_new": z_new, "weights_coarse": w_c}
+        self.aux = {"z": z_c, "z_all": z_all, "weights_coarse": w_c}
         return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
 
     def optimizer_step(self):

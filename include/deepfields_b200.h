@@ -41,6 +41,11 @@ int dfn_sample_pdf_with_cdf(const float* bins, const float* cdf, const float* u,
                             long long* inds_out, void* stream);
 /* torch.sort(cat([z_vals, z_samples]))  scripts/sampling.py:40.  NA+NB <= 256. */
 int dfn_merge_sort_z(const float* z_coarse, int NA, const float* z_fine, int NB, int B, float* z_out, void* stream);
+/* sample_pdf on (mid-points of z, weights[:, 1:-1]) + sort(cat(z, samples)) in one launch (scripts/train.py:157-158 and
+ * scripts/sampling.py:40): z [B,NA], weights [B,NA] = the full coarse weights, u [B,NS]; z_all [B,NA+NS]; z_new [B,NS] or NULL.
+ * Bit-identical to dfn_sample_pdf followed by dfn_merge_sort_z. */
+int dfn_sample_merge(const float* z, const float* weights, const float* u, int B, int NA, int NS, float* z_all, float* z_new,
+                     void* stream);
 
 /* ---- encoding ---------------------------------------------------------------------------------- */
 /* OptimizedPositionalEncoding.forward  scripts/model.py:32-53.  x [P,3], freqs [L] -> out [P, 3*inc + 6L]. */

@@ -142,6 +142,42 @@ def test_merge_sort_bit_exact(D, golden):
         assert torch.equal(out.cpu(), torch.sort(torch.cat([a, b], -1), -1).values)
 
 
+def test_merge_sort_unsorted_and_long_first_list(D):
+    """the rank merge needs an ascending first list; anything else must take the generic network - same values either way"""
+    g = torch.Generator().manual_seed(4)
+    for B, NA, NB in ((50, 64, 128), (9, 200, 40), (5, 128, 128), (3, 100, 156)):
+        a = torch.rand(B, NA, generator=g)                        # NOT sorted
+        a[0] = a[0].sort().values                                # one ascending row, with duplicates across the lists
+        b = torch.rand(B, NB, generator=g)
+        b[0, : min(NA, NB)] = a[0, : min(NA, NB)]
+        out = D.ops.merge_sort_z(a.cuda(), b.cuda())
+        assert torch.equal(out.cpu(), torch.sort(torch.cat([a, b], -1), -1).values)
+
+
+@pytest.mark.parametrize("B,NA,NS", [(48, 64, 128), (1000, 64, 128), (37, 64, 192), (5, 3, 1), (21, 128, 256), (64, 33, 77)])
+def test_sample_merge_equals_sample_pdf_then_merge(D, B, NA, NS):
+    """dfn_sample_merge (one launch, the train step / render path) is bit-identical to dfn_sample_pdf on the mid-points and
+    weights[:, 1:-1] followed by dfn_merge_sort_z (scripts/train.py:157-158 + scripts/sampling.py:40)."""
+    g = torch.Generator().manual_seed(B + NS)
+    z = (torch.rand(B, NA, generator=g) * 4 + 2).sort(-1).values.cuda()
+    w = (torch.rand(B, NA, generator=g) ** 6).cuda()
+    w[: B // 4] = 0.0                                              # all-zero rows -> uniform pdf
+    u = torch.rand(B, NS, generator=g).cuda()
+    u[:, 0] = 0.0
+    z_new_ref = D.ops.sample_pdf(z, w[:, 1:-1], u, bins_mid_of_z=True)
+    z_all_ref = (D.ops.merge_sort_z(z, z_new_ref) if NA + NS <= 256                 # (dfn_merge_sort_z takes at most 256 keys)
+                 else torch.sort(torch.cat([z, z_new_ref], -1), -1).values)
+    z_all, z_new = D.ops.sample_merge(z, w, u, want_new=True)
+    assert torch.equal(z_new, z_new_ref) and torch.equal(z_all, z_all_ref)
+    assert torch.equal(D.ops.sample_merge(z, w, u), z_all_ref)
+    assert torch.equal(z_all_ref, torch.sort(torch.cat([z, z_new_ref], -1), -1).values)
+    # coarse depths that are not ascending (a ray with far < near): the generic network gives the same sorted values
+    zr = z.flip(-1).contiguous()
+    z_all_r, z_new_r = D.ops.sample_merge(zr, w, u, want_new=True)
+    assert torch.equal(z_new_r, D.ops.sample_pdf(zr, w[:, 1:-1], u, bins_mid_of_z=True))
+    assert torch.equal(z_all_r, torch.sort(torch.cat([zr, z_new_r], -1), -1).values)
+
+
 def test_posenc(D, golden):
     x = T(golden["pe_in"]).cuda()
     for L, key in ((10, "pe_L10"), (4, "pe_L4")):

@@ -156,7 +156,7 @@ def test_fused_step_vs_oracle(D, train_mode):
     got = losses.cpu()
     want = torch.stack([ref["loss_coarse"], ref["loss_fine"]]).detach()
     assert torch.allclose(got, want, rtol=2e-2, atol=1e-5), (got, want)
-    # sampler path is bit-exact; the pdf consumes bf16-MLP weights, so compare z_new loosely
+    # sampler path is bit-exact; the pdf consumes bf16-MLP weights, so compare the merged depths loosely
     assert (tr.aux["z"].cpu() - ref["z"]).abs().max() < 1e-6
     assert (tr.aux["weights_coarse"].cpu() - ref["weights_coarse"].detach()).abs().max() < 2e-2
     assert (tr.aux["z_all"].cpu() - ref["z_all"]).abs().mean() < 2e-2
