@@ -45,6 +45,10 @@ SIGNATURES = {
     "dfn_sample_pdf_with_cdf": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "dfn_merge_sort_z": (_i, [_p, _i, _p, _i, _i, _p, _p]),
     "dfn_sample_merge": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),
+    "dfn_stratified_sample_rng": (_i, [_p, _p, _p, C.c_ulonglong, _p, _i, _i, _p, _p]),
+    "dfn_sample_merge_rng": (_i, [_p, _p, C.c_ulonglong, _p, _i, _i, _i, _p, _p, _p]),
+    "dfn_philox_dump": (_i, [C.c_ulonglong, _p, _u, _ll, _p, _p, _p]),
+    "dfn_mlp_forward_rng": (_i, [C.POINTER(PointSource), _ll, _p, _p, C.c_ulonglong, _p, _u, _p, _p, _p, _p]),
     "dfn_posenc": (_i, [_p, _p, _ll, _i, _i, _p, _p]),
     "dfn_composite_forward": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),
     "dfn_composite_backward": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),
@@ -55,6 +59,9 @@ SIGNATURES = {
     "dfn_mlp_stash_bytes": (_ll, [_ll]),
     "dfn_mlp_dz_bytes": (_ll, [_ll]),
     "dfn_mlp_pack_weights": (_i, [_p, _p, _p, _p, _p]),
+    "dfn_mlp_pack_map_bytes": (_ll, []),
+    "dfn_mlp_build_pack_map": (_i, [_p, _p]),
+    "dfn_mlp_pack_weights_mapped": (_i, [_p, _p, _p, _p, _p, _p]),
     "dfn_mlp_forward": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_mlp_backward": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_mlp_backward_dgrad": (_i, [_ll, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -3,6 +3,7 @@
 // u8 packing (scripts/extract_vol.py:123-206), fused AdamW on the flat parameter buffer
 // (scripts/train.py:244-259).
 #include "dfn_common.cuh"
+#include "rng.cuh"
 
 namespace {
 
@@ -107,6 +108,18 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
 
 __global__ void step_inc_kernel(int* step_ptr) { *step_ptr += 1; }
 
+// the uniforms / normals the in-kernel draws use, written out (known-answer tests of csrc/rng.cuh)
+__global__ void philox_dump_kernel(unsigned long long seed, const int* __restrict__ step_ptr, unsigned stream, long long n,
+                                   float* __restrict__ uniforms, float* __restrict__ normals) {
+  const uint32_t step = static_cast<uint32_t>(*step_ptr);
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 r = rng::uniform4(seed, step, stream, static_cast<unsigned long long>(i));
+    if (uniforms) reinterpret_cast<float4*>(uniforms)[i] = r;
+    if (normals) normals[i] = rng::normal1(seed, step, stream, static_cast<unsigned long long>(i));
+  }
+}
+
 inline int grid1d(long long n, int block) {
   long long g = (n + block - 1) / block;
   const long long cap = static_cast<long long>(dfn_num_sms()) * 8;
@@ -170,5 +183,14 @@ extern "C" int dfn_adamw_step(float* p, const float* g, float* m, float* v, long
                                                weight_decay, grad_scale);
   step_inc_kernel<<<1, 1, 0, st>>>(step_ptr);
   DFN_CHECK_LAUNCH("adamw_step");
+  return DFN_OK;
+}
+
+extern "C" int dfn_philox_dump(unsigned long long seed, const int* step_ptr, unsigned rng_stream, long long n_items, float* uniforms,
+                               float* normals, void* stream) {
+  DFN_CHECK_ARG(step_ptr && (uniforms || normals), "philox_dump: null pointer");
+  if (n_items == 0) return DFN_OK;
+  philox_dump_kernel<<<grid1d(n_items, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(seed, step_ptr, rng_stream, n_items, uniforms, normals);
+  DFN_CHECK_LAUNCH("philox_dump");
   return DFN_OK;
 }

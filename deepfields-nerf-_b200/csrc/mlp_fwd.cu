@@ -23,6 +23,7 @@
 // backward kernels: each epilogue thread stores the 16-byte groups it has rounded straight to global memory
 // (a warp covers 512 contiguous bytes per chunk), after the tile has been published to the issuer.
 #include "mlp_pipe.cuh"
+#include "rng.cuh"
 #include <stdlib.h>
 #include <string.h>
 #include <utility>
@@ -113,6 +114,9 @@ struct FwdArgs {
   const uint8_t* wpack;   // packed forward weights
   const float* consts;    // fp32 consts block
   const float* noise;     // [P] sigma noise or null (model.py:160-162)
+  const int* rng_step;    // non-null (and noise null): the noise is drawn in the kernel, N(0,1) = f(rng_seed, *rng_step, rng_stream, point)
+  unsigned long long rng_seed;
+  unsigned rng_stream;
   float* rgb;             // [P,3]
   float* sigma;           // [P]
   uint8_t* stash_h;       // TRAIN: [8][n_tiles][64 KB]
@@ -386,6 +390,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
                 float s = sdot + part[(t * 128 + row) * 3] + consts[kConstBsig];
                 s = round_bf16(s);
                 if (a.noise) s = round_bf16(s + round_bf16(a.noise[p]));
+                else if (a.rng_step) s = round_bf16(s + round_bf16(rng::normal1(a.rng_seed, static_cast<uint32_t>(*a.rng_step), a.rng_stream, static_cast<unsigned long long>(p))));
                 a.sigma[p] = fmaxf(s, 0.f);
               }
             }
@@ -457,49 +462,69 @@ __device__ __forceinline__ float param_w(const float* params, int layer, int o, 
   return params[po.w[layer] + o * layer_in(layer) + i];
 }
 
-__global__ void pack_weights_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ fwd,
-                                    __nv_bfloat16* __restrict__ bwd, float* __restrict__ consts, int replicas) {
+// Source of every element of the packed images: where in the flat fp32 parameter vector it comes from.  The layout only
+// depends on the architecture, so the index arithmetic (a division chain per element: 33 us per network) runs ONCE into an
+// int32 map; every later repack (after each optimiser step) is a plain gather.
+//   map[idx] >= 0 : params[map[idx]]      map[idx] == -1 : zero
+// idx runs over the forward image (bf16 elements), then the backward image; the fp32 consts block follows with the same coding.
+__device__ __forceinline__ int pack_source(int idx) {
   constexpr ParamOffsets po = param_offsets();
   const int nf = kFwdPackBytes / 2, nb = kBwdPackBytes / 2;
-  const int total = nf + nb + kConstFloats;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+  if (idx < nf) {
+    int j = 0;
+    while (j + 1 < kNumJobs && static_cast<uint32_t>(idx) * 2u >= job_off(j + 1)) ++j;
+    const int e0 = idx - job_off(j) / 2;
+    const int N = job_N(j), NH = N / 2;
+    const int half_elems = job_half_bytes(j) / 2;
+    const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half
+    const int kc = e / (NH * 8), n = r * NH + (e / 8) % NH, k = kc * 8 + (e & 7);
+    const int layer = j < 8 ? j : (j == 8 ? 9 : 10);   // reference layer index of job j
+    const int kdata = job_kc(j) * 8;
+    if (k >= kdata) return k == kdata ? po.b[layer] + n : -1;   // bias slice: column 0 carries the bias, the other 15 are zero
+    const int kin = layer_in(layer);
+    return k < kin ? po.w[layer] + n * kin + k : -1;            // K padding (63 -> 64, 319 -> 320, 283 -> 288) is zero
+  }
+  if (idx < nf + nb) {
+    const int bi = idx - nf;
+    int b = 0;
+    while (b + 1 < kNumBwdJobs && static_cast<uint32_t>(bi) * 2u >= bjob_off(b + 1)) ++b;
+    const int e0 = bi - bjob_off(b) / 2;
+    const int half_elems = bjob_bytes(b) / 4;
+    const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half of W^T's N rows
+    const int kc = e / (128 * 8), i = r * 128 + (e / 8) % 128, o = kc * 8 + (e & 7);
+    const int layer_of[kNumBwdJobs] = {10, 9, 7, 6, 5, 4, 3, 2, 1};
+    const int layer = layer_of[b];
+    return po.w[layer] + o * layer_in(layer) + i;
+  }
+  const int c = idx - nf - nb;
+  if (c < kConstWc2) return po.w[8] + (c - kConstWsig);
+  if (c < kConstBsig) return po.w[11] + (c - kConstWc2);
+  if (c == kConstBsig) return po.b[8];
+  if (c < kConstBc2 + 3) return po.b[11] + (c - kConstBc2);
+  return -1;
+}
+
+constexpr int kPackElems = kFwdPackBytes / 2 + kBwdPackBytes / 2 + kConstFloats;
+
+__global__ void pack_map_kernel(int* __restrict__ map) {
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < kPackElems; idx += gridDim.x * blockDim.x) map[idx] = pack_source(idx);
+}
+
+// map == nullptr: the sources are computed on the fly (dfn_mlp_pack_weights, the self-contained entry point)
+__global__ void pack_weights_kernel(const float* __restrict__ params, const int* __restrict__ map, __nv_bfloat16* __restrict__ fwd,
+                                    __nv_bfloat16* __restrict__ bwd, float* __restrict__ consts, int replicas) {
+  const int nf = kFwdPackBytes / 2, nb = kBwdPackBytes / 2;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < kPackElems; idx += gridDim.x * blockDim.x) {
+    const int src = map ? map[idx] : pack_source(idx);
+    const float v = src >= 0 ? params[src] : 0.f;
     if (idx < nf) {
-      int j = 0;
-      while (j + 1 < kNumJobs && static_cast<uint32_t>(idx) * 2u >= job_off(j + 1)) ++j;
-      const int e0 = idx - job_off(j) / 2;
-      const int N = job_N(j), NH = N / 2;
-      const int half_elems = job_half_bytes(j) / 2;
-      const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half
-      const int kc = e / (NH * 8), n = r * NH + (e / 8) % NH, k = kc * 8 + (e & 7);
-      const int layer = j < 8 ? j : (j == 8 ? 9 : 10);   // reference layer index of job j
-      const int kdata = job_kc(j) * 8;
-      float v = 0.f;
-      if (k >= kdata) {  // bias slice: column 0 carries the bias, the other 15 are zero
-        if (k == kdata) v = params[po.b[layer] + n];
-      } else if (j == 0) { if (k < 63) v = param_w(params, 0, n, k); }
-      else if (j == 4) { if (k < 256 + 63) v = param_w(params, 4, n, k); }
-      else if (j == 9) { if (k < 256 + 27) v = param_w(params, 10, n, k); }
-      else v = param_w(params, layer, n, k);
-      for (int r = 0; r < replicas; ++r) fwd[idx + static_cast<size_t>(r) * nf] = __float2bfloat16_rn(v);
+      const __nv_bfloat16 w = __float2bfloat16_rn(v);
+      for (int r = 0; r < replicas; ++r) fwd[idx + static_cast<size_t>(r) * nf] = w;
     } else if (idx < nf + nb) {
-      const int bi = idx - nf;
-      int b = 0;
-      while (b + 1 < kNumBwdJobs && static_cast<uint32_t>(bi) * 2u >= bjob_off(b + 1)) ++b;
-      const int e0 = bi - bjob_off(b) / 2;
-      const int half_elems = bjob_bytes(b) / 4;
-      const int r = e0 / half_elems, e = e0 % half_elems;   // r: which CTA of the pair holds this half of W^T's N rows
-      const int kc = e / (128 * 8), i = r * 128 + (e / 8) % 128, o = kc * 8 + (e & 7);
-      const int layer_of[kNumBwdJobs] = {10, 9, 7, 6, 5, 4, 3, 2, 1};
-      const __nv_bfloat16 wv = __float2bfloat16_rn(param_w(params, layer_of[b], o, i));
-      for (int r = 0; r < replicas; ++r) bwd[bi + static_cast<size_t>(r) * nb] = wv;
+      const __nv_bfloat16 w = __float2bfloat16_rn(v);
+      for (int r = 0; r < replicas; ++r) bwd[idx - nf + static_cast<size_t>(r) * nb] = w;
     } else {
-      const int c = idx - nf - nb;
-      float v = 0.f;
-      if (c < kConstWc2) v = round_bf16(params[po.w[8] + (c - kConstWsig)]);
-      else if (c < kConstBsig) v = round_bf16(params[po.w[11] + (c - kConstWc2)]);
-      else if (c == kConstBsig) v = round_bf16(params[po.b[8]]);
-      else if (c < kConstBc2 + 3) v = round_bf16(params[po.b[11] + (c - kConstBc2)]);
-      consts[c] = v;
+      consts[idx - nf - nb] = round_bf16(v);
     }
   }
 }
@@ -514,8 +539,26 @@ extern "C" long long dfn_mlp_stash_bytes(long long P) { return stash_total_bytes
 extern "C" int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream) {
   DFN_CHECK_ARG(params && fwd_pack && bwd_pack && consts, "mlp_pack_weights: null pointer");
   pack_weights_kernel<<<dfn_num_sms() * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      params, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts, weight_replicas());
+      params, nullptr, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts, weight_replicas());
   DFN_CHECK_LAUNCH("mlp_pack_weights");
+  return DFN_OK;
+}
+
+// The repack after every optimiser step as a gather through a precomputed source map (dfn_mlp_pack_map_bytes() bytes of int32,
+// filled once by dfn_mlp_build_pack_map; the same map serves every network of this architecture on the device).
+extern "C" long long dfn_mlp_pack_map_bytes(void) { return static_cast<long long>(kPackElems) * 4; }
+extern "C" int dfn_mlp_build_pack_map(int* map, void* stream) {
+  DFN_CHECK_ARG(map, "mlp_build_pack_map: null pointer");
+  pack_map_kernel<<<dfn_num_sms() * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(map);
+  DFN_CHECK_LAUNCH("mlp_build_pack_map");
+  return DFN_OK;
+}
+extern "C" int dfn_mlp_pack_weights_mapped(const float* params, const int* map, void* fwd_pack, void* bwd_pack, float* consts,
+                                           void* stream) {
+  DFN_CHECK_ARG(params && map && fwd_pack && bwd_pack && consts, "mlp_pack_weights_mapped: null pointer");
+  pack_weights_kernel<<<dfn_num_sms() * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      params, map, static_cast<__nv_bfloat16*>(fwd_pack), static_cast<__nv_bfloat16*>(bwd_pack), consts, weight_replicas());
+  DFN_CHECK_LAUNCH("mlp_pack_weights_mapped");
   return DFN_OK;
 }
 
@@ -528,8 +571,9 @@ static int check_source(const dfn_point_source* s, long long P, const char* who)
   return DFN_OK;
 }
 
-extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
-                               const float* noise, float* rgb, float* sigma, void* stash, void* stream) {
+static int mlp_forward_impl(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                            const float* noise, unsigned long long rng_seed, const int* rng_step, unsigned rng_stream, float* rgb,
+                            float* sigma, void* stash, void* stream) {
   if (int rc = check_source(src, P, "mlp_forward")) return rc;
   DFN_CHECK_ARG(fwd_pack && consts && rgb && sigma, "mlp_forward: null pointer");
   DFN_CHECK_ARG(P >= 0 && P < (1LL << 31) * kTile, "mlp_forward: P out of range");
@@ -539,6 +583,7 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   a.skew_ns = skew_ns;
   a.src = *src; a.P = P; a.n_tiles = static_cast<int>(num_tiles(P));
   a.wpack = static_cast<const uint8_t*>(fwd_pack); a.consts = consts; a.noise = noise; a.rgb = rgb; a.sigma = sigma;
+  a.rng_seed = rng_seed; a.rng_step = rng_step; a.rng_stream = rng_stream;
   if (stash) {
     uint8_t* s = static_cast<uint8_t*>(stash);
     a.stash_h = s;
@@ -562,4 +607,18 @@ extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const v
   }
   DFN_CHECK_LAUNCH("mlp_forward");
   return DFN_OK;
+}
+
+extern "C" int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                               const float* noise, float* rgb, float* sigma, void* stash, void* stream) {
+  return mlp_forward_impl(src, P, fwd_pack, consts, noise, 0ull, nullptr, 0u, rgb, sigma, stash, stream);
+}
+
+// training-mode forward with the sigma noise of model.py:160-162 drawn in the kernel (Philox, csrc/rng.cuh):
+// noise(point p) = N(0,1)(seed, *step_ptr, rng_stream, p), rounded to bf16 like randn_like on an autocast tensor
+extern "C" int dfn_mlp_forward_rng(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                                   unsigned long long seed, const int* step_ptr, unsigned rng_stream, float* rgb, float* sigma,
+                                   void* stash, void* stream) {
+  DFN_CHECK_ARG(step_ptr, "mlp_forward_rng: null step pointer");
+  return mlp_forward_impl(src, P, fwd_pack, consts, nullptr, seed, step_ptr, rng_stream, rgb, sigma, stash, stream);
 }

@@ -4,6 +4,7 @@
 // pts = o + d*z (scripts/sampling.py:24-31, :43-48).  All arithmetic that must be bit-identical to the
 // reference's separate torch ops uses explicit round-to-nearest intrinsics (no FMA contraction).
 #include "dfn_common.cuh"
+#include "rng.cuh"
 #include <math_constants.h>
 
 namespace {
@@ -24,10 +25,12 @@ __device__ __forceinline__ float strat_z(float n, float f, const float* __restri
 }
 
 // VEC = 4: S % 4 == 0, one thread per four consecutive samples of a ray (16-byte loads / stores)
+// t_rand == nullptr: the jitter is drawn in the kernel (Philox; item = group of four samples)
 template <int VEC>
 __global__ void stratified_kernel(const float* __restrict__ near, const float* __restrict__ far,
                                   const float* __restrict__ t_vals, const float* __restrict__ t_rand, int B, int S,
-                                  float* __restrict__ z_out) {
+                                  float* __restrict__ z_out, unsigned long long seed, const int* __restrict__ step_ptr) {
+  const uint32_t step = t_rand ? 0u : static_cast<uint32_t>(*step_ptr);
   const long long n_items = static_cast<long long>(B) * S / VEC;
   const unsigned per_ray = static_cast<unsigned>(S / VEC);
   for (long long it = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; it < n_items;
@@ -42,7 +45,8 @@ __global__ void stratified_kernel(const float* __restrict__ near, const float* _
     }
     const float n = __ldg(near + ray), f = __ldg(far + ray);
     if (VEC == 4) {
-      const float4 tr = *reinterpret_cast<const float4*>(t_rand + it * 4);
+      const float4 tr = t_rand ? *reinterpret_cast<const float4*>(t_rand + it * 4)
+                               : rng::uniform4(seed, step, rng::kStreamJitter, static_cast<unsigned long long>(it));
       float4 z;
       z.x = strat_z(n, f, t_vals, i0, S, tr.x);
       z.y = strat_z(n, f, t_vals, i0 + 1, S, tr.y);
@@ -50,7 +54,7 @@ __global__ void stratified_kernel(const float* __restrict__ near, const float* _
       z.w = strat_z(n, f, t_vals, i0 + 3, S, tr.w);
       *reinterpret_cast<float4*>(z_out + it * 4) = z;
     } else {
-      z_out[it] = strat_z(n, f, t_vals, i0, S, t_rand[it]);
+      z_out[it] = strat_z(n, f, t_vals, i0, S, t_rand ? t_rand[it] : rng::uniform4(seed, step, rng::kStreamJitter, static_cast<unsigned long long>(it)).x);
     }
   }
 }
@@ -263,13 +267,14 @@ __device__ __forceinline__ void sort_merge_warp(float (&v)[KPL], const float* zc
 template <int KPL>
 __global__ void __launch_bounds__(kSmWarps * 32) sample_merge_kernel(
     const float* __restrict__ z, const float* __restrict__ weights, const float* __restrict__ u, int B, int NA, int NS,
-    float* __restrict__ z_all, float* __restrict__ z_new) {
+    float* __restrict__ z_all, float* __restrict__ z_new, unsigned long long seed, const int* __restrict__ step_ptr) {
   constexpr int NF = 32 * KPL;                        // padded number of new depths
+  const uint32_t step = u ? 0u : static_cast<uint32_t>(*step_ptr);   // u == nullptr: the draws come from Philox
   __shared__ float s_cdf[kSmWarps][kSmMaxNA];
   __shared__ float s_bins[kSmWarps][kSmMaxNA];
   __shared__ float s_zc[kSmWarps][kSmMaxNA];
   __shared__ float s_f[kSmWarps][NF];
-  __shared__ float s_out[kSmWarps][kSmMaxNA + NF];
+  __shared__ float s_out[kSmWarps][NF <= 128 ? 256 : 512];   // the generic network pads NA + NS keys to a power of two
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* cdf = s_cdf[warp];
   float* bn = s_bins[warp];
@@ -294,12 +299,20 @@ __global__ void __launch_bounds__(kSmWarps * 32) sample_merge_kernel(
     pdf_to_cdf_warp(cdf, NW, lane);
     __syncwarp();
     float v[KPL];
+    float ur[KPL];
+    if (!u) {
+#pragma unroll
+      for (int j4 = 0; j4 < KPL / 4; ++j4) {   // item = (ray, lane, group of four draws)
+        const float4 r = rng::uniform4(seed, step, rng::kStreamPdf, (static_cast<unsigned long long>(ray) * 32 + lane) * (KPL / 4) + j4);
+        ur[4 * j4] = r.x; ur[4 * j4 + 1] = r.y; ur[4 * j4 + 2] = r.z; ur[4 * j4 + 3] = r.w;
+      }
+    }
 #pragma unroll
     for (int j = 0; j < KPL; ++j) {
       const int sidx = lane + 32 * j;
       v[j] = CUDART_INF_F;
       if (sidx < NS) {
-        const float uu = u[static_cast<size_t>(ray) * NS + sidx];
+        const float uu = u ? u[static_cast<size_t>(ray) * NS + sidx] : ur[j];
         int lo = 0, hi = NB;
         while (lo < hi) {   // searchsorted(right=True): first index with cdf[idx] > u
           const int mid = (lo + hi) >> 1;
@@ -336,7 +349,7 @@ __global__ void __launch_bounds__(kSmWarps * 32) merge_sort_kernel(const float* 
   constexpr int NF = 32 * KPL;
   __shared__ float s_zc[kSmWarps][kSmMaxNA];
   __shared__ float s_f[kSmWarps][NF];
-  __shared__ float s_out[kSmWarps][kSmMaxNA + NF];
+  __shared__ float s_out[kSmWarps][NF <= 128 ? 256 : 512];   // the generic network pads NA + NS keys to a power of two
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* zc = s_zc[warp];
   const int N = NA + NBn;
@@ -374,8 +387,8 @@ extern "C" int dfn_stratified_sample(const float* near, const float* far, const 
   const long long n = static_cast<long long>(B) * S;
   if (n == 0) return DFN_OK;
   const bool vec = (S % 4 == 0) && ((reinterpret_cast<uintptr_t>(t_rand) | reinterpret_cast<uintptr_t>(z_out)) % 16 == 0);
-  if (vec) stratified_kernel<4><<<grid_for(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out);
-  else stratified_kernel<1><<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out);
+  if (vec) stratified_kernel<4><<<grid_for(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out, 0ull, nullptr);
+  else stratified_kernel<1><<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, t_rand, B, S, z_out, 0ull, nullptr);
   DFN_CHECK_LAUNCH("stratified_sample");
   return DFN_OK;
 }
@@ -440,8 +453,36 @@ extern "C" int dfn_sample_merge(const float* z, const float* weights, const floa
   DFN_CHECK_ARG(NA >= 3 && NA <= kSmMaxNA && NS >= 1 && NS <= 256, "sample_merge: NA=%d outside [3,%d] or NS=%d outside [1,256]", NA, kSmMaxNA, NS);
   if (B == 0) return DFN_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (NS <= 128) sample_merge_kernel<4><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new);
-  else sample_merge_kernel<8><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new);
+  if (NS <= 128) sample_merge_kernel<4><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new, 0ull, nullptr);
+  else sample_merge_kernel<8><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, u, B, NA, NS, z_all, z_new, 0ull, nullptr);
   DFN_CHECK_LAUNCH("sample_merge");
+  return DFN_OK;
+}
+
+// The same two entry points with the draws made IN the kernel (Philox4x32-10, csrc/rng.cuh): draw = f(seed, *step_ptr, item),
+// step_ptr = the optimiser's step counter in device memory, so CUDA-graph replays advance and ranks differ through the seed.
+extern "C" int dfn_stratified_sample_rng(const float* near, const float* far, const float* t_vals, unsigned long long seed,
+                                         const int* step_ptr, int B, int S, float* z_out, void* stream) {
+  DFN_CHECK_ARG(near && far && t_vals && step_ptr && z_out, "stratified_sample_rng: null pointer");
+  DFN_CHECK_ARG(B >= 0 && S >= 1, "stratified_sample_rng: bad shape B=%d S=%d", B, S);
+  const long long n = static_cast<long long>(B) * S;
+  if (n == 0) return DFN_OK;
+  if (S % 4 == 0 && reinterpret_cast<uintptr_t>(z_out) % 16 == 0)
+    stratified_kernel<4><<<grid_for(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, nullptr, B, S, z_out, seed, step_ptr);
+  else
+    stratified_kernel<1><<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(near, far, t_vals, nullptr, B, S, z_out, seed, step_ptr);
+  DFN_CHECK_LAUNCH("stratified_sample_rng");
+  return DFN_OK;
+}
+
+extern "C" int dfn_sample_merge_rng(const float* z, const float* weights, unsigned long long seed, const int* step_ptr, int B,
+                                    int NA, int NS, float* z_all, float* z_new, void* stream) {
+  DFN_CHECK_ARG(z && weights && step_ptr && z_all, "sample_merge_rng: null pointer");
+  DFN_CHECK_ARG(NA >= 3 && NA <= kSmMaxNA && NS >= 1 && NS <= 256, "sample_merge_rng: NA=%d outside [3,%d] or NS=%d outside [1,256]", NA, kSmMaxNA, NS);
+  if (B == 0) return DFN_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (NS <= 128) sample_merge_kernel<4><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, nullptr, B, NA, NS, z_all, z_new, seed, step_ptr);
+  else sample_merge_kernel<8><<<grid_for(B, kSmWarps), kSmWarps * 32, 0, st>>>(z, weights, nullptr, B, NA, NS, z_all, z_new, seed, step_ptr);
+  DFN_CHECK_LAUNCH("sample_merge_rng");
   return DFN_OK;
 }

@@ -49,6 +49,32 @@ def stratified_sample(near: Tensor, far: Tensor, t_vals: Tensor, t_rand: Tensor)
     return z
 
 
+RNG_JITTER, RNG_PDF, RNG_NOISE_COARSE, RNG_NOISE_FINE = 1, 2, 3, 4   # stream ids of csrc/rng.cuh
+
+
+def _step_ptr(step: Tensor) -> int:
+    assert step.dtype == torch.int32 and step.is_cuda and step.numel() == 1
+    return step.data_ptr()
+
+
+def stratified_sample_rng(near: Tensor, far: Tensor, t_vals: Tensor, seed: int, step: Tensor) -> Tensor:
+    """stratified_sample with the jitter drawn in the kernel (Philox: f(seed, step counter on the device, sample))."""
+    near, far = _f32(near.reshape(-1), "near"), _f32(far.reshape(-1), "far")
+    B, S = near.numel(), t_vals.numel()
+    z = torch.empty(B, S, device=near.device, dtype=torch.float32)
+    _lib.call("dfn_stratified_sample_rng", near.data_ptr(), far.data_ptr(), _f32(t_vals, "t_vals").data_ptr(), int(seed),
+              _step_ptr(step), B, S, z.data_ptr(), _stream())
+    return z
+
+
+def philox_dump(seed: int, step: Tensor, rng_stream: int, n_items: int, normals: bool = False) -> Tensor:
+    """The uniforms [n,4] (or normals [n]) the in-kernel draws produce for items 0..n-1 (tests)."""
+    out = torch.empty(n_items if normals else (n_items, 4), device=step.device, dtype=torch.float32)
+    _lib.call("dfn_philox_dump", int(seed), _step_ptr(step), int(rng_stream), int(n_items), None if normals else out.data_ptr(),
+              out.data_ptr() if normals else None, _stream())
+    return out
+
+
 def points_on_rays(rays_o: Tensor, rays_d: Tensor, z: Tensor, want_dirs: bool = True):
     """scripts/sampling.py:24-31.  Returns pts [B*S,3] (and dirs [B*S,3])."""
     z = _f32(z, "z")
@@ -103,16 +129,25 @@ def merge_sort_z(z_coarse: Tensor, z_fine: Tensor) -> Tensor:
     return out
 
 
-def sample_merge(z: Tensor, weights: Tensor, u: Tensor, want_new: bool = False):
+def sample_merge(z: Tensor, weights: Tensor, u: Optional[Tensor], want_new: bool = False, n_new: Optional[int] = None,
+                 rng: Optional[Tuple[int, Tensor]] = None):
     """sample_pdf(mid-points of z, weights[:, 1:-1], u) + sort(cat(z, samples)) in one launch (scripts/train.py:157-158,
-    scripts/sampling.py:40); the new depths never reach HBM unless `want_new`.  Returns z_all [B,NA+NS] (, z_new [B,NS])."""
-    z, weights, u = _f32(z, "z"), _f32(weights, "weights"), _f32(u, "u")
+    scripts/sampling.py:40); the new depths never reach HBM unless `want_new`.  Returns z_all [B,NA+NS] (, z_new [B,NS]).
+    u = None with rng = (seed, step counter tensor): the n_new draws per ray are made in the kernel (Philox)."""
+    z, weights = _f32(z, "z"), _f32(weights, "weights")
     B, NA = z.shape
-    NS = u.shape[1]
-    assert weights.shape == (B, NA) and u.shape[0] == B
+    NS = int(n_new) if u is None else u.shape[1]
+    assert weights.shape == (B, NA)
     z_all = torch.empty(B, NA + NS, device=z.device, dtype=torch.float32)
     z_new = torch.empty(B, NS, device=z.device, dtype=torch.float32) if want_new else None
-    _lib.call("dfn_sample_merge", z.data_ptr(), weights.data_ptr(), u.data_ptr(), B, NA, NS, z_all.data_ptr(), _ptr(z_new), _stream())
+    if u is None:
+        seed, step = rng
+        _lib.call("dfn_sample_merge_rng", z.data_ptr(), weights.data_ptr(), int(seed), _step_ptr(step), B, NA, NS, z_all.data_ptr(),
+                  _ptr(z_new), _stream())
+    else:
+        u = _f32(u, "u")
+        assert u.shape[0] == B
+        _lib.call("dfn_sample_merge", z.data_ptr(), weights.data_ptr(), u.data_ptr(), B, NA, NS, z_all.data_ptr(), _ptr(z_new), _stream())
     return (z_all, z_new) if want_new else z_all
 
 
@@ -185,16 +220,27 @@ class PackedMLP:
     """bf16 operand images of one OptimizedVanillaNeRF (hidden 256, L 10/4) built from the flat fp32
     parameter vector (reference named_parameters() order)."""
 
+    _maps: Dict[str, Tensor] = {}   # per device: the int32 source map of the packed images (architecture-only, built once)
+
     def __init__(self, device):
         lib = _lib.load()
         self.fwd = torch.empty(lib.dfn_mlp_fwd_pack_bytes(), dtype=torch.uint8, device=device)
         self.bwd = torch.empty(lib.dfn_mlp_bwd_pack_bytes(), dtype=torch.uint8, device=device)
         self.consts = torch.empty(lib.dfn_mlp_consts_bytes() // 4, dtype=torch.float32, device=device)
 
+    def _map(self) -> Tensor:
+        key = str(self.fwd.device)
+        m = PackedMLP._maps.get(key)
+        if m is None:
+            m = torch.empty(_lib.load().dfn_mlp_pack_map_bytes() // 4, dtype=torch.int32, device=self.fwd.device)
+            _lib.call("dfn_mlp_build_pack_map", m.data_ptr(), _stream())
+            PackedMLP._maps[key] = m
+        return m
+
     def pack(self, flat_params: Tensor) -> None:
         p = _f32(flat_params, "flat_params")
         assert p.numel() == MLP_NUM_PARAMS, p.numel()
-        _lib.call("dfn_mlp_pack_weights", p.data_ptr(), self.fwd.data_ptr(), self.bwd.data_ptr(),
+        _lib.call("dfn_mlp_pack_weights_mapped", p.data_ptr(), self._map().data_ptr(), self.fwd.data_ptr(), self.bwd.data_ptr(),
                   self.consts.data_ptr(), _stream())
 
 
@@ -237,8 +283,10 @@ def mlp_dz_bytes(P: int) -> int:
 
 
 def mlp_forward(packed: PackedMLP, *, pos=None, view=None, rays=None, grid=None, noise: Optional[Tensor] = None,
-                stash: Optional[Tensor] = None, out: Optional[Tuple[Tensor, Tensor]] = None):
-    """OptimizedVanillaNeRF.forward (scripts/model.py:173-187).  Returns (rgb [P,3], sigma [P]) fp32."""
+                stash: Optional[Tensor] = None, out: Optional[Tuple[Tensor, Tensor]] = None,
+                noise_rng: Optional[Tuple[int, Tensor, int]] = None):
+    """OptimizedVanillaNeRF.forward (scripts/model.py:173-187).  Returns (rgb [P,3], sigma [P]) fp32.
+    noise_rng = (seed, step counter tensor, stream id): the sigma noise of model.py:160-162 is drawn in the kernel."""
     s, P, keep = _source(pos, view, rays, grid)
     dev = packed.fwd.device
     if out is None:
@@ -251,6 +299,11 @@ def mlp_forward(packed: PackedMLP, *, pos=None, view=None, rays=None, grid=None,
         assert noise.numel() == P
     if stash is not None:
         assert stash.is_cuda and stash.dtype == torch.uint8 and stash.numel() >= mlp_stash_bytes(P)
+    if noise is None and noise_rng is not None:
+        seed, step, sid = noise_rng
+        _lib.call("dfn_mlp_forward_rng", C.byref(s), P, packed.fwd.data_ptr(), packed.consts.data_ptr(), int(seed), _step_ptr(step),
+                  int(sid), rgb.data_ptr(), sigma.data_ptr(), _ptr(stash), _stream())
+        return rgb, sigma
     _lib.call("dfn_mlp_forward", C.byref(s), P, packed.fwd.data_ptr(), packed.consts.data_ptr(), _ptr(noise),
               rgb.data_ptr(), sigma.data_ptr(), _ptr(stash), _stream())
     return rgb, sigma

@@ -103,7 +103,11 @@ class FusedTrainer:
 
     def __init__(self, model_coarse: OptimizedVanillaNeRF, model_fine: OptimizedVanillaNeRF, N_samples=64,
                  N_importance=128, lr=5e-4, total_steps=1000, white_bg=False, dist_last=1e10, weight_decay=1e-6,
-                 train_noise=True, process_group=None):
+                 train_noise=True, process_group=None, rng="kernel", seed=None, use_graph=None):
+        """rng: "kernel" = jitter / inverse-CDF draws / sigma noise are drawn inside the kernels (Philox keyed by `seed`
+        and the step counter: no draw reaches HBM, graph-replayable), "torch" = torch.rand / torch.randn tensors as in
+        round 1; injected draws (parity tests) always win.  seed: defaults to 0x5EED + 7919 * rank (per-rank streams,
+        SURVEY 8e).  use_graph: replay the step as CUDA graphs (default: DFN_CUDA_GRAPH=1)."""
         dev = next(model_coarse.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("FusedTrainer needs CUDA models (no CPU fallback)")
@@ -112,6 +116,11 @@ class FusedTrainer:
         self.train_noise = train_noise
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if self._dist_on() else 1
+        rank = torch.distributed.get_rank(process_group) if self._dist_on() else 0
+        self.rng = rng
+        self.seed = int(seed) if seed is not None else 0x5EED + 7919 * rank
+        self.use_graph = (os.environ.get("DFN_CUDA_GRAPH", "0") == "1") if use_graph is None else bool(use_graph)
+        self._graphs = {}
         self.models = (model_coarse, model_fine)
         n = ops.MLP_NUM_PARAMS
         # re-home both models into one flat buffer
@@ -141,6 +150,8 @@ class FusedTrainer:
         self.profile = False
         self._marks = []
         self.launches_per_step = 0
+        self._pending = []
+        self._static, self._graph_misses = None, 0
 
     # ---- stage timing -----------------------------------------------------------------------------------
     def _mark(self, name, launches=1):
@@ -184,49 +195,79 @@ class FusedTrainer:
         S, I, T = self.S, self.I, self.S + self.I
         self._alloc(B)
         mc, mf = self.models
-        if t_rand is None:
+        kern = self.rng == "kernel"
+        if t_rand is None and not kern:
             t_rand = torch.rand(B, S, device=self.dev)
-        if u is None:
+        if u is None and not kern:
             u = torch.rand(B, I, device=self.dev)
+        rng_c = rng_f = None
         if self.train_noise:
             if noise_c is None:
-                noise_c = torch.randn(B * S, device=self.dev)
+                if kern:
+                    rng_c = (self.seed, self.step_dev, ops.RNG_NOISE_COARSE)
+                else:
+                    noise_c = torch.randn(B * S, device=self.dev)
             if noise_f is None:
-                noise_f = torch.randn(B * T, device=self.dev)
+                if kern:
+                    rng_f = (self.seed, self.step_dev, ops.RNG_NOISE_FINE)
+                else:
+                    noise_f = torch.randn(B * T, device=self.dev)
         self._n_launch = 0
         self._mark("begin", 0)
         self.loss_sum.zero_()
         self.grads.zero_()
         self._mark("zero", 0)  # torch memsets, not kernels of this library
         n = ops.MLP_NUM_PARAMS
-        z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
+        if t_rand is None:
+            z_c = ops.stratified_sample_rng(near, far, self.sampler.t_vals, self.seed, self.step_dev)
+        else:
+            z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
         self._mark("stratified")
         rays_c = (rays_o, rays_d, z_c)
-        rgb_c, sig_c = ops.mlp_forward(mc._packed, rays=rays_c, noise=noise_c, stash=self.stash_c, out=self.out_c)
+        rgb_c, sig_c = ops.mlp_forward(mc._packed, rays=rays_c, noise=noise_c, stash=self.stash_c, out=self.out_c, noise_rng=rng_c)
         self._mark("mlp_fwd_coarse")
         _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg,
                                                    self.dist_last)
         self._mark("render_loss_coarse")
-        z_all = ops.sample_merge(z_c, w_c, u)          # inverse-CDF resampling + sort in one launch; z_new never reaches HBM
+        # inverse-CDF resampling + sort in one launch; z_new never reaches HBM
+        z_all = ops.sample_merge(z_c, w_c, u, n_new=I, rng=(self.seed, self.step_dev))
         self._mark("sample_merge")
         rays_f = (rays_o, rays_d, z_all)
-        rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f)
+        rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f, noise_rng=rng_f)
         self._mark("mlp_fwd_fine")
         _, _, d_rgb_f, d_sig_f = ops.render_loss(rgb_f, sig_f, z_all, target, self.loss_sum[1:2], self.white_bg,
                                                  self.dist_last, want_weights=False)
         self._mark("render_loss_fine")
         mk_c = lambda nm: self._mark(nm + "_coarse")  # noqa: E731
         mk_f = lambda nm: self._mark(nm + "_fine")  # noqa: E731
-        ops.mlp_backward(mc._packed, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.dz, self.grads[:n], rays=rays_c,
-                         mark=mk_c)
-        ops.mlp_backward(mf._packed, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.dz, self.grads[n:], rays=rays_f,
-                         mark=mk_f)
+        # fine network first: its half of the flat gradient is all-reduced while the coarse network's backward runs
+        self._bwd(mf, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.grads[n:], rays_f, mk_f)
+        self._reduce_async(self.grads[n:])
+        self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, mk_c)
+        self._reduce_async(self.grads[:n])
         self.aux = {"z": z_c, "z_all": z_all, "weights_coarse": w_c}
         return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
 
-    def optimizer_step(self):
+    def _bwd(self, model, rgb, sig, d_rgb, d_sig, stash, grads, rays, mark):
+        if ops.bwd_fused_default():
+            P = rgb.shape[0]
+            if getattr(self, "_ws", None) is None or self._ws.numel() < ops.mlp_bwd_fused_ws_bytes(P):
+                self._ws = torch.empty(ops.mlp_bwd_fused_ws_bytes(P), dtype=torch.uint8, device=self.dev)
+            ops.mlp_backward_fused(model._packed, rgb, sig, d_rgb, d_sig, stash, self._ws, grads, rays=rays)
+            mark("bwd_fused")
+        else:
+            ops.mlp_backward(model._packed, rgb, sig, d_rgb, d_sig, stash, self.dz, grads, rays=rays, mark=mark)
+
+    def _reduce_async(self, g):
+        """Data-parallel exchange of one network's gradient, started as soon as it is complete (NCCL runs on the process
+        group's stream; the optimiser waits for it)."""
         if self.world > 1:
-            torch.distributed.all_reduce(self.grads, group=self.pg)
+            self._pending.append(torch.distributed.all_reduce(g, group=self.pg, async_op=True))
+
+    def optimizer_step(self):
+        for w in self._pending:
+            w.wait()
+        self._pending = []
         ops.adamw_step(self.flat, self.grads, self.m, self.v, self.lr_table, self.b1_table, self.step_dev,
                        weight_decay=self.wd, grad_scale=1.0 / self.world)
         self._mark("adamw")
@@ -236,7 +277,68 @@ class FusedTrainer:
         self._mark("pack_weights", 2)
         self.launches_per_step = self._n_launch
 
+    # ---- CUDA-graph replay of the step ------------------------------------------------------------------------------------
+    def _graph_for(self, tensors):
+        """The whole step (world == 1) or its forward/backward and optimiser halves around the eager NCCL all-reduce
+        (world > 1), captured once per distinct set of input buffers and replayed afterwards.  Everything that changes from
+        step to step lives in device memory (step counter -> OneCycleLR tables and the Philox counter), so a replay IS the
+        next step."""
+        key = tuple(t.data_ptr() for t in tensors) + (tensors[0].shape[0],)
+        g = self._graphs.get(key)
+        if g is None:
+            stream = torch.cuda.Stream(device=self.dev)
+            stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(stream):           # warm-up outside the capture (allocations, lazy initialisation)
+                self.forward_backward(*tensors)
+                self.optimizer_step()
+            torch.cuda.current_stream().wait_stream(stream)
+            torch.cuda.synchronize()
+            fb, opt = torch.cuda.CUDAGraph(), None
+            if self.world == 1:
+                with torch.cuda.graph(fb):
+                    losses = self.forward_backward(*tensors)
+                    self.optimizer_step()
+            else:
+                with torch.cuda.graph(fb):
+                    losses = self._forward_backward_no_reduce(*tensors)
+                opt = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(opt):
+                    self.optimizer_step()
+            g = (fb, opt, losses, tensors)            # `tensors` kept alive: the graph reads their buffers
+            self._graphs[key] = g
+            if len(self._graphs) > 64:
+                self._graphs.pop(next(iter(self._graphs)))
+        return g
+
+    def _forward_backward_no_reduce(self, *tensors):
+        world, self.world = self.world, 1
+        try:
+            return self.forward_backward(*tensors)
+        finally:
+            self.world = world
+
     def step(self, rays_o, rays_d, near, far, target, **draws):
+        if self.use_graph and not draws and not self.profile and self.rng == "kernel":
+            tensors = (rays_o, rays_d, near, far, target)
+            if not all(t.is_contiguous() for t in tensors):
+                tensors = tuple(t.contiguous() for t in tensors)
+            key = tuple(t.data_ptr() for t in tensors) + (tensors[0].shape[0],)
+            if key not in self._graphs and self._graph_misses >= 8:
+                # a stream of fresh input tensors (RayStore gathers): copy them into static buffers the graph reads
+                B = tensors[0].shape[0]
+                if self._static is None or self._static[0].shape[0] != B:
+                    self._static = tuple(torch.empty_like(t) for t in tensors)
+                for dst, src in zip(self._static, tensors):
+                    dst.copy_(src)
+                tensors = self._static
+            elif key not in self._graphs:
+                self._graph_misses += 1
+            fb, opt, losses, _ = self._graph_for(tensors)
+            fb.replay()
+            if opt is not None:
+                torch.distributed.all_reduce(self.grads, group=self.pg)
+                opt.replay()
+            return losses
         losses = self.forward_backward(rays_o, rays_d, near, far, target, **draws)
         self.optimizer_step()
         return losses

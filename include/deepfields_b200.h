@@ -47,6 +47,20 @@ int dfn_merge_sort_z(const float* z_coarse, int NA, const float* z_fine, int NB,
 int dfn_sample_merge(const float* z, const float* weights, const float* u, int B, int NA, int NS, float* z_all, float* z_new,
                      void* stream);
 
+/* ---- in-kernel random draws (csrc/rng.cuh: Philox4x32-10, draw = f(seed, *step_ptr, stream id, item)) -----------------
+ * The reference draws inside sampling.py:20 (torch.rand), train.py:53 (torch.rand) and model.py:162 (randn_like); the entry
+ * points above take those draws as tensors (parity tests inject the reference's), the ones below make them in the kernel:
+ * no draw ever reaches HBM, CUDA-graph replays advance through the step counter in device memory (step_ptr = the counter
+ * dfn_adamw_step increments), ranks use different seeds. */
+int dfn_stratified_sample_rng(const float* near, const float* far, const float* t_vals, unsigned long long seed,
+                              const int* step_ptr, int B, int S, float* z_out, void* stream);
+int dfn_sample_merge_rng(const float* z, const float* weights, unsigned long long seed, const int* step_ptr, int B, int NA,
+                         int NS, float* z_all, float* z_new, void* stream);
+/* what the kernels draw, written out: uniforms [n_items,4], normals [n_items] (either may be NULL); rng_stream: 1 jitter,
+ * 2 inverse-CDF draws, 3 / 4 sigma noise of the coarse / fine network */
+int dfn_philox_dump(unsigned long long seed, const int* step_ptr, unsigned rng_stream, long long n_items, float* uniforms,
+                    float* normals, void* stream);
+
 /* ---- encoding ---------------------------------------------------------------------------------- */
 /* OptimizedPositionalEncoding.forward  scripts/model.py:32-53.  x [P,3], freqs [L] -> out [P, 3*inc + 6L]. */
 int dfn_posenc(const float* x, const float* freqs, long long P, int L, int include_input, float* out, void* stream);
@@ -95,12 +109,21 @@ long long dfn_mlp_dz_bytes(long long P);    /* pre-activation gradients kept by 
 /* fp32 parameters (flat, DFN_MLP_NUM_PARAMS) -> bf16 operand images for the kernels.  Called after
  * load_state_dict and after every optimiser step. */
 int dfn_mlp_pack_weights(const float* params, void* fwd_pack, void* bwd_pack, float* consts, void* stream);
+/* the same repack as a gather through a precomputed source map (the layout depends on the architecture only): build the map
+ * once per device (dfn_mlp_pack_map_bytes() bytes of int32), then repack with it after every optimiser step */
+long long dfn_mlp_pack_map_bytes(void);
+int dfn_mlp_build_pack_map(int* map, void* stream);
+int dfn_mlp_pack_weights_mapped(const float* params, const int* map, void* fwd_pack, void* bwd_pack, float* consts, void* stream);
 
 /* OptimizedVanillaNeRF.forward  scripts/model.py:173-187 on P points: rgb [P,3], sigma [P] (fp32 values of the
  * bf16 computation).  noise [P] or NULL = the randn_like draw of model.py:162 (training mode).
  * stash != NULL keeps the activations the backward needs (dfn_mlp_stash_bytes). */
 int dfn_mlp_forward(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
                     const float* noise, float* rgb, float* sigma, void* stash, void* stream);
+/* the same in training mode with the sigma noise drawn in the kernel: noise(point p) = N(0,1)(seed, *step_ptr, rng_stream, p) */
+int dfn_mlp_forward_rng(const dfn_point_source* src, long long P, const void* fwd_pack, const float* consts,
+                        unsigned long long seed, const int* step_ptr, unsigned rng_stream, float* rgb, float* sigma, void* stash,
+                        void* stream);
 /* backward of the above w.r.t. the parameters: d_rgb [P,3], d_sigma [P] (fp32), rgb/sigma = forward outputs,
  * stash from the forward, dz = scratch of dfn_mlp_dz_bytes(P).  grads [DFN_MLP_NUM_PARAMS] fp32 is ACCUMULATED
  * into (zero it first). */

@@ -407,3 +407,112 @@ def test_mlp_backward_multi_iteration_equals_chunked(D):
     for k in got:
         assert rel_err(got[k], ref[k]) < 2e-3, (k, rel_err(got[k], ref[k]))
     assert float(grads.abs().sum()) > 0
+
+
+# ---- in-kernel draws (Philox), mapped weight repack, CUDA-graph replay ---------------------------------------------
+def _philox4x32_10(ctr, key):
+    """Reference Philox4x32-10 (Salmon et al., SC'11) in Python integers."""
+    M0, M1, W0, W1, MASK = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85, 0xFFFFFFFF
+    c, k = list(ctr), list(key)
+    for _ in range(10):
+        p0, p1 = M0 * c[0], M1 * c[2]
+        c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & MASK, (p0 >> 32) ^ c[3] ^ k[1], p0 & MASK]
+        k = [(k[0] + W0) & MASK, (k[1] + W1) & MASK]
+    return c
+
+
+def test_philox_known_answers_and_kernel_draws(D):
+    # known-answer vectors of the Random123 distribution (kat_vectors: philox4x32 10 rounds)
+    assert _philox4x32_10([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert _philox4x32_10([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert _philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    step = torch.tensor([5], dtype=torch.int32, device="cuda")
+    seed = (0x299f31d0 << 32) | 0xa4093822
+    n = 1000
+    got = D.ops.philox_dump(seed, step, 2, n).cpu()
+    for i in (0, 1, 17, 999):
+        w = _philox4x32_10([i, 0, 5, 2], [seed & 0xffffffff, seed >> 32])
+        want = torch.tensor([(x >> 8) * 2.0 ** -24 for x in w])
+        assert torch.equal(got[i], want), i
+    # the kernels consume exactly these draws: jitter of the stratified sampler, inverse-CDF draws of sample_merge
+    B, S, I = 300, 64, 128
+    o, d, near, far, _ = make_rays(4, B)
+    t_vals = torch.linspace(0, 1, S, device="cuda")
+    z = D.ops.stratified_sample_rng(near.cuda(), far.cuda(), t_vals, seed, step)
+    t_rand = D.ops.philox_dump(seed, step, 1, B * S // 4).reshape(B, S)
+    assert torch.equal(z, D.ops.stratified_sample(near.cuda(), far.cuda(), t_vals, t_rand))
+    w = torch.rand(B, S, device="cuda") ** 4
+    za = D.ops.sample_merge(z, w, None, n_new=I, rng=(seed, step))
+    u4 = D.ops.philox_dump(seed, step, 2, B * 32).reshape(B, 32, 4)           # item = (ray, lane): draws of samples lane + 32 j
+    u = u4.permute(0, 2, 1).reshape(B, I).contiguous()
+    assert torch.equal(za, D.ops.sample_merge(z, w, u))
+    # uniform in [0,1), mean / variance of U(0,1) and N(0,1)
+    big = D.ops.philox_dump(seed, step, 1, 1 << 18)
+    assert float(big.min()) >= 0.0 and float(big.max()) < 1.0
+    assert abs(float(big.mean()) - 0.5) < 2e-3 and abs(float(big.var()) - 1 / 12) < 1e-3
+    nrm = D.ops.philox_dump(seed, step, 3, 1 << 18, normals=True)
+    assert abs(float(nrm.mean())) < 5e-3 and abs(float(nrm.std()) - 1.0) < 5e-3 and bool(torch.isfinite(nrm).all())
+    step2 = torch.tensor([6], dtype=torch.int32, device="cuda")
+    assert not torch.equal(D.ops.philox_dump(seed, step2, 1, 64), big[:64])     # the step counter advances the stream
+
+
+def test_kernel_noise_matches_injected_noise(D):
+    """dfn_mlp_forward_rng == dfn_mlp_forward fed with the normals the kernel draws (model.py:160-162 in training mode)."""
+    P = 1000
+    sd = make_state_dict(5, 256)
+    pk = D.ops.PackedMLP("cuda")
+    pk.pack(flat_params(sd).cuda())
+    g = torch.Generator(device="cuda").manual_seed(2)
+    pos = torch.rand(P, 3, device="cuda", generator=g) * 2 - 1
+    view = torch.nn.functional.normalize(torch.randn(P, 3, device="cuda", generator=g), dim=-1)
+    step = torch.tensor([3], dtype=torch.int32, device="cuda")
+    noise = D.ops.philox_dump(77, step, D.ops.RNG_NOISE_FINE, P, normals=True)
+    r1, s1 = D.ops.mlp_forward(pk, pos=pos, view=view, noise=noise)
+    r2, s2 = D.ops.mlp_forward(pk, pos=pos, view=view, noise_rng=(77, step, D.ops.RNG_NOISE_FINE))
+    assert torch.equal(r1, r2) and torch.equal(s1, s2)
+    r3, s3 = D.ops.mlp_forward(pk, pos=pos, view=view)
+    assert not torch.equal(s1, s3)
+
+
+def test_mapped_weight_pack_equals_direct_pack(D):
+    sd = make_state_dict(9, 256)
+    flat = flat_params(sd).cuda()
+    pk = D.ops.PackedMLP("cuda")
+    pk.pack(flat)                                       # gather through the precomputed source map
+    ref = D.ops.PackedMLP("cuda")
+    D._lib.call("dfn_mlp_pack_weights", flat.data_ptr(), ref.fwd.data_ptr(), ref.bwd.data_ptr(), ref.consts.data_ptr(),
+                torch.cuda.current_stream().cuda_stream)
+    assert torch.equal(pk.fwd, ref.fwd) and torch.equal(pk.bwd, ref.bwd) and torch.equal(pk.consts, ref.consts)
+
+
+def test_graph_replay_equals_eager_steps(D):
+    """Steps replayed as CUDA graphs == the same steps run eagerly (same seed => same in-kernel draws).  The weight-gradient
+    flush adds fp32 partial sums with atomics in a different order every run, and AdamW's first steps turn a last-bit difference
+    of a near-zero gradient into a difference of the order of lr, so two EAGER runs of the same steps already differ; the
+    graph run must be no further from an eager run than a second eager run is (x5), and its losses must agree step by step."""
+    B, S, I = 256, 64, 128
+    batches = [tuple(t.cuda() if t.shape[-1] != 1 else t.reshape(-1).cuda() for t in make_rays(50 + i, B)) for i in range(2)]
+    seq = [0, 0, 1, 1, 0, 1]                       # what the graph run executes: warm-up(0), replay(0), warm-up(1), replay(1), replay(0), replay(1)
+
+    def run(use_graph):
+        mc, mf = D.get_nerf_models(device="cuda")
+        mc.load_state_dict(make_state_dict(31, 256))
+        mf.load_state_dict(make_state_dict(32, 256))
+        tr = D.FusedTrainer(mc, mf, S, I, total_steps=50, seed=123, use_graph=use_graph)
+        order = [0, 1, 0, 1] if use_graph else seq
+        losses = [tr.step(*batches[b]).clone() for b in order]
+        torch.cuda.synchronize()
+        assert int(tr.step_dev.item()) == len(seq)
+        return tr.flat.clone(), torch.stack(losses)
+
+    e1, l1 = run(False)
+    e2, l2 = run(False)
+    g1, lg = run(True)
+    rel = lambda a, b: float((a - b).norm() / b.norm())  # noqa: E731
+    base = rel(e2, e1)
+    assert rel(g1, e1) <= max(5.0 * base, 1e-5), (rel(g1, e1), base)
+    # the replayed steps are steps 2, 4, 5, 6 of the eager sequence
+    assert torch.allclose(lg, l1[[1, 3, 4, 5]], rtol=2e-3, atol=1e-6), (lg, l1)
+    assert bool(torch.isfinite(g1).all())
+    print(f"graph replay: rel L2 distance to eager {rel(g1, e1):.2e}; eager to eager {base:.2e}")
