@@ -69,7 +69,6 @@ SIGNATURES = {
     "dfn_mlp_bwd_fused_ws_bytes": (_ll, [_ll]),
     "dfn_mlp_backward_fused": (_i, [C.POINTER(PointSource), _ll, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "dfn_umma_selftest": (_i, [_p, _p, _i, _i, _i, _i, _u, _u, _u, _u, _u, _u, _p, _p]),
-    "dfn_umma_bench": (_i, [_i, _i, _i, _i, _i, _i, _p, _p]),
     "dfn_grid_points": (_i, [_p, _i, _ll, _ll, _p, _p]),
     "dfn_histogram": (_i, [_p, _ll, _f, _f, _i, _p, _p]),
     "dfn_pack_volume": (_i, [_p, _p, _ll, _f, _p, _p, _p]),

@@ -1,5 +1,5 @@
 """Loader for the reference's cfg/*.yml files: flat YAML namespace with OmegaConf-style ${key} / ${a.b}
-interpolation (cfg/base_cfg.yml:3-6,42-46).  omegaconf itself is used when installed."""
+interpolation (cfg/base_cfg.yml:3-6,42-46).  A self-contained loader: omegaconf is not required (nor used)."""
 from __future__ import annotations
 
 import re

@@ -37,15 +37,18 @@ void dfn_set_error(const char* fmt, ...);
     }                                                                             \
   } while (0)
 
+// SM count of the CURRENT device (cached per device: one process may drive several GPUs)
 static inline int dfn_num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
+  static int cache[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const int slot = dev >= 0 && dev < 64 ? dev : 0;
+  if (cache[slot] == 0) {
+    int n = 0;
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
+    cache[slot] = n > 0 ? n : 148;
   }
-  return n;
+  return cache[slot];
 }
 
 // ---- device helpers ---------------------------------------------------------------------------

@@ -522,12 +522,9 @@ extern "C" int dfn_hashgrid_backward(const float* pos, long long P, const void* 
          8ull * (coarse_entries + g->size[n_lv]) <= 160 * 1024)
     coarse_entries += g->size[n_lv++];
   if (n_lv > 0 && P >= 4096) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      DFN_CUDA(cudaFuncSetAttribute(hashgrid_backward_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024),
-               "dfn_hashgrid_backward");
-      attr_set = true;
-    }
+    // (set on every launch: the attribute belongs to the function in the CURRENT device's context)
+    DFN_CUDA(cudaFuncSetAttribute(hashgrid_backward_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024),
+             "dfn_hashgrid_backward");
     long long nb = (P * n_lv + 1023) / 1024;
     if (nb > dfn_num_sms()) nb = dfn_num_sms();
     hashgrid_backward_coarse_kernel<<<(int)nb, 1024, 8ull * coarse_entries, (cudaStream_t)stream>>>(
@@ -569,11 +566,7 @@ extern "C" int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_str
          coarse_bytes + 4ull * g->size[smem_levels] <= 80 * 1024)
     coarse_bytes += 4ull * g->size[smem_levels++];
   const size_t smem = kWHalves * 2 + kLevels * sizeof(LevelDev) + coarse_bytes;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DFN_CUDA(cudaFuncSetAttribute(ngp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024), "dfn_ngp_forward");
-    attr_set = true;
-  }
+  DFN_CUDA(cudaFuncSetAttribute(ngp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024), "dfn_ngp_forward");
   const long long tiles = (P + 31) / 32;
   long long blocks = (tiles + kNgpWarps - 1) / kNgpWarps;
   const long long cap = 2ll * dfn_num_sms();

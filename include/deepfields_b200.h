@@ -152,9 +152,6 @@ int dfn_umma_selftest(const void* a_tile, const void* b_tile, int N, int K, int 
                       unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, unsigned a_kstep, unsigned b_kstep,
                       float* d_out, void* stream);
 
-/* bring-up microbenchmark (tools/umma_bench.py): tcgen05.mma issue rate under a commit/wait pattern (mode 0 K-major,
- * 2 MN-major), TMEM drain rate of 8 warps (mode 1), both together (mode 3); cycles_out [grid] device int64. */
-int dfn_umma_bench(int mode, int iters, int group, int depth, int N, int grid, long long* cycles_out, void* stream);
 
 /* ---- dense grid / volume (scripts/extract_vol.py:57-206) ---------------------------------------- */
 int dfn_grid_points(const float* lin, int R, long long start, long long count, float* out, void* stream);

@@ -4,8 +4,8 @@
 //   mode bit 1: fence.proxy.async + mbarrier arrive after every tile (what publish() does)
 //   mode bit 2: stores go through shared memory + one 64 KB bulk copy (TMA) per tile instead of STG.128
 //   mode bit 3: st.global.cs (streaming) instead of default stores
-#include "dfn_common.cuh"
-#include "umma.cuh"
+#include "../../deepfields-nerf-_b200/csrc/dfn_common.cuh"
+#include "../../deepfields-nerf-_b200/csrc/umma.cuh"
 
 namespace {
 using namespace umma;

@@ -1,8 +1,8 @@
 // Bring-up microbenchmarks (not on the product path): issue-rate of tcgen05.mma under different
 // commit / wait patterns and the TMEM -> register drain rate of the epilogue warps.  Results feed the
 // pipeline design notes in DESIGN.md.
-#include "dfn_common.cuh"
-#include "umma.cuh"
+#include "../../deepfields-nerf-_b200/csrc/dfn_common.cuh"
+#include "../../deepfields-nerf-_b200/csrc/umma.cuh"
 
 namespace {
 using namespace umma;

@@ -3,7 +3,9 @@ import os, sys, ctypes as C
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepfields_nerf_b200 as d
-lib = d._lib.load()
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "micro"))
+import build as _mb
+lib = C.CDLL(_mb.LIB if os.path.exists(_mb.LIB) else _mb.build())   # tools/micro/libdfn_microbench.so, not the product library
 fn = lib.dfn_pair_mma_bench; fn.restype = C.c_int
 fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
 buf = torch.empty(2 << 30, dtype=torch.uint8, device='cuda')

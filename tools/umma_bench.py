@@ -3,7 +3,20 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepfields_nerf_b200 as d
-from deepfields_nerf_b200 import _lib
+import ctypes as C
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "micro"))
+import build as _mb
+_mlib = C.CDLL(_mb.LIB if os.path.exists(_mb.LIB) else _mb.build())
+_mlib.dfn_umma_bench.restype = C.c_int
+_mlib.dfn_umma_bench.argtypes = [C.c_int] * 6 + [C.c_void_p, C.c_void_p]
+
+
+class _lib:  # the probes live in tools/micro/libdfn_microbench.so, not in the product library
+    @staticmethod
+    def call(name, *args):
+        rc = getattr(_mlib, name)(*args)
+        if rc != 0:
+            raise RuntimeError(f"{name} failed ({rc})")
 
 def run(mode, iters, group, depth, N, grid):
     out = torch.zeros(grid, dtype=torch.int64, device="cuda")
