@@ -6,7 +6,7 @@ from . import _lib, ops  # noqa: F401
 from .sampling import StratifiedSampler  # noqa: F401
 from .model import OptimizedPositionalEncoding, OptimizedVanillaNeRF, get_nerf_models, InstantNGP  # noqa: F401
 from .train import (  # noqa: F401
-    sample_pdf, raw2outputs, process_rays_in_chunks, forward_pass, FusedTrainer, RayStore, onecycle_tables, train,
+    sample_pdf, raw2outputs, process_rays_in_chunks, forward_pass, FusedTrainer, NGPTrainer, RayStore, onecycle_tables, train,
 )
 from .extract_vol import (  # noqa: F401
     generate_3d_grid, volume_extraction, apply_otsu_threshold, save_volume, extract_volume_fused, gather_slabs, global_stats,
@@ -19,6 +19,6 @@ from .config import load_config  # noqa: F401
 
 __all__ = [
     "StratifiedSampler", "OptimizedPositionalEncoding", "OptimizedVanillaNeRF", "get_nerf_models", "InstantNGP", "sample_pdf",
-    "raw2outputs", "process_rays_in_chunks", "forward_pass", "FusedTrainer", "RayStore", "onecycle_tables", "train", "generate_3d_grid",
+    "raw2outputs", "process_rays_in_chunks", "forward_pass", "FusedTrainer", "NGPTrainer", "RayStore", "onecycle_tables", "train", "generate_3d_grid",
     "volume_extraction", "apply_otsu_threshold", "save_volume", "extract_volume_fused", "load_config", "ops", "get_rays", "ray_cube_intersection", "ray_cube_intersection_numpy", "precompute_rays_on_device", "volume_points", "slice_aabb", "render_rays", "render_image", "row_range", "gather_rows", "gather_slabs", "global_stats", "slab_range",
 ]

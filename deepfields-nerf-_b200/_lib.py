@@ -88,6 +88,10 @@ SIGNATURES = {
     "dfn_hashgrid_backward": (_i, [_p, _ll, _p, C.POINTER(HashGrid), _f, _p, _p]),
     "dfn_sh4_encode": (_i, [_p, _ll, _p, _p]),
     "dfn_ngp_forward": (_i, [_p, _p, _i, _ll, _p, C.POINTER(HashGrid), _p, _p, _p, _p, _p]),
+    "dfn_ngp_forward_f32": (_i, [_p, _p, _i, _i, _ll, _p, C.POINTER(HashGrid), _p, _p, _p, _p, _p]),
+    "dfn_ngp_backward": (_i, [_p, _p, _i, _i, _ll, _p, C.POINTER(HashGrid), _p, _p, _p, _p, _f, _p, _p, _p, _p]),
+    "dfn_adamw_step_shadow": (_i, [_p, _p, _p, _p, _ll, _p, _p, _p, _i, _f, _f, _f, _f, _p, _p, _p]),
+    "dfn_nonfinite_flag": (_i, [_p, _ll, _p, _p]),
     "dfn_adamw_step": (_i, [_p, _p, _p, _p, _ll, _p, _p, _p, _i, _f, _f, _f, _f, _p]),
 }
 

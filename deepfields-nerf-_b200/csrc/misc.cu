@@ -4,6 +4,7 @@
 // (scripts/train.py:244-259).
 #include "dfn_common.cuh"
 #include "rng.cuh"
+#include <cuda_fp16.h>
 
 namespace {
 
@@ -108,6 +109,47 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
 
 __global__ void step_inc_kernel(int* step_ptr) { *step_ptr += 1; }
 
+// flag[0] = 1 if any gradient is inf / NaN (flag must be zero on entry): the guard torch.amp.GradScaler puts in front of
+// optimizer.step (scripts/train.py:262-323) as one pass over the flat gradient
+__global__ void nonfinite_flag_kernel(const float* __restrict__ g, long long n, int* __restrict__ flag) {
+  bool bad = false;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float v = g[i];
+    bad = bad || !(fabsf(v) <= 3.4028234e38f);
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
+// adamw_kernel + an fp16 copy of the updated parameters (the operands the Instant-NGP kernels read) + skip when *skip != 0
+__global__ void adamw_shadow_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                    float* __restrict__ v, long long n, const float* __restrict__ lr_table,
+                                    const float* __restrict__ beta1_table, const int* __restrict__ step_ptr, int table_len,
+                                    float beta2, float eps, float wd, float grad_scale, __half* __restrict__ shadow,
+                                    const int* __restrict__ skip) {
+  if (skip && *skip != 0) return;
+  const int step0 = *step_ptr;
+  const int ti = step0 < table_len ? step0 : table_len - 1;
+  const float lr = lr_table[ti], b1 = beta1_table[ti];
+  const float t = static_cast<float>(step0 + 1);
+  const float bc1 = 1.0f - powf(b1, t);
+  const float bc2 = 1.0f - powf(beta2, t);
+  const float step_size = lr / bc1;
+  const float bc2_sqrt = sqrtf(bc2);
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float gi = g[i] * grad_scale;
+    float pi = p[i] * (1.0f - lr * wd);
+    const float mi = b1 * m[i] + (1.0f - b1) * gi;
+    const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    pi -= step_size * (mi / denom);
+    p[i] = pi; m[i] = mi; v[i] = vi;
+    shadow[i] = __float2half_rn(pi);
+  }
+}
+__global__ void step_inc_unless_kernel(int* step_ptr, const int* skip) { if (!skip || *skip == 0) *step_ptr += 1; }
+
 // the uniforms / normals the in-kernel draws use, written out (known-answer tests of csrc/rng.cuh)
 __global__ void philox_dump_kernel(unsigned long long seed, const int* __restrict__ step_ptr, unsigned stream, long long n,
                                    float* __restrict__ uniforms, float* __restrict__ normals) {
@@ -192,5 +234,31 @@ extern "C" int dfn_philox_dump(unsigned long long seed, const int* step_ptr, uns
   if (n_items == 0) return DFN_OK;
   philox_dump_kernel<<<grid1d(n_items, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(seed, step_ptr, rng_stream, n_items, uniforms, normals);
   DFN_CHECK_LAUNCH("philox_dump");
+  return DFN_OK;
+}
+
+// AdamW(+OneCycleLR tables) on a flat fp32 buffer that also refreshes an fp16 copy of the parameters (what the Instant-NGP
+// kernels read: tcnn casts its fp32 master parameters to fp16 per call).  skip_flag (nullable, device int): the update and the
+// step increment are skipped when it is non-zero - set it with dfn_nonfinite_flag, the guard GradScaler.step applies.
+extern "C" int dfn_adamw_step_shadow(float* p, const float* g, float* m, float* v, long long n, const float* lr_table,
+                                     const float* beta1_table, int* step_ptr, int table_len, float beta2, float eps,
+                                     float weight_decay, float grad_scale, void* shadow_f16, const int* skip_flag, void* stream) {
+  DFN_CHECK_ARG(p && g && m && v && lr_table && beta1_table && step_ptr && shadow_f16 && table_len > 0, "adamw_step_shadow: bad args");
+  if (n == 0) return DFN_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  adamw_shadow_kernel<<<grid1d(n, 256), 256, 0, st>>>(p, g, m, v, n, lr_table, beta1_table, step_ptr, table_len, beta2, eps,
+                                                      weight_decay, grad_scale, static_cast<__half*>(shadow_f16), skip_flag);
+  step_inc_unless_kernel<<<1, 1, 0, st>>>(step_ptr, skip_flag);
+  DFN_CHECK_LAUNCH("adamw_step_shadow");
+  return DFN_OK;
+}
+
+extern "C" int dfn_nonfinite_flag(const float* g, long long n, int* flag, void* stream) {
+  DFN_CHECK_ARG(g && flag, "nonfinite_flag: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DFN_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st), "nonfinite_flag");
+  if (n == 0) return DFN_OK;
+  nonfinite_flag_kernel<<<grid1d(n, 256), 256, 0, st>>>(g, n, flag);
+  DFN_CHECK_LAUNCH("nonfinite_flag");
   return DFN_OK;
 }

@@ -184,19 +184,33 @@ class _TcnnParams(nn.Module):
         self.params = nn.Parameter(torch.zeros(n_params, dtype=torch.float32))
 
 
-class _HashGridEncode(torch.autograd.Function):
-    """Hash-grid encode with its scatter-add backward (both hand-written kernels, csrc/ngp.cu)."""
+class _NGPFunction(torch.autograd.Function):
+    """InstantNGP.forward under autograd on this library's kernels only: forward = the fused query (encode + both tiny MLPs in
+    one launch), backward = dfn_ngp_backward (recompute + mma.sync dgrad / wgrad + table scatter-add in one launch)."""
 
     @staticmethod
-    def forward(ctx, pos, params, grid):
-        ctx.grid = grid
-        ctx.save_for_backward(pos)
-        return ops.hashgrid_forward(pos, params.detach().half(), grid)
+    def forward(ctx, module, pos, view, table_p, dmlp_p, cmlp_p):
+        table, dw, cw = module._half_params()
+        rgb, features = ops.ngp_forward(pos, view, table, module.grid, dw, cw)
+        ctx.module, ctx.pos, ctx.view = module, pos, view
+        return rgb, features
 
     @staticmethod
-    def backward(ctx, d_out):
-        (pos,) = ctx.saved_tensors
-        return None, ops.hashgrid_backward(pos, d_out.contiguous(), ctx.grid), None
+    def backward(ctx, d_rgb, d_features):
+        m = ctx.module
+        table, dw, cw = m._half_params()
+        if d_features is not None and d_features.shape[1] > 1 and bool(d_features[:, 1:].any()):
+            raise NotImplementedError("InstantNGP: only sigma (feature 0) and rgb carry gradients on the fused training path; "
+                                      "the other 15 density features are consumed inside the kernel")
+        P = ctx.pos.shape[0]
+        dev = ctx.pos.device
+        d_rgb = torch.zeros(P, 3, device=dev) if d_rgb is None else d_rgb.float().contiguous()
+        d_sig = torch.zeros(P, device=dev) if d_features is None else d_features[:, 0].float().contiguous()
+        g_t = torch.zeros(2 * m.grid.n_entries, device=dev)
+        g_d = torch.zeros(ops.NGP_DMLP_PARAMS, device=dev)
+        g_c = torch.zeros(ops.NGP_CMLP_PARAMS, device=dev)
+        ops.ngp_backward(ctx.pos, ctx.view, table, m.grid, dw, cw, d_rgb, d_sig, g_t, g_d, g_c)
+        return None, None, None, g_t, g_d, g_c
 
 
 class InstantNGP(nn.Module):
@@ -204,8 +218,8 @@ class InstantNGP(nn.Module):
     submodule names, `query_density(pos) -> (sigma, features)` and `forward(pos, viewdirs) -> (rgb, sigma)` returning
     fp16 like tcnn.  The arithmetic of tiny-cuda-nn (un-vendored, commit 74ea173d) is restated: parity unpinned
     (DESIGN.md section 2).  Inference (no grad) is ONE fused launch (`dfn_ngp_forward`); with grad enabled the hash-grid
-    encode and its scatter-add backward are the kernels and the two 10 k-parameter MLPs run as plain fp16 library GEMMs
-    under autograd."""
+    backward is ONE more launch of this library (csrc/ngp_train.cu: recompute + mma.sync dgrad / wgrad + table scatter-add):
+    no library GEMM anywhere on the path."""
 
     LOG2_SIZE = {"small": 15, "medium": 17, "large": 19}
 
@@ -243,27 +257,18 @@ class InstantNGP(nn.Module):
             raise RuntimeError(f"InstantNGP: {name} must be a CUDA tensor (no CPU fallback)")
         return x.reshape(-1, 3).float()
 
-    def _mlp(self, x, params, shapes, out_act):
-        o = 0
-        for k, (r, c) in enumerate(shapes):
-            w = params[o:o + r * c].view(r, c).half()
-            o += r * c
-            x = x @ w.t()
-            x = torch.relu(x) if k + 1 < len(shapes) else out_act(x)
-        return x
-
-    def _features_autograd(self, pos):
-        enc = _HashGridEncode.apply(pos, self.pos_encoding.params, self.grid)
-        return self._mlp(enc, self.dmlp.params, ((64, 32), (16, 64)), torch.relu)
-
     def _training_path(self):
         return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+
+    def _fused_autograd(self, pos, view):
+        return _NGPFunction.apply(self, pos, view, self.pos_encoding.params, self.dmlp.params, self.cmlp.params)
 
     def query_density(self, pos):
         """instantngp.py:66-80"""
         pos = self._flat(pos, "pos")
         if self._training_path():
-            features = self._features_autograd(pos)
+            # (gradients flow through sigma = feature 0 only; the colour head is evaluated with a dummy view and discarded)
+            _, features = self._fused_autograd(pos, torch.tensor([0.5, 0.5, 0.5], device=pos.device))
         else:
             table, dw, cw = self._half_params()
             _, features = ops.ngp_forward(pos, None, table, self.grid, dw, cw, want_features=True, want_rgb=False)
@@ -273,16 +278,14 @@ class InstantNGP(nn.Module):
         """instantngp.py:82-104.  `noise` (the vanilla model's injected sigma noise) is accepted and ignored: this variant
         adds none (:77-80)."""
         pos = self._flat(pos, "pos")
-        if self._training_path():
-            features = self._features_autograd(pos)
-            x = torch.cat([features, ops.sh4_encode(self._flat(viewdirs, "viewdirs"))], dim=-1)
-            rgb = self._mlp(x, self.cmlp.params, ((64, 32), (64, 64), (16, 64)), torch.sigmoid)[:, :3]
-            return rgb, features[:, :1]
-        table, dw, cw = self._half_params()
         view = viewdirs.float()
         if view.numel() != 3 and not (view.dim() == 2 and view.stride(0) == 0):
             view = self._flat(view, "viewdirs")
         else:
             view = view.reshape(-1, 3)[0]  # an expanded canonical view (extract_vol.py:100) stays one direction
+        if self._training_path():
+            rgb, features = self._fused_autograd(pos, view.contiguous())
+            return rgb, features[:, :1]
+        table, dw, cw = self._half_params()
         rgb, features = ops.ngp_forward(pos, view, table, self.grid, dw, cw)
         return rgb, features[:, :1]

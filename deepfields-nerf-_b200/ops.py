@@ -536,6 +536,23 @@ def adamw_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, bet
               float(weight_decay), float(grad_scale), _stream())
 
 
+def adamw_step_shadow(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr_table: Tensor, beta1_table: Tensor, step: Tensor,
+                      shadow: Tensor, skip_flag: Optional[Tensor] = None, beta2=0.999, eps=1e-8, weight_decay=1e-6,
+                      grad_scale=1.0) -> None:
+    """adamw_step that also refreshes `shadow` (fp16 copy of p) and is skipped when skip_flag[0] != 0 (nonfinite_flag)."""
+    assert step.dtype == torch.int32 and step.is_cuda and shadow.dtype == torch.float16 and shadow.numel() == p.numel()
+    _lib.call("dfn_adamw_step_shadow", _f32(p, "p").data_ptr(), _f32(g, "g").data_ptr(), _f32(m, "m").data_ptr(),
+              _f32(v, "v").data_ptr(), p.numel(), _f32(lr_table, "lr_table").data_ptr(),
+              _f32(beta1_table, "beta1_table").data_ptr(), step.data_ptr(), lr_table.numel(), float(beta2), float(eps),
+              float(weight_decay), float(grad_scale), shadow.data_ptr(), _ptr(skip_flag), _stream())
+
+
+def nonfinite_flag(g: Tensor, flag: Tensor) -> None:
+    """flag[0] (int32, device) = 1 iff g holds an inf / NaN: GradScaler's guard in front of optimizer.step."""
+    assert flag.dtype == torch.int32 and flag.is_cuda
+    _lib.call("dfn_nonfinite_flag", _f32(g, "g").data_ptr(), g.numel(), flag.data_ptr(), _stream())
+
+
 # ---- Instant-NGP variant (scripts/instantngp.py) ---------------------------------------------------
 NGP_LEVELS = 16
 NGP_DMLP_PARAMS = 64 * 32 + 16 * 64
@@ -617,3 +634,38 @@ def ngp_forward(pos: Tensor, dirs: Optional[Tensor], table: Tensor, grid, dmlp_w
     _lib.call("dfn_ngp_forward", pos.data_ptr(), _ptr(dirs) if want_rgb else None, stride, P, table.data_ptr(), C.byref(grid),
               dmlp_w.data_ptr(), cmlp_w.data_ptr(), _ptr(feat), _ptr(rgb), _stream())
     return rgb, feat
+
+
+def _dirs_args(dirs: Tensor, P: int, dirs_group: int):
+    dirs = _f32(dirs, "dirs")
+    if dirs.numel() == 3:
+        return dirs.reshape(3), 0, 1
+    assert dirs.dim() == 2 and dirs.shape[1] == 3 and dirs.shape[0] * dirs_group == P, (dirs.shape, P, dirs_group)
+    return dirs, 3, int(dirs_group)
+
+
+def ngp_forward_f32(pos: Tensor, dirs: Tensor, table: Tensor, grid, dmlp_w: Tensor, cmlp_w: Tensor, dirs_group: int = 1,
+                    out: Optional[Tuple[Tensor, Tensor]] = None) -> Tuple[Tensor, Tensor]:
+    """InstantNGP.forward as ONE launch with fp32 outputs for the compositing kernels: rgb [P,3], sigma [P] (fp16 values).
+    dirs: [P / dirs_group, 3] (dirs_group consecutive points share a direction: the samples of a ray) or one direction [3]."""
+    pos, table = _pos(pos, "pos"), _f16(table, "table")
+    P = pos.shape[0]
+    d, stride, group = _dirs_args(dirs, P, dirs_group)
+    rgb, sigma = out if out is not None else (torch.empty(P, 3, device=pos.device), torch.empty(P, device=pos.device))
+    _lib.call("dfn_ngp_forward_f32", pos.data_ptr(), d.data_ptr(), stride, group, P, table.data_ptr(), C.byref(grid),
+              _f16(dmlp_w, "dmlp_w").data_ptr(), _f16(cmlp_w, "cmlp_w").data_ptr(), rgb.data_ptr(), sigma.data_ptr(), _stream())
+    return rgb, sigma
+
+
+def ngp_backward(pos: Tensor, dirs: Tensor, table: Tensor, grid, dmlp_w: Tensor, cmlp_w: Tensor, d_rgb: Tensor, d_sigma: Tensor,
+                 d_table: Tensor, d_dmlp: Tensor, d_cmlp: Tensor, dirs_group: int = 1, loss_scale: float = 128.0) -> None:
+    """Accumulates d loss / d (table, density MLP, colour MLP) (fp32) from d loss / d rgb [P,3], d loss / d sigma [P]: ONE
+    launch, the forward is recomputed in registers (csrc/ngp_train.cu)."""
+    pos, table = _pos(pos, "pos"), _f16(table, "table")
+    P = pos.shape[0]
+    d, stride, group = _dirs_args(dirs, P, dirs_group)
+    assert d_table.numel() == 2 * grid.n_entries and d_dmlp.numel() == NGP_DMLP_PARAMS and d_cmlp.numel() == NGP_CMLP_PARAMS
+    _lib.call("dfn_ngp_backward", pos.data_ptr(), d.data_ptr(), stride, group, P, table.data_ptr(), C.byref(grid),
+              _f16(dmlp_w, "dmlp_w").data_ptr(), _f16(cmlp_w, "cmlp_w").data_ptr(), _f32(d_rgb.reshape(-1, 3), "d_rgb").data_ptr(),
+              _f32(d_sigma.reshape(-1), "d_sigma").data_ptr(), float(loss_scale), _f32(d_table, "d_table").data_ptr(),
+              _f32(d_dmlp, "d_dmlp").data_ptr(), _f32(d_cmlp, "d_cmlp").data_ptr(), _stream())

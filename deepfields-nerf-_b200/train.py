@@ -523,63 +523,186 @@ def train(cfg_in):
     return tr
 
 
+class NGPTrainer:
+    """One training step of scripts/train.py:282-323 with cfg.ngp true (:219-220: ONE InstantNGP is both the coarse and the
+    fine model) as launches of this library only - no autograd graph, no library GEMM:
+        stratified z (in-kernel jitter) -> points -> fused query (encode + both tiny MLPs) -> compositing + MSE + backward
+        -> inverse-CDF resampling + sort -> points -> fused query -> compositing + MSE + backward
+        -> fused backward of the query for the fine and the coarse points (recompute + mma.sync dgrad / wgrad + table
+        scatter-add, gradients accumulate) -> [ONE NCCL all-reduce of the flat gradient] -> non-finite guard ->
+        fused AdamW(+OneCycleLR) on the flat fp32 parameters, which also refreshes their fp16 copy.
+    All parameters (hash table, density MLP, colour MLP) live in ONE flat fp32 buffer in the module's parameter order; the
+    nn.Parameters are views of it, so state_dict() keeps the reference keys (pos_encoding.params, dmlp.params, cmlp.params).
+    Like the reference, world coordinates and view directions go to the encodings unnormalised (instantngp.py:77,98).
+    tiny-cuda-nn parity is unpinned; loss_scale = tcnn's default 128, steps with a non-finite gradient are
+    skipped as torch.amp.GradScaler.step does (train.py:262-323)."""
+
+    def __init__(self, model, N_samples=64, N_importance=128, lr=5e-4, total_steps=1000, white_bg=False, dist_last=1e10,
+                 weight_decay=1e-6, process_group=None, seed=None, loss_scale=128.0):
+        dev = model.pos_encoding.params.device
+        if dev.type != "cuda":
+            raise RuntimeError("NGPTrainer needs a CUDA model (no CPU fallback)")
+        self.model, self.dev, self.S, self.I = model, dev, N_samples, N_importance
+        self.white_bg, self.dist_last, self.wd, self.loss_scale = white_bg, dist_last, weight_decay, float(loss_scale)
+        self.pg = process_group
+        dist_on = torch.distributed.is_available() and torch.distributed.is_initialized()
+        self.world = torch.distributed.get_world_size(process_group) if dist_on else 1
+        rank = torch.distributed.get_rank(process_group) if dist_on else 0
+        self.seed = int(seed) if seed is not None else 0x5EED + 7919 * rank
+        ps = [model.pos_encoding.params, model.dmlp.params, model.cmlp.params]
+        self.sizes = [p.numel() for p in ps]
+        n = sum(self.sizes)
+        self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+        off = 0
+        for p in ps:
+            c = p.numel()
+            self.flat[off:off + c].copy_(p.detach().reshape(-1))
+            p.data = self.flat[off:off + c]
+            off += c
+        self.half = self.flat.half()                      # the operands of the kernels, refreshed by the optimiser
+        self.grads = torch.zeros_like(self.flat)
+        self.m, self.v = torch.zeros_like(self.flat), torch.zeros_like(self.flat)
+        lrs, b1s = onecycle_tables(total_steps, lr)
+        self.lr_table = torch.tensor(lrs, dtype=torch.float32, device=dev)
+        self.b1_table = torch.tensor(b1s, dtype=torch.float32, device=dev)
+        self.total_steps = total_steps
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.skip = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.sampler = StratifiedSampler(N_samples, dev)
+        self.loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.profile, self._marks = False, []
+
+    def _views(self, buf):
+        t, d = self.sizes[0], self.sizes[1]
+        return buf[:t], buf[t:t + d], buf[t + d:]
+
+    def _mark(self, name):
+        if self.profile:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._marks.append((name, ev))
+
+    stage_times_ms = FusedTrainer.stage_times_ms
+
+    def forward_backward(self, rays_o, rays_d, near, far, target, t_rand=None, u=None):
+        B, S, I = rays_o.shape[0], self.S, self.I
+        T = S + I
+        grid = self.model.grid
+        tab, dw, cw = self._views(self.half)
+        g_t, g_d, g_c = self._views(self.grads)
+        self._mark("begin")
+        self.loss_sum.zero_()
+        self.grads.zero_()
+        self._mark("zero")
+        if t_rand is None:
+            z_c = ops.stratified_sample_rng(near, far, self.sampler.t_vals, self.seed, self.step_dev)
+        else:
+            z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
+        pts_c = ops.points_on_rays(rays_o, rays_d, z_c, want_dirs=False)
+        self._mark("sample_coarse")
+        rgb_c, sig_c = ops.ngp_forward_f32(pts_c, rays_d, tab, grid, dw, cw, dirs_group=S)
+        self._mark("query_coarse")
+        _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg, self.dist_last)
+        self._mark("render_loss_coarse")
+        z_all = ops.sample_merge(z_c, w_c, u, n_new=I, rng=(self.seed, self.step_dev))
+        pts_f = ops.points_on_rays(rays_o, rays_d, z_all, want_dirs=False)
+        self._mark("sample_fine")
+        rgb_f, sig_f = ops.ngp_forward_f32(pts_f, rays_d, tab, grid, dw, cw, dirs_group=T)
+        self._mark("query_fine")
+        _, _, d_rgb_f, d_sig_f = ops.render_loss(rgb_f, sig_f, z_all, target, self.loss_sum[1:2], self.white_bg, self.dist_last,
+                                                 want_weights=False)
+        self._mark("render_loss_fine")
+        ops.ngp_backward(pts_f, rays_d, tab, grid, dw, cw, d_rgb_f, d_sig_f, g_t, g_d, g_c, dirs_group=T, loss_scale=self.loss_scale)
+        self._mark("backward_fine")
+        ops.ngp_backward(pts_c, rays_d, tab, grid, dw, cw, d_rgb_c, d_sig_c, g_t, g_d, g_c, dirs_group=S, loss_scale=self.loss_scale)
+        self._mark("backward_coarse")
+        self.aux = {"z": z_c, "z_all": z_all, "weights_coarse": w_c}
+        return self.loss_sum / (3.0 * B)
+
+    def optimizer_step(self):
+        if self.world > 1:
+            torch.distributed.all_reduce(self.grads, group=self.pg)       # ONE collective: table + both MLPs
+        ops.nonfinite_flag(self.grads, self.skip)
+        ops.adamw_step_shadow(self.flat, self.grads, self.m, self.v, self.lr_table, self.b1_table, self.step_dev, self.half,
+                              skip_flag=self.skip, weight_decay=self.wd, grad_scale=1.0 / self.world)
+        self.model._half = None          # the module's cached fp16 copies are stale: the next module call re-derives them
+        self._mark("adamw")
+
+    def step(self, rays_o, rays_d, near, far, target, **draws):
+        losses = self.forward_backward(rays_o, rays_d, near, far, target, **draws)
+        self.optimizer_step()
+        return losses
+
+    def optimizer_state_dict(self):
+        """torch.optim.AdamW layout over model.parameters() = [pos_encoding.params, dir_encoding.params (empty: no state, as
+        torch keeps none for a parameter that never had a gradient), dmlp.params, cmlp.params] (instantngp.py:23-64)."""
+        i = min(int(self.step_dev.item()), self.total_steps - 1)
+        step = float(self.step_dev.item())
+        state, off = {}, 0
+        for idx, c in zip((0, 2, 3), self.sizes):
+            state[idx] = {"step": torch.tensor(step), "exp_avg": self.m[off:off + c].clone(), "exp_avg_sq": self.v[off:off + c].clone()}
+            off += c
+        base_lr = float(self.lr_table[0])
+        group = {"lr": float(self.lr_table[i]), "betas": (float(self.b1_table[i]), 0.999), "eps": 1e-8, "weight_decay": self.wd,
+                 "amsgrad": False, "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": True, "initial_lr": base_lr, "max_lr": base_lr * 10.0, "min_lr": base_lr / 100.0,
+                 "base_momentum": 0.85, "max_momentum": 0.95, "params": [0, 1, 2, 3]}
+        return {"state": state, "param_groups": [group]}
+
+    def save_checkpoint(self, path, iteration):
+        sd = OrderedDict((k, v.detach().clone()) for k, v in self.model.state_dict().items())
+        torch.save({"iteration": iteration, "nerf_coarse_state_dict": sd, "nerf_fine_state_dict": sd,
+                    "optimizer_state_dict": self.optimizer_state_dict()}, path)
+
+
 def train_ngp(cfg_in):
     """scripts/train.py:189-370 with cfg.ngp true (:219-220): ONE InstantNGP serves as coarse and fine model; AdamW +
-    OneCycleLR as :244-259.  The step runs under autograd: sampling, resampling, compositing and the hash-grid encode /
-    scatter-add backward are this library's kernels, the two tiny MLPs are fp16 library GEMMs.  Like the reference, world
-    coordinates and view directions go to the encodings unnormalised.  tiny-cuda-nn parity is unpinned."""
+    OneCycleLR as :244-259.  The step is NGPTrainer's: only kernels of this library, one flat gradient all-reduce.
+    tiny-cuda-nn parity is unpinned."""
     global cfg
     cfg = cfg_in
     from .model import InstantNGP
-    from .sampling import StratifiedSampler
     dist_on = "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1
     rank, world = 0, 1
-    if dist_on:
-        torch.distributed.init_process_group("nccl")
-        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
+    if dist_on:
+        if not torch.distributed.is_initialized():
+            torch.distributed.init_process_group("nccl", device_id=dev)
+        rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     ckpt_dir = str(cfg.checkpoint_dir)
     os.makedirs(ckpt_dir, exist_ok=True)
+    writer = _open_writer(cfg, rank)
     store = RayStore(str(cfg.rays_file), dev, rank, world)
-    steps_per_epoch = len(store) // cfg.batch_size
-    torch.manual_seed(0)
+    steps_per_epoch = store.steps_per_epoch(cfg.batch_size)
+    torch.manual_seed(0)                                             # identical initial weights on every rank
     model = InstantNGP(getattr(cfg, "nerf_type", "large")).to(dev)
-    params = [p for p in model.parameters() if p.numel() > 0]
-    opt = torch.optim.AdamW(params, lr=cfg.lr, betas=(0.9, 0.999), weight_decay=1e-6, eps=1e-8)
-    sched = torch.optim.lr_scheduler.OneCycleLR(opt, max_lr=cfg.lr * 10, total_steps=max(cfg.num_epochs * steps_per_epoch, 1),
-                                                pct_start=0.1, anneal_strategy="cos", div_factor=10.0, final_div_factor=100.0)
-    sampler, criterion = StratifiedSampler(cfg.N_samples, dev), torch.nn.MSELoss()
-    scale = 128.0  # tcnn's default loss_scale for fp16 parameters (tinycudann/modules.py): keeps fp16 gradients normal
-
-    def save(path, epoch):
-        sd = model.state_dict()
-        torch.save({"iteration": epoch, "nerf_coarse_state_dict": sd, "nerf_fine_state_dict": sd,
-                    "optimizer_state_dict": opt.state_dict()}, path)
-
+    tr = NGPTrainer(model, cfg.N_samples, cfg.N_importance, cfg.lr, max(cfg.num_epochs * steps_per_epoch, 1), bool(cfg.white_bg))
+    perm_gen = torch.Generator(device=dev)
+    perm_gen.manual_seed(0)
     t0 = time.time()
     for epoch in range(1, cfg.num_epochs + 1):
-        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size)):
-            opt.zero_grad(set_to_none=True)
-            total, lc, lf = forward_pass(model, model, o, d, near, far, rgb, sampler, criterion, dev, bool(cfg.white_bg))
-            (total * scale).backward()
-            for p in params:
-                if p.grad is not None:
-                    p.grad.mul_(1.0 / scale)
-                    if dist_on:
-                        torch.distributed.all_reduce(p.grad)
-                        p.grad.mul_(1.0 / world)
-            opt.step()
-            sched.step()
-            if it % 100 == 0 and rank == 0:
-                print(f"epoch {epoch} it {it}/{steps_per_epoch} loss {total.item():.5f} (c {lc.item():.5f} f {lf.item():.5f}) "
-                      f"psnr {-10.0 * math.log10(max(lf.item(), 1e-12)):.2f} {time.time() - t0:.1f}s")
+        for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size, perm_gen)):
+            losses = tr.step(o, d, near, far, rgb)
+            if it % 100 == 0:
+                if world > 1:
+                    losses = losses.clone()
+                    torch.distributed.all_reduce(losses)
+                    losses /= world
+                if rank == 0:
+                    lc, lf = losses.tolist()
+                    print(f"| Epoch: {epoch} | Iteration: {it} | Loss: {lc + lf:.4f} (Coarse: {lc:.4f}, Fine: {lf:.4f}) | "
+                          f"PSNR: {-10.0 * math.log10(max(lf, 1e-12)):.2f} | Time: {time.time() - t0:.2f}s |")
+                    done = min(int(tr.step_dev.item()), tr.total_steps - 1)
+                    _log_scalars(writer, epoch * steps_per_epoch + it, lc, lf, float(tr.lr_table[done]))
         if epoch % 2 == 0 and rank == 0:
-            save(os.path.join(ckpt_dir, f"nerf_epoch_{epoch:06d}.pth"), epoch)
+            tr.save_checkpoint(os.path.join(ckpt_dir, f"nerf_epoch_{epoch:06d}.pth"), epoch)
     if rank == 0:
-        save(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
+        tr.save_checkpoint(os.path.join(ckpt_dir, "nerf_final.pth"), cfg.num_epochs)
         print(f"Training completed in {time.time() - t0:.2f}s")
-    return model
+    if writer is not None:
+        writer.close()
+    return tr
 
 
 def main(argv=None):

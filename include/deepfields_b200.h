@@ -210,6 +210,13 @@ int dfn_compact_indices(const unsigned char* flags, const int* idx_in, long long
 int dfn_adamw_step(float* p, const float* g, float* m, float* v, long long n, const float* lr_table,
                    const float* beta1_table, int* step_ptr, int table_len, float beta2, float eps, float weight_decay,
                    float grad_scale, void* stream);
+/* the same update that also refreshes an fp16 copy of the parameters (the operands of the Instant-NGP kernels) and is skipped,
+ * step counter included, when *skip_flag != 0 (nullable); dfn_nonfinite_flag sets flag[0] = 1 iff a gradient is inf / NaN -
+ * the guard torch.amp.GradScaler.step applies in scripts/train.py:262-323 */
+int dfn_adamw_step_shadow(float* p, const float* g, float* m, float* v, long long n, const float* lr_table,
+                          const float* beta1_table, int* step_ptr, int table_len, float beta2, float eps, float weight_decay,
+                          float grad_scale, void* shadow_f16, const int* skip_flag, void* stream);
+int dfn_nonfinite_flag(const float* g, long long n, int* flag, void* stream);
 
 /* ---- Instant-NGP variant (scripts/instantngp.py:7-104; arithmetic of tiny-cuda-nn 74ea173d restated, parity unpinned) ---- */
 #define DFN_NGP_LEVELS 16
@@ -240,6 +247,17 @@ int dfn_sh4_encode(const float* dirs, long long P, void* out_f16, void* stream);
 int dfn_ngp_forward(const float* pos, const float* dirs, int dirs_stride, long long P, const void* table_f16,
                     const dfn_hashgrid* g, const void* dmlp_w_f16, const void* cmlp_w_f16, void* features_f16, void* rgb_f16,
                     void* stream);
+/* the same query with fp32 outputs for the compositing kernels of the train step: rgb [P,3], sigma [P] (= feature 0) hold the
+ * fp16 values.  dirs_group: that many consecutive points share one direction (the samples of a ray; 1 = per point). */
+int dfn_ngp_forward_f32(const float* pos, const float* dirs, int dirs_stride, int dirs_group, long long P, const void* table_f16,
+                        const dfn_hashgrid* g, const void* dmlp_w_f16, const void* cmlp_w_f16, float* rgb, float* sigma, void* stream);
+/* training backward of InstantNGP.forward in ONE launch (csrc/ngp_train.cu): the forward is recomputed in registers (nothing is
+ * stashed), d loss / d rgb [P,3] and d loss / d sigma [P] (fp32) are pushed through both tiny MLPs with mma.sync and scattered
+ * into the fp32 gradients of the hash table [n_entries,2], the density MLP [3072] and the colour MLP [7168] (all ACCUMULATED).
+ * loss_scale (tcnn's default 128) keeps the fp16 gradient fragments in range; the results are unscaled. */
+int dfn_ngp_backward(const float* pos, const float* dirs, int dirs_stride, int dirs_group, long long P, const void* table_f16,
+                     const dfn_hashgrid* g, const void* dmlp_w_f16, const void* cmlp_w_f16, const float* d_rgb, const float* d_sigma,
+                     float loss_scale, float* d_table, float* d_dmlp, float* d_cmlp, void* stream);
 
 #ifdef __cplusplus
 }
