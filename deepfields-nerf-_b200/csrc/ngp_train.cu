@@ -5,8 +5,12 @@
 //   d rgb -> sigmoid' -> colour MLP (64 <- 64 <- 32) -> features (+ d sigma on feature 0) -> density MLP (64 <- 32) -> encoding
 // Data gradients  dA = dZ W    : mma.m16n8k16 against TRANSPOSED weight images in shared memory, ReLU masks taken from the
 //                                recomputed activations in the same register layout;
-// weight gradients dW = dZ^T A : mma.m16n8k16 with both operands transposed in registers (movmatrix.m8n8.trans), reduction over
-//                                the tile's 16 points, accumulated per CTA in shared memory (fp32, red.shared) and flushed once;
+// weight gradients dW = dZ^T A : every warp parks its tile's activations and pre-activation gradients (fp16) in shared memory;
+//                                after a CTA barrier warp w owns 10 of the 80 (16 out x 8 in) output tiles and reduces them
+//                                over ALL 128 points of the round with mma.m16n8k16 (operands through ldmatrix.trans),
+//                                accumulating in REGISTERS across rounds; one global flush at the end.  (A first version
+//                                reduced per 16-point tile into shared memory with red.shared.f32: 640 shared atomics per
+//                                point, 2 cycles per lane - ten times the cost of everything else in the kernel.)
 // table gradient               : the d-encoding accumulators ARE laid out as (point, level) pairs - the same pairs the lane
 //                                encoded - so the trilinear scatter-add (x-pair vector reductions, as hashgrid_backward_kernel)
 //                                runs straight from registers, in fp32.
@@ -39,32 +43,41 @@ __device__ __forceinline__ void mask_repack(const float (&c)[2 * KB][4], const u
     }
   }
 }
-// dW[16 ob + .., 8 nj + ..] += dZ^T (16 outs x 16 points) * A (16 points x 8 ins) for every (ob, nj); operands arrive transposed
-// (TD: out blocks, TX: in blocks); dWs: shared-memory accumulator [OUT][IN + 8] fp32
-template <int KBO, int KBI>
-__device__ __forceinline__ void wgrad_tile(const uint32_t (&TD)[KBO][4], const uint32_t (&TX)[KBI][4], float* dWs, int g, int t) {
-  constexpr int LD = 16 * KBI + 8;
-#pragma unroll
-  for (int ob = 0; ob < KBO; ++ob) {
-    const uint32_t a[4] = {TD[ob][0], TD[ob][2], TD[ob][1], TD[ob][3]};   // rows = outs, cols = points
-#pragma unroll
-    for (int nj = 0; nj < 2 * KBI; ++nj) {
-      float c[4] = {0.f, 0.f, 0.f, 0.f};
-      mma16816(c, a, TX[nj >> 1][2 * (nj & 1)], TX[nj >> 1][2 * (nj & 1) + 1]);
-      float* d = dWs + (16 * ob + g) * LD + 8 * nj + 2 * t;
-      atomicAdd(d, c[0]);
-      atomicAdd(d + 1, c[1]);
-      atomicAdd(d + 8 * LD, c[2]);
-      atomicAdd(d + 8 * LD + 1, c[3]);
-    }
-  }
-}
-template <int KB>
-__device__ __forceinline__ void trans_frag(const uint32_t (&x)[KB][4], uint32_t (&tx)[KB][4]) {
+// ---- staging of a warp's fragments for the CTA-wide weight-gradient reduction ----
+// one A-layout fragment set (KB k-blocks of 16 columns, 16 rows) -> shared memory [128 points][LD halves], rows 16 w + ..
+template <int KB, int LD>
+__device__ __forceinline__ void park(const uint32_t (&x)[KB][4], __half* dst, int row0, int g, int t) {
 #pragma unroll
   for (int kb = 0; kb < KB; ++kb)
 #pragma unroll
-    for (int r = 0; r < 4; ++r) tx[kb][r] = trans8x8(x[kb][r]);
+    for (int r = 0; r < 4; ++r)
+      *reinterpret_cast<uint32_t*>(dst + (row0 + g + 8 * (r & 1)) * LD + 16 * kb + 8 * (r >> 1) + 2 * t) = x[kb][r];
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], const __half* p) {
+  const uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2_trans(uint32_t (&r)[2], const __half* p) {
+  const uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+}
+// A' = dZ^T block (16 outs from column out0, 16 points from row pt0) of Ds [points][LD]: matrices (pts 0-7, outs 0-7),
+// (pts 0-7, outs 8-15), (pts 8-15, outs 0-7), (pts 8-15, outs 8-15), each transposed on load = the A fragment registers
+template <int LD>
+__device__ __forceinline__ void load_at(uint32_t (&a)[4], const __half* Ds, int pt0, int out0, int lane) {
+  const int mi = lane >> 3, r = lane & 7;
+  ldsm_x4_trans(a, Ds + (pt0 + r + 8 * (mi >> 1)) * LD + out0 + 8 * (mi & 1));
+}
+// B for two 8-wide input tiles (columns in0 .. in0 + 15) of Xs [points][LD]: {b0, b1} of tile 0, {b0, b1} of tile 1
+template <int LD>
+__device__ __forceinline__ void load_b2(uint32_t (&b)[4], const __half* Xs, int pt0, int in0, int lane) {
+  const int mi = lane >> 3, r = lane & 7;
+  ldsm_x4_trans(b, Xs + (pt0 + r + 8 * (mi & 1)) * LD + in0 + 8 * (mi >> 1));
+}
+template <int LD>
+__device__ __forceinline__ void load_b1(uint32_t (&b)[2], const __half* Xs, int pt0, int in0, int lane) {
+  const int mi = (lane >> 3) & 1, r = lane & 7;
+  ldsm_x2_trans(b, Xs + (pt0 + r + 8 * mi) * LD + in0);
 }
 
 // transposed weight images (halves): image of a [OUT][IN] layer = [IN rows][OUT + 8]; only the first 16 input columns of the
@@ -75,9 +88,20 @@ constexpr int kTC0 = kTD1 + 64 * 24;         // Wc0[:, :16]^T [16][72]
 constexpr int kTC1 = kTC0 + 16 * 72;         // Wc1^T [64][72]
 constexpr int kTC2 = kTC1 + 64 * 72;         // Wc2^T [64][24]
 constexpr int kTHalves = kTC2 + 64 * 24;
-// fp32 weight-gradient accumulators [OUT][IN + 8]
-constexpr int kGD0 = 0, kGD1 = kGD0 + 64 * 40, kGC0 = kGD1 + 16 * 72, kGC1 = kGC0 + 64 * 40, kGC2 = kGC1 + 64 * 72,
-              kGFloats = kGC2 + 16 * 72;
+// staging of one round (8 warps x 16 points) for the weight gradients: activations X and pre-activation gradients D, fp16,
+// [128 points][columns + 8] (row strides of 48 / 80 / 144 bytes: ldmatrix reads 8 rows without bank conflicts)
+constexpr int kPts = 128;
+constexpr int kSEnc = 0;                        // enc  [128][40]
+constexpr int kSHd1 = kSEnc + kPts * 40;        // hd1  [128][72]
+constexpr int kSCin = kSHd1 + kPts * 72;        // cin  [128][40]  (features | SH)
+constexpr int kSHc1 = kSCin + kPts * 40;        // hc1  [128][72]
+constexpr int kSHc2 = kSHc1 + kPts * 72;        // hc2  [128][72]
+constexpr int kSDzd = kSHc2 + kPts * 72;        // d pre hd1 [128][72]
+constexpr int kSDfe = kSDzd + kPts * 72;        // d pre feat [128][24]
+constexpr int kSDz1 = kSDfe + kPts * 24;        // d pre hc1 [128][72]
+constexpr int kSDz2 = kSDz1 + kPts * 72;        // d pre hc2 [128][72]
+constexpr int kSDx3 = kSDz2 + kPts * 72;        // d x3 [128][24]
+constexpr int kSHalves = kSDx3 + kPts * 24;
 
 __device__ __forceinline__ void stage_transposed(__half* dst, const __half* __restrict__ src, int out, int in_total, int in_used) {
   const int ld = out + 8;
@@ -107,8 +131,8 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __half* W = reinterpret_cast<__half*>(smem_raw);
   __half* WT = W + kWHalves;
-  float* dWs = reinterpret_cast<float*>(smem_raw + (kWHalves + kTHalves) * 2);
-  LevelDev* lv = reinterpret_cast<LevelDev*>(dWs + kGFloats);
+  __half* ST = WT + kTHalves;
+  LevelDev* lv = reinterpret_cast<LevelDev*>(ST + kSHalves);
 
   stage_weights(W + kOffD0, a.dmlp_w, 64, 32);
   stage_weights(W + kOffD1, a.dmlp_w + 64 * 32, 16, 64);
@@ -120,20 +144,32 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
   stage_transposed(WT + kTC0, a.cmlp_w, 64, 32, 16);
   stage_transposed(WT + kTC1, a.cmlp_w + 64 * 32, 64, 64, 64);
   stage_transposed(WT + kTC2, a.cmlp_w + 64 * 32 + 64 * 64, 16, 64, 64);
-  for (int i = threadIdx.x; i < kGFloats; i += blockDim.x) dWs[i] = 0.f;
   if (threadIdx.x < kLevels) lv[threadIdx.x] = grid.lv[threadIdx.x];
   __syncthreads();
 
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const long long P = a.P;
-  const long long n_tiles = (P + 15) / 16;                       // 16-point tiles: one per warp iteration
-  const long long warp_global = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+  const long long n_tiles = (P + 15) / 16;                       // 16-point tiles: one per warp and round
+  const int warp = threadIdx.x >> 5;
+  const long long n_rounds = (n_tiles + 8ll * gridDim.x - 1) / (8ll * gridDim.x);
   const float inv_scale = 1.0f / a.loss_scale;
   float2* d_table = reinterpret_cast<float2*>(a.d_table);
+  // this warp's share of the weight gradients: Wc1 (ob = w/2, 4 input tiles), Wd0 and Wc0 (ob = w/2, 2 input tiles each),
+  // Wd1 and Wc2 (input tile w)
+  float acc_c1[4][4], acc_d0[2][4], acc_c0[2][4], acc_d1[4], acc_c2[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    acc_d1[i] = acc_c2[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc_c1[j][i] = 0.f;
+    acc_d0[0][i] = acc_d0[1][i] = acc_c0[0][i] = acc_c0[1][i] = 0.f;
+  }
 
-  for (long long tile = warp_global; tile < n_tiles; tile += warp_stride) {
-    const long long p0 = tile * 16;
+  for (long long round = 0; round < n_rounds; ++round) {
+    const long long tile = (round * gridDim.x + blockIdx.x) * 8 + warp;
+    // (a warp without a tile in the last round runs on clamped points with zero output gradients: it parks zeros)
+    const long long p0 = (tile < n_tiles ? tile : n_tiles - 1) * 16;
+    const bool live = tile < n_tiles;
     // ---- re-encode the 16 points into A fragments (as ngp_forward_kernel) ----
     uint32_t enc[2][4];
     float px[2], py[2], pz[2];
@@ -196,7 +232,7 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
     float dsig[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      const bool valid = pr[h] < P;
+      const bool valid = live && pr[h] < P;
       dsig[h] = valid ? a.loss_scale * __ldg(a.d_sigma + pr[h]) : 0.f;
       float g0 = 0.f, g1 = 0.f;
       if (valid && t < 2) {
@@ -215,29 +251,17 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
       layer<16, 8>(dx3, WT + kTC2, g, t, acc);          // d hc2 = d x3 * Wc2
       mask_repack<4>(acc, hc2, dz2);
     }
-    {
-      uint32_t TD[1][4], TX[4][4];
-      trans_frag<1>(dx3, TD);
-      trans_frag<4>(hc2, TX);
-      wgrad_tile<1, 4>(TD, TX, dWs + kGC2, g, t);        // d Wc2 += d x3^T hc2
-    }
+    park<1, 24>(dx3, ST + kSDx3, 16 * warp, g, t);
+    park<4, 72>(hc2, ST + kSHc2, 16 * warp, g, t);
     {
       float acc[8][4];
       layer<64, 8>(dz2, WT + kTC1, g, t, acc);           // d hc1 = d z2 * Wc1
       mask_repack<4>(acc, hc1, dz1);
     }
-    {
-      uint32_t TD[4][4], TX[4][4];
-      trans_frag<4>(dz2, TD);
-      trans_frag<4>(hc1, TX);
-      wgrad_tile<4, 4>(TD, TX, dWs + kGC1, g, t);        // d Wc1 += d z2^T hc1
-    }
-    {
-      uint32_t TD[4][4], TX[2][4];
-      trans_frag<4>(dz1, TD);
-      trans_frag<2>(cin, TX);
-      wgrad_tile<4, 2>(TD, TX, dWs + kGC0, g, t);        // d Wc0 += d z1^T [features | SH]
-    }
+    park<4, 72>(dz2, ST + kSDz2, 16 * warp, g, t);
+    park<4, 72>(hc1, ST + kSHc1, 16 * warp, g, t);
+    park<4, 72>(dz1, ST + kSDz1, 16 * warp, g, t);
+    park<2, 40>(cin, ST + kSCin, 16 * warp, g, t);
     {
       float acc[2][4];
       layer<64, 2>(dz1, WT + kTC0, g, t, acc);           // d features = d z1 * Wc0[:, :16]
@@ -251,25 +275,17 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
       layer<16, 8>(dfe, WT + kTD1, g, t, acc);           // d hd1 = d feat * Wd1
       mask_repack<4>(acc, hd1, dzd);
     }
-    {
-      uint32_t TD[1][4], TX[4][4];
-      trans_frag<1>(dfe, TD);
-      trans_frag<4>(hd1, TX);
-      wgrad_tile<1, 4>(TD, TX, dWs + kGD1, g, t);        // d Wd1 += d feat^T hd1
-    }
-    {
-      uint32_t TD[4][4], TX[2][4];
-      trans_frag<4>(dzd, TD);
-      trans_frag<2>(enc, TX);
-      wgrad_tile<4, 2>(TD, TX, dWs + kGD0, g, t);        // d Wd0 += d zd^T enc
-    }
+    park<1, 24>(dfe, ST + kSDfe, 16 * warp, g, t);
+    park<4, 72>(hd1, ST + kSHd1, 16 * warp, g, t);
+    park<4, 72>(dzd, ST + kSDzd, 16 * warp, g, t);
+    park<2, 40>(enc, ST + kSEnc, 16 * warp, g, t);
     float denc[4][4];
     layer<64, 4>(dzd, WT + kTD0, g, t, denc);            // d enc = d zd * Wd0: (row g / g+8, level 4j + t, features 0 / 1)
 
     // ---- trilinear scatter-add into the table gradient, straight from the accumulators ----
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      if (pr[h] >= P) continue;
+      if (!live || pr[h] >= P) continue;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float d0 = denc[j][2 * h] * inv_scale, d1 = denc[j][2 * h + 1] * inv_scale;
@@ -293,22 +309,61 @@ __global__ void __launch_bounds__(kThreads, 1) ngp_backward_kernel(const NgpBwdA
         }
       }
     }
+
+    // ---- weight gradients of the round: dW += D^T X over the 128 parked points, this warp's 10 output tiles ----
+    __syncthreads();
+    {
+      const int ob = warp >> 1, hw = warp & 1;
+#pragma unroll 2
+      for (int ks = 0; ks < 8; ++ks) {
+        const int pt0 = 16 * ks;
+        uint32_t at[4], b4[4], b2[2];
+        load_at<72>(at, ST + kSDz2, pt0, 16 * ob, lane);                      // d Wc1 [64 x 64]
+#pragma unroll
+        for (int pr2 = 0; pr2 < 2; ++pr2) {
+          load_b2<72>(b4, ST + kSHc1, pt0, 32 * hw + 16 * pr2, lane);
+          mma16816(acc_c1[2 * pr2], at, b4[0], b4[1]);
+          mma16816(acc_c1[2 * pr2 + 1], at, b4[2], b4[3]);
+        }
+        load_at<72>(at, ST + kSDzd, pt0, 16 * ob, lane);                      // d Wd0 [64 x 32]
+        load_b2<40>(b4, ST + kSEnc, pt0, 16 * hw, lane);
+        mma16816(acc_d0[0], at, b4[0], b4[1]);
+        mma16816(acc_d0[1], at, b4[2], b4[3]);
+        load_at<72>(at, ST + kSDz1, pt0, 16 * ob, lane);                      // d Wc0 [64 x 32]
+        load_b2<40>(b4, ST + kSCin, pt0, 16 * hw, lane);
+        mma16816(acc_c0[0], at, b4[0], b4[1]);
+        mma16816(acc_c0[1], at, b4[2], b4[3]);
+        load_at<24>(at, ST + kSDfe, pt0, 0, lane);                            // d Wd1 [16 x 64]
+        load_b1<72>(b2, ST + kSHd1, pt0, 8 * warp, lane);
+        mma16816(acc_d1, at, b2[0], b2[1]);
+        load_at<24>(at, ST + kSDx3, pt0, 0, lane);                            // d Wc2 [16 x 64]
+        load_b1<72>(b2, ST + kSHc2, pt0, 8 * warp, lane);
+        mma16816(acc_c2, at, b2[0], b2[1]);
+      }
+    }
+    __syncthreads();   // the staging arrays are rewritten by the next round
   }
 
-  // ---- flush the CTA's weight gradients (unscaled) ----
-  __syncthreads();
-  auto flush = [&](const float* src, float* dst, int out, int in) {
-    const int ld = in + 8;
-    for (int i = threadIdx.x; i < out * in; i += blockDim.x) {
-      const float v = src[(i / in) * ld + (i % in)] * inv_scale;
-      if (v != 0.f) atomicAdd(dst + i, v);
+  // ---- flush this warp's weight-gradient tiles (unscaled): c[0], c[1] = (out g, ins 2t, 2t+1), c[2], c[3] = out g + 8 ----
+  {
+    const int ob = warp >> 1, hw = warp & 1;
+    auto put = [&](float* W0, int in_dim, int out0, int in0, const float (&c)[4]) {
+      float* d = W0 + (out0 + g) * in_dim + in0 + 2 * t;
+      if (c[0] != 0.f) atomicAdd(d, c[0] * inv_scale);
+      if (c[1] != 0.f) atomicAdd(d + 1, c[1] * inv_scale);
+      if (c[2] != 0.f) atomicAdd(d + 8 * in_dim, c[2] * inv_scale);
+      if (c[3] != 0.f) atomicAdd(d + 8 * in_dim + 1, c[3] * inv_scale);
+    };
+#pragma unroll
+    for (int j = 0; j < 4; ++j) put(a.d_cmlp + 64 * 32, 64, 16 * ob, 32 * hw + 8 * j, acc_c1[j]);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      put(a.d_dmlp, 32, 16 * ob, 16 * hw + 8 * j, acc_d0[j]);
+      put(a.d_cmlp, 32, 16 * ob, 16 * hw + 8 * j, acc_c0[j]);
     }
-  };
-  flush(dWs + kGD0, a.d_dmlp, 64, 32);
-  flush(dWs + kGD1, a.d_dmlp + 64 * 32, 16, 64);
-  flush(dWs + kGC0, a.d_cmlp, 64, 32);
-  flush(dWs + kGC1, a.d_cmlp + 64 * 32, 64, 64);
-  flush(dWs + kGC2, a.d_cmlp + 64 * 32 + 64 * 64, 16, 64);
+    put(a.d_dmlp + 64 * 32, 64, 0, 8 * warp, acc_d1);
+    put(a.d_cmlp + 64 * 32 + 64 * 64, 64, 0, 8 * warp, acc_c2);
+  }
 }
 
 }  // namespace
@@ -330,7 +385,7 @@ extern "C" int dfn_ngp_backward(const float* pos, const float* dirs, int dirs_st
   a.pos = pos; a.dirs = dirs; a.dirs_stride = dirs_stride; a.dirs_group = dirs_group < 1 ? 1 : dirs_group; a.P = P; a.table = (const __half2*)table_f16;
   a.dmlp_w = (const __half*)dmlp_w_f16; a.cmlp_w = (const __half*)cmlp_w_f16; a.d_rgb = d_rgb; a.d_sigma = d_sigma;
   a.loss_scale = loss_scale; a.d_table = d_table; a.d_dmlp = d_dmlp; a.d_cmlp = d_cmlp;
-  const size_t smem = (kWHalves + kTHalves) * 2 + kGFloats * 4 + kLevels * sizeof(LevelDev);
+  const size_t smem = (kWHalves + kTHalves + kSHalves) * 2 + kLevels * sizeof(LevelDev);
   DFN_CUDA(cudaFuncSetAttribute(ngp_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "dfn_ngp_backward");
   const long long tiles = (P + 15) / 16;
   long long blocks = (tiles + kThreads / 32 - 1) / (kThreads / 32);
