@@ -16,6 +16,7 @@ from .precompute_rays import get_rays, ray_cube_intersection, ray_cube_intersect
 from .post_process_vol import volume_points, slice_aabb  # noqa: F401
 from .render import render_rays, render_image, row_range, gather_rows  # noqa: F401
 from .config import load_config  # noqa: F401
+from . import torch_ops  # noqa: F401  (registers torch.ops.dfn.*)
 
 __all__ = [
     "StratifiedSampler", "OptimizedPositionalEncoding", "OptimizedVanillaNeRF", "get_nerf_models", "InstantNGP", "sample_pdf",

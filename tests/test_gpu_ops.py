@@ -261,7 +261,7 @@ def test_mlp_forward_golden(D, golden):
     # training-mode noise and the peaked-sigma weight set
     noise = make_noise(16, 512)
     rgb, sig = D.ops.mlp_forward(_packed(D, sd), pos=pos, view=view, noise=noise.cuda())
-    np.testing.assert_allclose(sig.cpu().numpy(), golden["mlp_fp32_train_sigma"][:, 0], atol=3e-2, rtol=2e-2)
+    np.testing.assert_allclose(sig.cpu().numpy(), golden["mlp_fp32_train_sigma"][:, 0], atol=2e-2, rtol=2e-2)
     rgb, sig = D.ops.mlp_forward(_packed(D, peaked(sd)), pos=pos, view=view)
     np.testing.assert_allclose(sig.cpu().numpy(), golden["mlp_peaked_sigma"][:, 0], atol=0.3, rtol=2e-2)
 
@@ -315,7 +315,7 @@ def test_mlp_forward_sources_and_module(D, golden):
         sg, feat = m.query_density(pts.cuda())
     assert rgb.shape == (B * S, 3) and sig.shape == (B * S, 1) and feat.shape == (B * S, 256)
     assert torch.equal(rgb, a[0]) and torch.equal(sig[:, 0], a[1]) and torch.equal(sg, sig)
-    np.testing.assert_allclose(feat.float().cpu().numpy()[:512], O_feat(sd, pts[:512]), atol=3e-2, rtol=2e-2)
+    np.testing.assert_allclose(feat.float().cpu().numpy()[:512], O_feat(sd, pts[:512]), atol=2e-2, rtol=2e-2)
 
 
 def O_feat(sd, pos):
