@@ -39,6 +39,7 @@ class HashGrid(C.Structure):
 SIGNATURES = {
     "dfn_last_error": (C.c_char_p, []),
     "dfn_abi_version": (_i, []),
+    "dfn_set_sm_limit": (_i, [_i]),
     "dfn_stratified_sample": (_i, [_p, _p, _p, _p, _i, _i, _p, _p]),
     "dfn_points_on_rays": (_i, [_p, _p, _p, _i, _i, _p, _p, _p]),
     "dfn_sample_pdf": (_i, [_p, _i, _p, _ll, _i, _p, _i, _i, _i, _p, _p, _p, _p]),

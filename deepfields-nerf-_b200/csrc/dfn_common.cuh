@@ -51,6 +51,9 @@ static inline int dfn_num_sms() {
   return cache[slot];
 }
 
+// SM count the MLP launchers size their grids to: the device's, or the calling thread's budget (dfn_set_sm_limit, dfn_error.cu)
+int dfn_mlp_sms();
+
 // ---- device helpers ---------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

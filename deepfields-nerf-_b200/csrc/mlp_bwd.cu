@@ -427,7 +427,7 @@ extern "C" int dfn_mlp_backward_dgrad(long long P, const void* bwd_pack, const f
   WeightMaps maps;
   a.replicas = weight_replicas();
   if (int rc = make_weight_maps(bwd_pack, static_cast<unsigned long long>(kBwdPackBytes) * a.replicas, &maps)) return rc;
-  int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  int pairs = a.n_tiles / 2 < dfn_mlp_sms() / 2 ? a.n_tiles / 2 : dfn_mlp_sms() / 2;
   static const int pairs_env = [] { const char* e = getenv("DFN_DGRAD_PAIRS"); return e ? atoi(e) : 0; }();   // bring-up: per-pair speed on fewer SMs
   if (pairs_env > 0 && pairs_env < pairs) pairs = pairs_env;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

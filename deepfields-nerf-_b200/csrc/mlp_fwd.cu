@@ -595,7 +595,7 @@ static int mlp_forward_impl(const dfn_point_source* src, long long P, const void
   a.replicas = weight_replicas();
   if (int rc = make_weight_maps(fwd_pack, static_cast<unsigned long long>(kFwdPackBytes) * a.replicas, &maps)) return rc;
   // one CTA per SM, paired: grid = 2 * min(#SM / 2, #super-tiles)
-  const int pairs = a.n_tiles / 2 < dfn_num_sms() / 2 ? a.n_tiles / 2 : dfn_num_sms() / 2;
+  const int pairs = a.n_tiles / 2 < dfn_mlp_sms() / 2 ? a.n_tiles / 2 : dfn_mlp_sms() / 2;
   const int grid = 2 * pairs;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (stash) {

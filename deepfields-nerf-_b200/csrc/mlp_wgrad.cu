@@ -408,7 +408,7 @@ int dfn_launch_wgrad(const dfn_point_source* src, long long P, int n_tiles, cons
                      float* grads, cudaStream_t st) {
   WgradArgs a{};
   a.src = *src; a.P = P; a.n_tiles = n_tiles; a.stash = stash; a.dz = dz; a.grads = grads;
-  const int sms = dfn_num_sms();
+  const int sms = dfn_mlp_sms();
   // 8 big jobs + PE + colour share the SMs in proportion to their (HBM-bound, roughly equal) per-tile cost
   int per = sms / 10;
   if (per < 1) per = 1;

@@ -49,6 +49,19 @@ def stratified_sample(near: Tensor, far: Tensor, t_vals: Tensor, t_rand: Tensor)
     return z
 
 
+class sm_limit:
+    """`with ops.sm_limit(n):` the MLP launches inside size their persistent grids to n SMs (dfn_set_sm_limit)."""
+
+    def __init__(self, n_sms: int):
+        self.n = int(n_sms)
+
+    def __enter__(self):
+        _lib.load().dfn_set_sm_limit(self.n)
+
+    def __exit__(self, *exc):
+        _lib.load().dfn_set_sm_limit(0)
+
+
 RNG_JITTER, RNG_PDF, RNG_NOISE_COARSE, RNG_NOISE_FINE = 1, 2, 3, 4   # stream ids of csrc/rng.cuh
 
 

@@ -121,6 +121,13 @@ class FusedTrainer:
         self.seed = int(seed) if seed is not None else 0x5EED + 7919 * rank
         self.use_graph = (os.environ.get("DFN_CUDA_GRAPH", "0") == "1") if use_graph is None else bool(use_graph)
         self._graphs = {}
+        # overlap = (SMs of the fine forward, SMs of the coarse backward): the coarse network's backward only depends on the
+        # coarse loss, so it runs on a side stream BESIDE the fine network's forward, each on its share of the SMs
+        # (DFN_OVERLAP="100,48"; unset / "0" = everything in sequence on the whole device)
+        ov = os.environ.get("DFN_OVERLAP", "0")
+        self.overlap = tuple(int(x) for x in ov.split(",")) if "," in ov else None
+        self._side = torch.cuda.Stream(device=dev) if self.overlap else None
+        self._keep = None
         self.models = (model_coarse, model_fine)
         n = ops.MLP_NUM_PARAMS
         # re-home both models into one flat buffer
@@ -185,6 +192,7 @@ class FusedTrainer:
         u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=dev)  # noqa: E731
         self.stash_c, self.stash_f = u8(ops.mlp_stash_bytes(Pc)), u8(ops.mlp_stash_bytes(Pf))
         self.dz = u8(max(ops.mlp_dz_bytes(Pc), ops.mlp_dz_bytes(Pf)))
+        self.dz_c = u8(ops.mlp_dz_bytes(Pc)) if self.overlap else self.dz   # its own scratch when the two backward passes overlap
         self.out_c = (torch.empty(Pc, 3, device=dev), torch.empty(Pc, device=dev))
         self.out_f = (torch.empty(Pf, 3, device=dev), torch.empty(Pf, device=dev))
         self._B = B
@@ -229,26 +237,40 @@ class FusedTrainer:
         _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg,
                                                    self.dist_last)
         self._mark("render_loss_coarse")
+        mk_c = lambda nm: self._mark(nm + "_coarse")  # noqa: E731
+        mk_f = lambda nm: self._mark(nm + "_fine")  # noqa: E731
+        done_c = None
+        if self.overlap:
+            # the coarse network's backward starts NOW on the side stream, on its share of the SMs
+            main = torch.cuda.current_stream()
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side), ops.sm_limit(self.overlap[1]):
+                self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, lambda nm: None, self.dz_c)
+                done_c = torch.cuda.Event()
+                done_c.record(self._side)
+            self._keep = (rgb_c, sig_c, d_rgb_c, d_sig_c, z_c)    # read by the side stream: alive until the optimiser has waited
         # inverse-CDF resampling + sort in one launch; z_new never reaches HBM
         z_all = ops.sample_merge(z_c, w_c, u, n_new=I, rng=(self.seed, self.step_dev))
         self._mark("sample_merge")
         rays_f = (rays_o, rays_d, z_all)
-        rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f, noise_rng=rng_f)
+        with ops.sm_limit(self.overlap[0] if self.overlap else 0):
+            rgb_f, sig_f = ops.mlp_forward(mf._packed, rays=rays_f, noise=noise_f, stash=self.stash_f, out=self.out_f, noise_rng=rng_f)
         self._mark("mlp_fwd_fine")
         _, _, d_rgb_f, d_sig_f = ops.render_loss(rgb_f, sig_f, z_all, target, self.loss_sum[1:2], self.white_bg,
                                                  self.dist_last, want_weights=False)
         self._mark("render_loss_fine")
-        mk_c = lambda nm: self._mark(nm + "_coarse")  # noqa: E731
-        mk_f = lambda nm: self._mark(nm + "_fine")  # noqa: E731
         # fine network first: its half of the flat gradient is all-reduced while the coarse network's backward runs
-        self._bwd(mf, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.grads[n:], rays_f, mk_f)
+        self._bwd(mf, rgb_f, sig_f, d_rgb_f, d_sig_f, self.stash_f, self.grads[n:], rays_f, mk_f, self.dz)
         self._reduce_async(self.grads[n:])
-        self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, mk_c)
+        if done_c is not None:
+            torch.cuda.current_stream().wait_event(done_c)
+        else:
+            self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, mk_c, self.dz_c)
         self._reduce_async(self.grads[:n])
         self.aux = {"z": z_c, "z_all": z_all, "weights_coarse": w_c}
         return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
 
-    def _bwd(self, model, rgb, sig, d_rgb, d_sig, stash, grads, rays, mark):
+    def _bwd(self, model, rgb, sig, d_rgb, d_sig, stash, grads, rays, mark, dz):
         if ops.bwd_fused_default():
             P = rgb.shape[0]
             if getattr(self, "_ws", None) is None or self._ws.numel() < ops.mlp_bwd_fused_ws_bytes(P):
@@ -256,7 +278,7 @@ class FusedTrainer:
             ops.mlp_backward_fused(model._packed, rgb, sig, d_rgb, d_sig, stash, self._ws, grads, rays=rays)
             mark("bwd_fused")
         else:
-            ops.mlp_backward(model._packed, rgb, sig, d_rgb, d_sig, stash, self.dz, grads, rays=rays, mark=mark)
+            ops.mlp_backward(model._packed, rgb, sig, d_rgb, d_sig, stash, dz, grads, rays=rays, mark=mark)
 
     def _reduce_async(self, g):
         """Data-parallel exchange of one network's gradient, started as soon as it is complete (NCCL runs on the process

@@ -20,6 +20,9 @@ extern "C" {
 
 const char* dfn_last_error(void);
 int dfn_abi_version(void);
+/* SM budget of the MLP launches (dfn_mlp_forward*, dfn_mlp_backward*) of the CALLING THREAD: their persistent grids are sized to
+ * n_sms instead of the whole device (0 = whole device), so that two of them can be resident at once on two streams. */
+int dfn_set_sm_limit(int n_sms);
 
 /* ---- sampling ---------------------------------------------------------------------------------- */
 /* StratifiedSampler.__call__  scripts/sampling.py:10-21.  near/far [B], t_vals [S] (the sampler's linspace),
