@@ -65,6 +65,54 @@ def peaks():
     return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback (B200_PROFILING.md)"}
 
 
+class AuxDeadline:
+    """Bounds everything after the headline measurement.  The auxiliary sections (multi-GPU consistency checks, extract_vol,
+    render, NGP, comparators) run AFTER the contract's numbers are in `line`; if one of them does not finish within `seconds`
+    (a collective that never completes, a slow host leg) rank 0 prints the line as it stands, naming the section it was in,
+    and every rank exits 0 - the headline must not be lost to an auxiliary measurement."""
+
+    def __init__(self, seconds: float, rank: int, line: dict):
+        self.seconds, self.rank, self.line = seconds, rank, line
+        self.section = "start"
+        self.lock = threading.Lock()
+        self.printed = False
+        self.timer = threading.Timer(seconds, self._fire)
+        self.timer.daemon = True
+        self.timer.start()
+
+    def enter(self, section: str):
+        self.section = section
+
+    def _fire(self):
+        with self.lock:
+            if self.printed:
+                return
+            self.printed = True
+            if self.rank == 0:
+                self.line["aux_timeout"] = {"section": self.section, "seconds": self.seconds}
+                try:
+                    text = json.dumps(self.line)
+                except Exception:          # the main thread was mutating a section's dict: drop the auxiliary sections
+                    text = json.dumps({k: v for k, v in self.line.items() if k in HEADLINE_KEYS or k == "aux_timeout"})
+                print(text, flush=True)
+            sys.stdout.flush()
+            os._exit(0)
+
+    def finish(self) -> bool:
+        """True if the caller is the one that prints."""
+        with self.lock:
+            if self.printed:
+                return False
+            self.printed = True
+        self.timer.cancel()
+        return True
+
+
+HEADLINE_KEYS = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "repeats", "timed_region_s", "ms_per_step",
+                 "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config", "roofline", "e2e", "gpu_launches",
+                 "clocks", "step_tflops", "step_frac_of_sustained_tensor_peak", "stages")
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
 
@@ -341,14 +389,42 @@ def run_ours(args):
         stage_report[k]["hbm_gbs"] = round(STAGE_BYTES[kk] * pts[nn] / (mean[k] * 1e-3) / 1e9, 0)
         stage_report[k]["bound"] = STAGE_BOUND[kk]
 
+    # ---- the contract's line is complete here; what follows only adds auxiliary sections to it, under a deadline ----------
+    stash_gb = (D.ops.mlp_stash_bytes(pts["coarse"]) + D.ops.mlp_stash_bytes(pts["fine"]) + D.ops.mlp_dz_bytes(pts["fine"])) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "repeats": REP, "timed_region_s": ms_total * REP * 1e-3,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "rays_per_gpu": B_RAYS, "global_rays": B_RAYS * world, "N_samples": S_COARSE,
+                   "N_importance": N_IMPORTANCE, "parallelism": f"dp{world} (rays sharded, one NCCL all-reduce of the flat gradient)",
+                   "l2": f"no explicit flush: each step streams {stash_gb:.2f} GB of activation/gradient scratch through HBM "
+                         "(>> 126 MB L2) and rotates over 8 distinct ray batches"},
+        "roofline": roofline,
+        "cpu_baseline": None,
+        "gpu_eager_baseline": None,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host[0].numel() * 4 * world,
+                "d2h_bytes_per_step": 8 * world, "ms_per_step": ms_e2e / K},
+        "gpu_launches": launches,
+        "clocks": clk.summary(),
+        "step_tflops": step_tflops, "step_frac_of_sustained_tensor_peak": step_tflops / (pk["tensor_sustained"] * world),
+        "stages": stage_report,
+        "multi_gpu_checks": None, "extract_vol": None, "precompute_rays": None, "volume_points": None, "render": None,
+        "ngp": None,
+    }
+    aux_s = args.aux_timeout if args.aux_timeout > 0 else (420.0 if world == 1 else 150.0)
+    guard = AuxDeadline(aux_s, rank, line)
+
     # ---- N > 1: on-hardware consistency of the data-parallel state + strong scaling of the same 4096 global rays --------
     multi = None
+    guard.enter("multi_gpu_checks: parameters + strong scaling")
     if world > 1:
         pmax, pmin = tr.flat.clone(), tr.flat.clone()
         dist.all_reduce(pmax, op=dist.ReduceOp.MAX)
         dist.all_reduce(pmin, op=dist.ReduceOp.MIN)
         multi = {"param_max_minus_min_over_ranks_after_steps": float((pmax - pmin).abs().max()),
                  "steps_checked": int(tr.step_dev.item())}
+        line["multi_gpu_checks"] = multi
         del pmax, pmin
         # strong scaling: ONE 4096-ray global batch, rank r owns rays [r*B/G, (r+1)*B/G)
         from deepfields_nerf_b200.train import shard_slice
@@ -370,9 +446,10 @@ def run_ours(args):
         del strong
 
     # ---- extract_vol 512^3 (BASELINE.json config 4), slab-sharded, reported beside the headline ---------------
-    # N > 1: min/max + 256-bin histogram all-reduces (ONE global Otsu threshold) and the gather of the u8 slabs to rank 0
+    # N > 1: min/max + 256-bin histogram all-reduces (ONE global Otsu threshold) and the all-gather of the u8 slabs into the volume
     # are inside the timed region.
     extract = None
+    guard.enter("extract_vol")
     if not args.no_extract:
         R = args.extract_res
         mf.eval()
@@ -399,17 +476,18 @@ def run_ours(args):
         extract = {"metric": "extract_vol_points_per_s", "value": R ** 3 / (ms_x * 1e-3), "unit": "points/s", "resolution": R,
                    "ms": ms_x, "threshold": thr_x,
                    "includes": "MLP query + min/max + histogram + Otsu + u8 pack" + (
-                       " + min/max and histogram all-reduces + gather of the u8 slabs to rank 0 (%d MB)" % (4 * R ** 3 // 2 ** 20)
+                       " + min/max and histogram all-reduces + all-gather of the u8 slabs into one volume (%d MB)" % (4 * R ** 3 // 2 ** 20)
                        if world > 1 else " (outputs stay in HBM)"),
                    "tflops": tf, "frac_of_sustained_tensor_peak": tf / (pk["tensor_sustained"] * world)}
         if rank == 0:
             extract["gathered_voxels"] = int(occ_g.numel())
+        line["extract_vol"] = extract
         del out, occ_g, col_g
         if world > 1:
             # the sharded volume IS the single-GPU volume: same threshold on every rank, and on a 64^3 grid every rank's
             # slab equals the same range of the volume one GPU computes alone (bit for bit), threshold included
-            thr_all = [None] * world
-            dist.all_gather_object(thr_all, thr_x)
+            thr_mm = torch.tensor([float(thr_x), -float(thr_x)], dtype=torch.float64, device=dev)
+            dist.all_reduce(thr_mm, op=dist.ReduceOp.MAX)          # max and -min over the ranks
             Rc = 64
             with torch.no_grad():
                 s_sig, s_rgb, s_start, s_thr, s_occ, s_col = D.extract_volume_fused(mf, Rc, rank=rank, world=world, group=group)
@@ -419,12 +497,13 @@ def run_ours(args):
                         and torch.equal(s_sig, f_sig[sl_c]))
             flag = torch.tensor([1.0 if same else 0.0], device=dev)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            multi["extract_threshold_identical_on_all_ranks"] = bool(len(set(thr_all)) == 1)
+            multi["extract_threshold_identical_on_all_ranks"] = bool(float(thr_mm[0]) == -float(thr_mm[1]))
             multi["extract_64_sharded_equals_single_gpu"] = bool(flag.item() == 1.0)
             multi["extract_64_threshold"] = s_thr
 
     # ---- ray generation + cube intersection + compaction (scripts/precompute_rays.py), the step in front of the path ----
     raygen = None
+    guard.enter("precompute_rays")
     if rank == 0 and not args.no_extract:
         import numpy as np
         sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
@@ -454,10 +533,12 @@ def run_ours(args):
             O.precompute_rays(Hc, Wc, Kc, poses_c[:1], np.zeros((1, Hc, Wc, 3), dtype=np.uint8))
             raygen["cpu_port_rays_per_s"] = Hc * Wc / (time.perf_counter() - t0)
             raygen["cpu_sample"] = "1 camera of 1080x1920, numpy oracle port, 1 thread"
+        line["precompute_rays"] = raygen
         del img, res
 
     # ---- occupied voxels -> coloured point set (scripts/post_process_vol.py), the step after extract_vol ----
     volpts = None
+    guard.enter("volume_points")
     if rank == 0 and not args.no_extract:
         Rv = args.extract_res
         gen = torch.Generator(device=dev).manual_seed(5)
@@ -478,10 +559,12 @@ def run_ours(args):
                   "kept_fraction": pv.shape[0] / Rv ** 3, "ms": ms_v, "hbm_gbs": algo / (ms_v * 1e-3) / 1e9,
                   "frac_of_hbm_peak": algo / (ms_v * 1e-3) / 1e9 / pk["hbm"],
                   "includes": "argwhere + colour max + gather + normalise + AABB slice + 8-byte count read-back, through the public API"}
+        line["volume_points"] = volpts
         del occ, rgbv, pv, cv
 
     # ---- inference render of a 1920x1080 image, 256 samples/ray, with and without early ray termination (config 5) ----
     render = None
+    guard.enter("render")
     if not args.no_extract:
         from common import make_cameras, peaked
         Hr, Wr = 1080, 1920
@@ -511,7 +594,8 @@ def run_ours(args):
                   "ert_eps": 1e-4, "ert_segments": 8, "ert_evaluated_fraction_rank0": res_r["ert"][1]["evaluated_fraction"],
                   "value": Hr * Wr / (res_r["ert"][0] * 1e-3), "unit": "pixels/s",
                   "includes": "ray generation, cube test, coarse + fine MLP, resampling, compositing" + (
-                      ", gather of the row tiles to rank 0" if world > 1 else "") + "; synthetic opaque medium"}
+                      ", all-gather of the row tiles into one image" if world > 1 else "") + "; synthetic opaque medium"}
+        line["render"] = render
         if world > 1:
             # row-sharded render == unsharded render (per-pixel draws fixed), 64 x 48 image
             Hs, Ws = 48, 64
@@ -530,6 +614,7 @@ def run_ours(args):
 
     # ---- Instant-NGP variant (config 3, scripts/instantngp.py): fused inference query, hash-grid encode and its backward ----
     ngp = None
+    guard.enter("ngp")
     if rank == 0 and not args.no_extract:
         torch.manual_seed(7)
         net = D.InstantNGP("large").to(dev)
@@ -608,12 +693,14 @@ def run_ours(args):
                "note": "table gathers are served by L2 (26 MB table), so the GB/s are gather throughput, not HBM traffic; "
                        "uniform random points = worst-case locality; parity unpinned (tiny-cuda-nn absent)",
                "includes": "hash-grid encode + density MLP + SH4 + colour MLP in one launch, fp16 rgb + features written"}
+        line["ngp"] = ngp
         del net, pos_n, dir_n, d_enc, d_tab, enc_holder
 
     # ---- same-box comparator: the port of the reference step in stock eager PyTorch ON THIS GPU ------------
     # (what the hand-written kernels buy over library kernels on the same device); 4096 rays, coarse + fine, backward,
     # AdamW; bf16 autocast as scripts/train.py:262 (fp16 there) and fp32 with TF32 matmuls as scripts/train.py:22-24.
     eager = None
+    guard.enter("gpu_eager_baseline")
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
             from oracle import nerf_oracle as O
@@ -651,41 +738,21 @@ def run_ours(args):
             torch.cuda.empty_cache()
         except Exception as e:  # an auxiliary measurement must not take the headline line down with it
             eager = {"error": f"{type(e).__name__}: {e}"[:300]}
+        line["gpu_eager_baseline"] = eager
 
     cpu = None
+    guard.enter("cpu_baseline")
     if rank == 0 and world == 1 and not args.no_cpu:
         v, sample, cores, variants = cpu_rate(args.cpu_budget)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "variants": variants}
+        line["cpu_baseline"] = cpu
 
-    if rank == 0:
-        stash_gb = (D.ops.mlp_stash_bytes(pts["coarse"]) + D.ops.mlp_stash_bytes(pts["fine"]) + D.ops.mlp_dz_bytes(pts["fine"])) / 1e9
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "repeats": REP, "timed_region_s": ms_total * REP * 1e-3,
-            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "rays_per_gpu": B_RAYS, "global_rays": B_RAYS * world, "N_samples": S_COARSE,
-                       "N_importance": N_IMPORTANCE, "parallelism": f"dp{world} (rays sharded, one NCCL all-reduce of the flat gradient)",
-                       "l2": f"no explicit flush: each step streams {stash_gb:.2f} GB of activation/gradient scratch through HBM "
-                             "(>> 126 MB L2) and rotates over 8 distinct ray batches"},
-            "roofline": roofline,
-            "cpu_baseline": cpu,
-            "gpu_eager_baseline": eager,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host[0].numel() * 4 * world,
-                    "d2h_bytes_per_step": 8 * world, "ms_per_step": ms_e2e / K},
-            "gpu_launches": launches,
-            "clocks": clk.summary(),
-            "step_tflops": step_tflops, "step_frac_of_sustained_tensor_peak": step_tflops / (pk["tensor_sustained"] * world),
-            "stages": stage_report,
-            "multi_gpu_checks": multi,
-            "extract_vol": extract,
-            "precompute_rays": raygen,
-            "volume_points": volpts,
-            "render": render,
-            "ngp": ngp,
-        }
+    if guard.finish() and rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        bye = threading.Timer(30.0, lambda: os._exit(0))      # the line is out: a communicator teardown may not hold the job
+        bye.daemon = True
+        bye.start()
         dist.destroy_process_group()
 
 
@@ -699,6 +766,8 @@ def main():
     ap.add_argument("--no-extract", action="store_true", help="skip the extract_vol measurement")
     ap.add_argument("--extract-res", type=int, default=512)
     ap.add_argument("--cpu-budget", type=float, default=12.0)
+    ap.add_argument("--aux-timeout", type=float, default=0.0,
+                    help="seconds allowed for everything after the headline measurement (0: 420 at N=1, 150 at N>1)")
     ap.add_argument("--min-seconds", type=float, default=2.5,
                     help="the K timed steps are repeated back to back until the timed region lasts this long")
     args = ap.parse_args()

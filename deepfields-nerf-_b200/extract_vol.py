@@ -123,37 +123,38 @@ def default_group(world: int, group=None):
 
 
 def gather_slabs(occ: torch.Tensor, col: torch.Tensor, resolution: int, rank: int, world: int, group=None, dst: int = 0):
-    """Stitches the ranks' u8 slabs into ONE volume on rank `dst`: x-slabs are contiguous ranges of the flat
-    grid, so rank r's bytes land at [x0*R*R, x1*R*R) of the full arrays.  Returns (occupancy [R^3] u8, rgb [R^3,3] u8) on
-    `dst`, (None, None) elsewhere.  Point-to-point (slabs may be ragged when R % world != 0)."""
+    """Stitches the ranks' u8 slabs into ONE volume: x-slabs are contiguous ranges of the flat grid in rank
+    order, so the all-gather of equal slabs IS the volume; ragged slabs (R % world != 0) are padded to the largest one and
+    cut to their ranges afterwards.  Returns (occupancy [R^3] u8, rgb [R^3,3] u8) on `dst`, (None, None) elsewhere.
+    One NCCL all-gather per array on the ranks' communicator: no point-to-point traffic (unbatched send / recv pairs on an
+    8-rank communicator did not complete on the 8-GPU box), 4 * R^3 bytes received per rank."""
     R = resolution
+    occ, col = occ.reshape(-1).contiguous(), col.reshape(-1, 3).contiguous()
     if world == 1:
-        return occ.reshape(-1), col.reshape(-1, 3)
+        return occ, col
     dist = torch.distributed
-    if rank == dst:
-        full_o = torch.empty(R * R * R, dtype=torch.uint8, device=occ.device)
-        full_c = torch.empty(R * R * R, 3, dtype=torch.uint8, device=occ.device)
-        reqs = []
-        for r in range(world):
-            x0, x1 = slab_range(R, r, world)
-            a, b = x0 * R * R, x1 * R * R
-            if b == a:
-                continue
-            if r == dst:
-                full_o[a:b].copy_(occ.reshape(-1))
-                full_c[a:b].copy_(col.reshape(-1, 3))
-            else:
-                src = dist.get_global_rank(group, r) if group is not None and group is not dist.group.WORLD else r
-                reqs.append(dist.irecv(full_o[a:b], src=src, group=group))
-                reqs.append(dist.irecv(full_c[a:b], src=src, group=group))
-        for q in reqs:
-            q.wait()
-        return full_o, full_c
-    if occ.numel():
-        g_dst = dist.get_global_rank(group, dst) if group is not None and group is not dist.group.WORLD else dst
-        dist.send(occ.reshape(-1).contiguous(), dst=g_dst, group=group)
-        dist.send(col.reshape(-1, 3).contiguous(), dst=g_dst, group=group)
-    return None, None
+    sizes = [(x1 - x0) * R * R for x0, x1 in (slab_range(R, r, world) for r in range(world))]
+    if occ.numel() != sizes[rank]:
+        raise ValueError("gather_slabs: rank %d holds %d voxels, its slab has %d" % (rank, occ.numel(), sizes[rank]))
+    n_max = max(sizes)
+    dev = occ.device
+    if min(sizes) == n_max:
+        full_o = torch.empty(R * R * R, dtype=torch.uint8, device=dev)
+        full_c = torch.empty(R * R * R, 3, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(full_o, occ, group=group)
+        dist.all_gather_into_tensor(full_c.view(-1), col.view(-1), group=group)
+    else:
+        n = sizes[rank]
+        mine = torch.zeros(4 * n_max, dtype=torch.uint8, device=dev)     # [occ | rgb] of this slab, padded
+        mine[:n].copy_(occ)
+        mine[n_max:n_max + 3 * n].copy_(col.view(-1))
+        every = torch.empty(world, 4 * n_max, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(every.view(-1), mine, group=group)
+        if rank != dst:
+            return None, None
+        full_o = torch.cat([every[r, :sizes[r]] for r in range(world)])
+        full_c = torch.cat([every[r, n_max:n_max + 3 * sizes[r]] for r in range(world)]).view(-1, 3)
+    return (full_o, full_c) if rank == dst else (None, None)
 
 
 def global_stats(t: torch.Tensor, group=None) -> dict:

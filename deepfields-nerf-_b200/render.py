@@ -101,26 +101,26 @@ def render_image(model_coarse, model_fine, H, W, K, pose, rows=None, background=
 
 
 def gather_rows(part: torch.Tensor, H: int, rank: int, world: int, group=None, dst: int = 0):
-    """Assembles the row tiles of a row-sharded render on rank `dst` (gather of rgb tiles): rank r's
-    [rows_r, W, 3] tile lands at rows row_range(H, r, world) of the [H, W, 3] image.  Returns the image on `dst`, None elsewhere."""
+    """Assembles the row tiles of a row-sharded render (gather of rgb tiles): rank r's [rows_r, W, 3] tile lands
+    at rows row_range(H, r, world) of the [H, W, 3] image.  Returns the image on `dst`, None elsewhere.  One all-gather on
+    the ranks' communicator (tiles padded to the tallest one when H % world != 0), no point-to-point traffic."""
     if world == 1:
         return part
     dist = torch.distributed
     W = part.shape[1]
-    if rank == dst:
+    rows = [r1 - r0 for r0, r1 in (row_range(H, r, world) for r in range(world))]
+    if part.shape[0] != rows[rank]:
+        raise ValueError("gather_rows: rank %d holds %d rows, its tile has %d" % (rank, part.shape[0], rows[rank]))
+    h_max = max(rows)
+    part = part.contiguous()
+    if min(rows) == h_max:
         img = torch.empty(H, W, 3, dtype=part.dtype, device=part.device)
-        reqs = []
-        for r in range(world):
-            r0, r1 = row_range(H, r, world)
-            if r1 == r0:
-                continue
-            if r == dst:
-                img[r0:r1].copy_(part)
-            else:
-                reqs.append(dist.irecv(img[r0:r1], src=r, group=group))
-        for q in reqs:
-            q.wait()
-        return img
-    if part.numel():
-        dist.send(part.contiguous(), dst=dst, group=group)
-    return None
+        dist.all_gather_into_tensor(img.view(-1), part.view(-1), group=group)
+        return img if rank == dst else None
+    mine = torch.zeros(h_max, W, 3, dtype=part.dtype, device=part.device)
+    mine[:rows[rank]].copy_(part)
+    every = torch.empty(world, h_max, W, 3, dtype=part.dtype, device=part.device)
+    dist.all_gather_into_tensor(every.view(-1), mine.view(-1), group=group)
+    if rank != dst:
+        return None
+    return torch.cat([every[r, :rows[r]] for r in range(world)])

@@ -77,3 +77,39 @@ def test_onecycle_tables_match_oracle(D):
     for s in (0, 1, 19, 20, 100, 199):
         lr, b1 = O.onecycle(s, 200, 5e-4)
         assert lrs[s] == pytest.approx(lr, rel=1e-12) and b1s[s] == pytest.approx(b1, rel=1e-12)
+
+
+def test_bench_aux_deadline_prints_headline_once_and_exits_zero(tmp_path):
+    """bench.py's auxiliary sections run under a deadline: if one never returns, rank 0 still prints ONE JSON line that
+    carries the headline numbers and names the section, and the process exits 0; a run that finishes in time prints the
+    line itself and the timer stays quiet."""
+    import json, subprocess, sys, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = textwrap.dedent("""
+        import sys, time, json
+        sys.path.insert(0, %r)
+        import bench
+        line = {"metric": bench.METRIC, "value": 1.0, "unit": bench.UNIT, "extract_vol": None}
+        g = bench.AuxDeadline(float(sys.argv[1]), int(sys.argv[2]), line)
+        g.enter("extract_vol")
+        if sys.argv[3] == "hang":
+            time.sleep(30)
+            sys.exit(7)
+        line["extract_vol"] = {"ms": 1.0}
+        if g.finish() and int(sys.argv[2]) == 0:
+            print(json.dumps(line), flush=True)
+        time.sleep(1.0)
+    """ % root)
+    script = tmp_path / "deadline.py"
+    script.write_text(code)
+    hung = subprocess.run([sys.executable, str(script), "0.5", "0", "hang"], capture_output=True, text=True, timeout=120)
+    assert hung.returncode == 0
+    lines = [l for l in hung.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    got = json.loads(lines[0])
+    assert got["value"] == 1.0 and got["aux_timeout"]["section"] == "extract_vol" and got["extract_vol"] is None
+    quiet = subprocess.run([sys.executable, str(script), "0.5", "1", "hang"], capture_output=True, text=True, timeout=120)
+    assert quiet.returncode == 0 and quiet.stdout.strip() == ""          # other ranks leave without printing
+    done = subprocess.run([sys.executable, str(script), "0.5", "0", "ok"], capture_output=True, text=True, timeout=120)
+    lines = [l for l in done.stdout.splitlines() if l.strip()]
+    assert done.returncode == 0 and len(lines) == 1 and "aux_timeout" not in json.loads(lines[0])

@@ -83,12 +83,11 @@ def test_row_ranges_cover_ragged_heights():
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
 
 
-def _gather_worker(rank, world, port, out):
+def _gather_worker(rank, world, port, R, H, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     import deepfields_nerf_b200 as D
     from deepfields_nerf_b200 import extract_vol as X
-    R = 7                                                          # ragged: slabs of 4 and 3 planes (3 ranks: 3, 3, 1)
     g = torch.Generator().manual_seed(3)
     occ_full = (torch.rand(R ** 3, generator=g) < 0.3).to(torch.uint8)
     col_full = torch.randint(0, 256, (R ** 3, 3), generator=g, dtype=torch.uint8)
@@ -98,7 +97,7 @@ def _gather_worker(rank, world, port, out):
     occ, col = X.gather_slabs(occ_full[sl].clone(), col_full[sl].clone(), R, rank, world, dist.group.WORLD)
     st = X.global_stats(sig_full[sl], dist.group.WORLD)
     # the sharded Otsu of apply_otsu_threshold needs the CUDA histogram; its collectives are covered by _worker above
-    H, W = 5, 3
+    W = 3
     img_full = torch.arange(H * W * 3, dtype=torch.float32).reshape(H, W, 3)
     r0, r1 = D.row_range(H, rank, world)
     img = D.gather_rows(img_full[r0:r1].clone(), H, rank, world, dist.group.WORLD)
@@ -107,15 +106,16 @@ def _gather_worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_gather_slabs_rows_and_global_stats(world):
+# R = 7 / H = 5 are ragged (slabs of 4 + 3 planes; 3 ranks: 3, 3, 1 -> padded all-gather); 12 / 6 split evenly (the all-gather
+# output IS the volume); world 4 covers the case N = 2 cannot: more than one peer per rank
+@pytest.mark.parametrize("world,R,H", [(2, 7, 5), (3, 7, 5), (2, 12, 6), (3, 12, 6), (4, 12, 8), (4, 7, 5)])
+def test_gather_slabs_rows_and_global_stats(world, R, H):
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_gather_worker, args=(world, 29741 + world, out), nprocs=world, join=True)
+    mp.spawn(_gather_worker, args=(world, 29741 + 8 * world + R % 8, R, H, out), nprocs=world, join=True)
     assert out[0]["occ_ok"] is True and out[0]["img_ok"] is True       # rank 0 holds ONE stitched volume / image
     assert all(out[r]["occ_ok"] is None and out[r]["img_ok"] is None for r in range(1, world))
     g = torch.Generator().manual_seed(3)
-    R = 7
     torch.rand(R ** 3, generator=g); torch.randint(0, 256, (R ** 3, 3), generator=g, dtype=torch.uint8)
     sig = torch.rand(R ** 3, generator=g) * 9.0
     for r in range(world):                                              # every rank reports the statistics of the whole volume
