@@ -235,6 +235,31 @@ def cpu_rate(budget_s: float):
     return out[best]["rays_per_s"], sample, cores, out
 
 
+def cpu_extract_rate(R: int = 64):
+    """points/s of the CPU port of extract_vol (the dense query on a 64^3 sub-grid, per-point rate comparable with
+    the 512^3 figure since the work per point does not depend on R): grid, eval-mode query, Otsu, u8 pack; fp32, all host threads,
+    one warm-up batch, median of 3."""
+    import torch
+    from common import make_state_dict
+    from oracle import nerf_oracle as O
+    cores = use_all_host_threads()
+    sd = make_state_dict(32, 256)
+    view = torch.tensor([0.0, 0.0, 1.0])
+    with torch.no_grad():
+        O.dense_query(sd, O.grid_points((-1.0, 1.0), 16), view)
+        ts = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            pts = O.grid_points((-1.0, 1.0), R)
+            sig, rgb = O.dense_query(sd, pts, view)
+            thr = O.otsu_threshold(sig)
+            O.pack_volume(sig, rgb, thr, R)
+            ts.append(time.perf_counter() - t0)
+    ts.sort()
+    return {"value": R ** 3 / ts[1], "unit": "points/s", "cores": cores, "kind": "port",
+            "sample": f"median of 3 passes over a {R}^3 grid (grid + query + Otsu + u8 pack), oracle port, torch CPU fp32"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -482,6 +507,11 @@ def run_ours(args):
         if rank == 0:
             extract["gathered_voxels"] = int(occ_g.numel())
         line["extract_vol"] = extract
+        if rank == 0 and world == 1 and not args.no_cpu:
+            try:
+                extract["cpu_baseline"] = cpu_extract_rate(64)
+            except Exception as e:  # an auxiliary measurement must not take the headline line down with it
+                extract["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"[:300]}
         del out, occ_g, col_g
         if world > 1:
             # the sharded volume IS the single-GPU volume: same threshold on every rank, and on a 64^3 grid every rank's
