@@ -777,6 +777,8 @@ def run_ours(args):
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "variants": variants}
         line["cpu_baseline"] = cpu
 
+    guard.enter("final barrier")
+    barrier()                      # rank 0 alone ran the last sections: leave together, so that the teardown is not skewed
     if guard.finish() and rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
