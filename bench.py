@@ -685,7 +685,8 @@ def run_ours(args):
             Bn = 1 << 18
             o_n, d_n, near_n, far_n, tgt_n = (t.to(dev) for t in make_rays(9, Bn))
             near_n, far_n = near_n.reshape(-1), far_n.reshape(-1)
-            trn = D.NGPTrainer(net, S_COARSE, N_IMPORTANCE, lr=5e-4, total_steps=64)
+            trn = D.NGPTrainer(net, S_COARSE, N_IMPORTANCE, lr=5e-4, total_steps=64,
+                               process_group=False)     # rank 0 alone runs this section: no gradient exchange
             for _ in range(2):
                 trn.step(o_n, d_n, near_n, far_n, tgt_n)
             torch.cuda.synchronize()

@@ -114,7 +114,9 @@ class FusedTrainer:
         self.dev, self.S, self.I = dev, N_samples, N_importance
         self.white_bg, self.dist_last, self.wd = white_bg, dist_last, weight_decay
         self.train_noise = train_noise
-        self.pg = process_group
+        # process_group=False: this trainer is local to the process even though a process group exists (no gradient exchange)
+        self.local = process_group is False
+        self.pg = process_group = None if self.local else process_group
         self.world = torch.distributed.get_world_size(process_group) if self._dist_on() else 1
         rank = torch.distributed.get_rank(process_group) if self._dist_on() else 0
         self.rng = rng
@@ -182,7 +184,7 @@ class FusedTrainer:
         return out
 
     def _dist_on(self):
-        return torch.distributed.is_available() and torch.distributed.is_initialized()
+        return not self.local and torch.distributed.is_available() and torch.distributed.is_initialized()
 
     def _alloc(self, B):
         if self._B == B:
@@ -566,8 +568,10 @@ class NGPTrainer:
             raise RuntimeError("NGPTrainer needs a CUDA model (no CPU fallback)")
         self.model, self.dev, self.S, self.I = model, dev, N_samples, N_importance
         self.white_bg, self.dist_last, self.wd, self.loss_scale = white_bg, dist_last, weight_decay, float(loss_scale)
-        self.pg = process_group
-        dist_on = torch.distributed.is_available() and torch.distributed.is_initialized()
+        # process_group=False: this trainer is local to the process even though a process group exists (no gradient exchange)
+        local = process_group is False
+        self.pg = process_group = None if local else process_group
+        dist_on = not local and torch.distributed.is_available() and torch.distributed.is_initialized()
         self.world = torch.distributed.get_world_size(process_group) if dist_on else 1
         rank = torch.distributed.get_rank(process_group) if dist_on else 0
         self.seed = int(seed) if seed is not None else 0x5EED + 7919 * rank
