@@ -84,6 +84,8 @@ SIGNATURES = {
     "dfn_ert_update": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _f, _f, _p, _p, _p, _p, _p]),
     "dfn_compact_indices_workspace_bytes": (_ll, [_ll]),
     "dfn_compact_indices": (_i, [_p, _p, _ll, _p, _p, _p, _p]),
+    "dfn_compact_indices_static_max_n": (_ll, []),
+    "dfn_compact_indices_static": (_i, [_p, _p, _ll, _p, _p, _p]),
     "dfn_hashgrid_init": (_ll, [C.POINTER(HashGrid), _i]),
     "dfn_hashgrid_forward": (_i, [_p, _ll, _p, C.POINTER(HashGrid), _p, _p]),
     "dfn_hashgrid_backward": (_i, [_p, _ll, _p, C.POINTER(HashGrid), _f, _p, _p]),

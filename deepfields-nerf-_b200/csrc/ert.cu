@@ -7,6 +7,8 @@
 //                transmittance by prod(1 - alpha + 1e-10) of the segment (train.py:89-95), flag the ray alive or not
 //   compact      ordered compaction of the active list by those flags (compact.cuh)
 #include "compact.cuh"
+#include <mutex>
+#include "../../include/deepfields_b200.h"
 
 namespace {
 using dfn_compact::kChunk;
@@ -91,5 +93,70 @@ extern "C" int dfn_compact_indices(const unsigned char* flags, const int* idx_in
   DFN_CHECK_LAUNCH("compact_indices(scan)");
   emit_indices_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(idx_in, w.offsets, w.ballots, idx_out);
   DFN_CHECK_LAUNCH("compact_indices(emit)");
+  return DFN_OK;
+}
+
+// ---- dfn_compact_indices_static: the same compaction for callers that have no device memory to hand over as a workspace ----
+// dfn_compact_indices needs ~0.14 B of scratch per flag (chunk counts, chunk offsets, warp ballots) and leaves the allocation to
+// the caller.  Some hosts of this library cannot make one: a render thread living inside an engine that reserved the whole
+// device for its own arena at start-up (a later cudaMalloc simply fails there), a frame loop that must not take the
+// device-wide synchronisation cudaMalloc / cudaFree imply, or a plug-in whose contract hands it input and output buffers and
+// nothing else.  For them the scratch lives in the library image itself: one fixed array per GPU, present from the moment the
+// library is loaded on that GPU until the process exits, large enough for DFN_COMPACT_STATIC_MAX_N flags.
+namespace {
+constexpr long long kStaticMaxN = 1LL << 22;                         // = DFN_COMPACT_STATIC_MAX_N (static_assert below)
+constexpr long long kStaticChunks = kStaticMaxN / kChunk;            // 4096
+constexpr long long kStaticBytes = ((kStaticChunks * 4 + 16 + kStaticChunks * 8 + 16 + kStaticChunks * (kChunk / 8) + 255) / 256) * 256;
+static_assert(kStaticBytes == 573696, "static scratch size quoted in the header / DESIGN.md");
+static_assert(kStaticMaxN == DFN_COMPACT_STATIC_MAX_N, "header and kernel disagree on the limit");
+
+// The scratch.  In device code this name is the array; in HOST code it is only a handle for the runtime's symbol table (its
+// host address is meaningless to a kernel), so the launcher below asks the runtime for the device address once per GPU.
+static __device__ __align__(256) unsigned char g_compact_scratch[kStaticBytes];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+void* g_scratch_ptr[kMaxDevices] = {nullptr};   // device address of g_compact_scratch on GPU i, filled on first use
+}  // namespace
+
+extern "C" long long dfn_compact_indices_static_max_n(void) { return kStaticMaxN; }
+
+extern "C" int dfn_compact_indices_static(const unsigned char* flags, const int* idx_in, long long n, int* idx_out, long long* count,
+                                          void* stream) {
+  DFN_CHECK_ARG(n >= 0, "compact_indices_static: negative length");
+  DFN_CHECK_ARG(n <= kStaticMaxN,
+                "compact_indices_static: %lld flags exceed the built-in scratch (at most %lld per call); split the list or use "
+                "dfn_compact_indices with a caller-owned workspace", n, kStaticMaxN);
+  DFN_CHECK_ARG(count, "compact_indices_static: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (n == 0) { DFN_CUDA(cudaMemsetAsync(count, 0, 8, st), "compact_indices_static"); return DFN_OK; }
+  DFN_CHECK_ARG(flags && idx_out, "compact_indices_static: null pointer");
+
+  // set-up, once per GPU, with that GPU current: resolve the array's device address (every GPU has its own copy)
+  int dev = -1;
+  DFN_CUDA(cudaGetDevice(&dev), "compact_indices_static(cudaGetDevice)");
+  DFN_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "compact_indices_static: device ordinal %d not supported", dev);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (g_scratch_ptr[dev] == nullptr) {
+      void* p = nullptr;
+      DFN_CUDA(cudaGetSymbolAddress(&p, g_compact_scratch), "compact_indices_static(cudaGetSymbolAddress)");
+      DFN_CHECK_ARG(p != nullptr, "compact_indices_static: the runtime returned no address for the scratch array");
+      g_scratch_ptr[dev] = p;
+    }
+    scratch = g_scratch_ptr[dev];
+  }
+
+  // from here on identical to dfn_compact_indices.  Nothing in the scratch has to start at zero: every count, offset and
+  // ballot word this call reads was written earlier in this call (whatever the previous call left is overwritten or unread).
+  const long long chunks = (n + kChunk - 1) / kChunk;
+  const dfn_compact::Workspace w = dfn_compact::carve(scratch, n);
+  count_flags_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(flags, n, w.counts, w.ballots);
+  DFN_CHECK_LAUNCH("compact_indices_static(count)");
+  scan_counts_kernel<<<1, 1024, 0, st>>>(w.counts, chunks, w.offsets, count);
+  DFN_CHECK_LAUNCH("compact_indices_static(scan)");
+  emit_indices_kernel<<<static_cast<unsigned int>(chunks), kChunk, 0, st>>>(idx_in, w.offsets, w.ballots, idx_out);
+  DFN_CHECK_LAUNCH("compact_indices_static(emit)");
   return DFN_OK;
 }

@@ -206,6 +206,27 @@ int dfn_ert_update(const int* active, int n, const float* seg_rgb, const float* 
 long long dfn_compact_indices_workspace_bytes(long long n);
 int dfn_compact_indices(const unsigned char* flags, const int* idx_in, long long n, int* idx_out, long long* count,
                         void* workspace, void* stream);
+/* dfn_compact_indices without a workspace argument.  No counterpart in the reference (which has no compaction and no C
+ * interface); it exists for hosts that cannot give this library device memory beyond the input and output buffers: a render
+ * thread inside an engine whose arena already owns the whole GPU (cudaMalloc fails there), a frame loop that cannot afford the
+ * device-wide stall of cudaMalloc / cudaFree, a plug-in that is handed buffers and may not create any.  The scratch
+ * (573 696 bytes) is a fixed array inside the library image: every GPU on which the library gets loaded carries it until the
+ * process ends, whether this function is called or not.  Limits and rules:
+ *   - n <= DFN_COMPACT_STATIC_MAX_N (2^22 flags, enough for the 1920 x 1080 rays of a frame); a longer list is refused with an
+ *     error message, nothing is launched;
+ *   - the call itself allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); flags, idx_in, idx_out and
+ *     count are still the caller's;
+ *   - the first call on each GPU looks up the array's device address (cudaGetSymbolAddress, with that GPU current) and keeps
+ *     it; make that first call during start-up, before any stream capture begins;
+ *   - all calls on one GPU share the one array: two calls whose kernels may overlap on the GPU (different streams without an
+ *     ordering between them, or two host threads) corrupt each other's counts -- order them on one stream or with events.
+ *     The array keeps whatever the last call wrote; the function does not rely on it (every word it reads it has written
+ *     earlier in the same call), so no clearing is needed between calls.
+ * Output is identical to dfn_compact_indices. */
+#define DFN_COMPACT_STATIC_MAX_N (1LL << 22)
+long long dfn_compact_indices_static_max_n(void); /* DFN_COMPACT_STATIC_MAX_N as the loaded library was built */
+int dfn_compact_indices_static(const unsigned char* flags, const int* idx_in, long long n, int* idx_out, long long* count,
+                               void* stream);
 
 /* ---- optimiser (scripts/train.py:244-259, :321-322) ---------------------------------------------- */
 /* AdamW on a flat buffer; lr_table/beta1_table [table_len] hold the OneCycleLR schedule, *step_ptr (device int,
