@@ -82,9 +82,13 @@ constexpr int kMaxBins = 256;
 
 // cdf[0] = 0, cdf[i+1] = fl32(sum_{j<=i} pdf[j]) with the running sum kept in double and rounded to fp32 per prefix - the
 // accumulation torch's CPU cumsum performs.  On entry cdf[1..NW] holds the pdf.  The sum runs as a warp
-// scan: every lane adds a contiguous run, the run totals are scanned with shuffles.  The pdf values are fp32 numbers within
-// 2^-17 of each other at most ((w + 1e-5) / sum, at most 255 terms), so every partial sum is EXACT in double whatever the
-// association, and the rounded prefixes are bit-identical to the sequential loop's.
+// scan: every lane adds a contiguous run, the run totals are scanned with shuffles, the exclusive prefix of a lane is its
+// left neighbour's inclusive one (a shuffle, not a subtraction).
+// PRECONDITION of the bit-for-bit claim: the weights are compositing weights (sum <= 1, what scripts/train.py:158 passes).
+// Then pdf = (w + 1e-5) / sum lies in [2^-17, 1], 24-bit mantissas spread over 17 binades plus 8 bits of carry fit the 53
+// bits of a double, every partial sum is EXACT whatever the association, and the rounded prefixes are bit-identical to the
+// sequential loop's.  The entry points accept any non-negative weights; with large or unnormalised ones (1e-5 / sum below
+// ~2^-21) the partial sums round, the association matters, and the prefixes are only within an fp32 ulp of torch's.
 __device__ __forceinline__ void pdf_to_cdf_warp(float* cdf, int NW, int lane) {
   const int per = (NW + 31) >> 5;              // <= 8
   const int i0 = lane * per;
@@ -102,7 +106,8 @@ __device__ __forceinline__ void pdf_to_cdf_warp(float* cdf, int NW, int lane) {
     const double t = __shfl_up_sync(0xffffffffu, incl, o);
     if (lane >= o) incl += t;
   }
-  const double excl = incl - run;              // exact: see above
+  double excl = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane == 0) excl = 0.0;
   __syncwarp();
 #pragma unroll
   for (int k = 0; k < 8; ++k) {

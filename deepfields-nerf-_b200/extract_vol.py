@@ -4,6 +4,7 @@ threshold, `volume.pth` in the reference layout.  The grid is never materialised
 from __future__ import annotations
 
 import argparse
+import datetime
 import os
 import time
 from pathlib import Path
@@ -14,6 +15,10 @@ import torch
 from . import ops
 from .config import load_config
 from .model import InstantNGP, OptimizedVanillaNeRF
+
+# a collective that cannot complete (a rank that died, a mismatched call) fails after this long instead of holding the GPUs
+# for NCCL's default ten minutes
+_PG_TIMEOUT = datetime.timedelta(seconds=180)
 
 
 def generate_3d_grid(bounds: Tuple[float, float], resolution: int, device="cuda") -> torch.Tensor:
@@ -279,7 +284,7 @@ def main(argv=None):
     torch.cuda.set_device(dev)   # the ops launch on the current device's stream
     own_pg = False
     if world > 1 and not torch.distributed.is_initialized():
-        torch.distributed.init_process_group("nccl", device_id=dev)
+        torch.distributed.init_process_group("nccl", device_id=dev, timeout=_PG_TIMEOUT)
         own_pg = True
     group = torch.distributed.group.WORLD if world > 1 else None
     R = int(cfg.volume_resolution)   # --resolution is ignored in favour of the cfg (:283-284, :346-347)

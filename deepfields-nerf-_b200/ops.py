@@ -4,6 +4,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -49,17 +50,24 @@ def stratified_sample(near: Tensor, far: Tensor, t_vals: Tensor, t_rand: Tensor)
     return z
 
 
+_sm_limit_now = threading.local()   # mirror of the library's thread-local budget (the C ABI has a setter only)
+
+
 class sm_limit:
-    """`with ops.sm_limit(n):` the MLP launches inside size their persistent grids to n SMs (dfn_set_sm_limit)."""
+    """`with ops.sm_limit(n):` the MLP launches inside size their persistent grids to n SMs (dfn_set_sm_limit, per calling
+    thread; 0 = whole device).  Nests: leaving the block restores the budget that was in force when it was entered."""
 
     def __init__(self, n_sms: int):
         self.n = int(n_sms)
 
     def __enter__(self):
+        self.prev = getattr(_sm_limit_now, "n", 0)
         _lib.load().dfn_set_sm_limit(self.n)
+        _sm_limit_now.n = self.n
 
     def __exit__(self, *exc):
-        _lib.load().dfn_set_sm_limit(0)
+        _lib.load().dfn_set_sm_limit(self.prev)
+        _sm_limit_now.n = self.prev
 
 
 RNG_JITTER, RNG_PDF, RNG_NOISE_COARSE, RNG_NOISE_FINE = 1, 2, 3, 4   # stream ids of csrc/rng.cuh

@@ -4,6 +4,7 @@ entry point and bench.py use (one launch per stage, flat gradient buffer, fused 
 from __future__ import annotations
 
 import math
+import datetime
 import os
 import time
 from collections import OrderedDict
@@ -15,6 +16,10 @@ import torch
 from . import ops
 from .model import OptimizedVanillaNeRF, get_nerf_models
 from .sampling import StratifiedSampler
+
+# a collective that cannot complete (a rank that died, a mismatched call) fails after this long instead of holding the GPUs
+# for NCCL's default ten minutes
+_PG_TIMEOUT = datetime.timedelta(seconds=180)
 
 # forward_pass reads a module-global cfg exactly like the reference (scripts/train.py:148-177)
 cfg = SimpleNamespace(N_samples=64, N_importance=128, chunk_size=32768)
@@ -107,7 +112,7 @@ class FusedTrainer:
         """rng: "kernel" = jitter / inverse-CDF draws / sigma noise are drawn inside the kernels (Philox keyed by `seed`
         and the step counter: no draw reaches HBM, graph-replayable), "torch" = torch.rand / torch.randn tensors as in
         round 1; injected draws (parity tests) always win.  seed: defaults to 0x5EED + 7919 * rank (per-rank streams,
-        SURVEY 8e).  use_graph: replay the step as CUDA graphs (default: DFN_CUDA_GRAPH=1)."""
+        SURVEY 8e).  use_graph: replay the step as CUDA graphs (default: off; DFN_CUDA_GRAPH=1 turns it on)."""
         dev = next(model_coarse.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("FusedTrainer needs CUDA models (no CPU fallback)")
@@ -129,6 +134,11 @@ class FusedTrainer:
         ov = os.environ.get("DFN_OVERLAP", "0")
         self.overlap = tuple(int(x) for x in ov.split(",")) if "," in ov else None
         self._side = torch.cuda.Stream(device=dev) if self.overlap else None
+        if self.overlap and ops.bwd_fused_default():
+            # the one-launch backward sizes itself to the whole device and both networks would share one ring workspace on
+            # two streams at once: corrupted gradients or the ring's time-out trap
+            raise RuntimeError("DFN_BWD_FUSED=1 and DFN_OVERLAP cannot be combined: the fused backward needs the whole device "
+                               "and a workspace of its own per concurrent launch")
         self._keep = None
         self.models = (model_coarse, model_fine)
         n = ops.MLP_NUM_PARAMS
@@ -154,13 +164,13 @@ class FusedTrainer:
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.sampler = StratifiedSampler(N_samples, dev)
         self.loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
-        self._B = None
+        self._B, self._scratch = None, {}
         # optional per-stage CUDA-event timing (bench.py): list of (stage name, event) per recorded step
         self.profile = False
         self._marks = []
         self.launches_per_step = 0
         self._pending = []
-        self._static, self._graph_misses = None, 0
+        self._static, self.graph_captures = {}, 0   # static input buffers per batch size; graphs captured so far
 
     # ---- stage timing -----------------------------------------------------------------------------------
     def _mark(self, name, launches=1):
@@ -189,6 +199,17 @@ class FusedTrainer:
     def _alloc(self, B):
         if self._B == B:
             return
+        names = ("stash_c", "stash_f", "dz", "dz_c", "out_c", "out_f")
+        if self.use_graph:
+            # a captured graph holds the addresses of its batch size's scratch: keep one set per batch size alive instead of
+            # freeing the full batch's set when the short last batch of an epoch comes by
+            if self._B is not None:
+                self._scratch[self._B] = tuple(getattr(self, k) for k in names)
+            if B in self._scratch:
+                for k, v in zip(names, self._scratch[B]):
+                    setattr(self, k, v)
+                self._B = B
+                return
         S, T, dev = self.S, self.S + self.I, self.dev
         Pc, Pf = B * S, B * T
         u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=dev)  # noqa: E731
@@ -302,19 +323,29 @@ class FusedTrainer:
         self.launches_per_step = self._n_launch
 
     # ---- CUDA-graph replay of the step ------------------------------------------------------------------------------------
-    def _graph_for(self, tensors):
+    def _graph_for(self, B):
         """The whole step (world == 1) or its forward/backward and optimiser halves around the eager NCCL all-reduce
-        (world > 1), captured once per distinct set of input buffers and replayed afterwards.  Everything that changes from
-        step to step lives in device memory (step counter -> OneCycleLR tables and the Philox counter), so a replay IS the
-        next step."""
-        key = tuple(t.data_ptr() for t in tensors) + (tensors[0].shape[0],)
-        g = self._graphs.get(key)
+        (world > 1), captured ONCE PER BATCH SIZE on static input buffers and replayed afterwards (`step` copies every
+        batch into them: 44 B per ray).  Everything that changes from step to step lives in device memory (step counter ->
+        OneCycleLR tables and the Philox counter), so a replay IS the next step.  The warm-up run in front of the capture
+        (allocations, lazy initialisation) leaves no trace: parameters, Adam moments and the step counter are put back and
+        the bf16 weight images repacked, so the number of optimiser steps equals the number of `step()` calls, as in the
+        reference loop (scripts/train.py:285-323).  At world > 1 the replayed path exchanges the whole flat gradient with one
+        blocking all-reduce between the two graphs: it does NOT keep the eager path's fine/coarse overlap."""
+        g = self._graphs.get(B)
         if g is None:
+            tensors = self._static[B]
+            saved = [t.clone() for t in (self.flat, self.m, self.v, self.step_dev)]
             stream = torch.cuda.Stream(device=self.dev)
             stream.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(stream):           # warm-up outside the capture (allocations, lazy initialisation)
+            with torch.cuda.stream(stream):           # warm-up outside the capture, undone below
                 self.forward_backward(*tensors)
                 self.optimizer_step()
+                for dst, src in zip((self.flat, self.m, self.v, self.step_dev), saved):
+                    dst.copy_(src)
+                for m in self.models:
+                    m._packed.pack(m._flat)
+                    m._packed_version = (m._flat._version, sum(p._version for p in m._ordered_params()))
             torch.cuda.current_stream().wait_stream(stream)
             torch.cuda.synchronize()
             fb, opt = torch.cuda.CUDAGraph(), None
@@ -328,10 +359,9 @@ class FusedTrainer:
                 opt = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(opt):
                     self.optimizer_step()
-            g = (fb, opt, losses, tensors)            # `tensors` kept alive: the graph reads their buffers
-            self._graphs[key] = g
-            if len(self._graphs) > 64:
-                self._graphs.pop(next(iter(self._graphs)))
+            g = (fb, opt, losses)
+            self._graphs[B] = g
+            self.graph_captures += 1
         return g
 
     def _forward_backward_no_reduce(self, *tensors):
@@ -344,20 +374,14 @@ class FusedTrainer:
     def step(self, rays_o, rays_d, near, far, target, **draws):
         if self.use_graph and not draws and not self.profile and self.rng == "kernel":
             tensors = (rays_o, rays_d, near, far, target)
-            if not all(t.is_contiguous() for t in tensors):
-                tensors = tuple(t.contiguous() for t in tensors)
-            key = tuple(t.data_ptr() for t in tensors) + (tensors[0].shape[0],)
-            if key not in self._graphs and self._graph_misses >= 8:
-                # a stream of fresh input tensors (RayStore gathers): copy them into static buffers the graph reads
-                B = tensors[0].shape[0]
-                if self._static is None or self._static[0].shape[0] != B:
-                    self._static = tuple(torch.empty_like(t) for t in tensors)
-                for dst, src in zip(self._static, tensors):
+            B = tensors[0].shape[0]
+            static = self._static.get(B)
+            if static is None:                        # one set of input buffers per batch size, kept for the trainer's life
+                static = self._static[B] = tuple(torch.empty_like(t, memory_format=torch.contiguous_format) for t in tensors)
+            for dst, src in zip(static, tensors):
+                if dst.data_ptr() != src.data_ptr():
                     dst.copy_(src)
-                tensors = self._static
-            elif key not in self._graphs:
-                self._graph_misses += 1
-            fb, opt, losses, _ = self._graph_for(tensors)
+            fb, opt, losses = self._graph_for(B)
             fb.replay()
             if opt is not None:
                 torch.distributed.all_reduce(self.grads, group=self.pg)
@@ -507,7 +531,7 @@ def train(cfg_in):
     torch.cuda.set_device(dev)
     if dist_on:
         if not torch.distributed.is_initialized():
-            torch.distributed.init_process_group("nccl", device_id=dev)
+            torch.distributed.init_process_group("nccl", device_id=dev, timeout=_PG_TIMEOUT)
         rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     ckpt_dir = str(cfg.checkpoint_dir)
     os.makedirs(ckpt_dir, exist_ok=True)
@@ -520,7 +544,9 @@ def train(cfg_in):
                       bool(cfg.white_bg))
     perm_gen = torch.Generator(device=dev)
     perm_gen.manual_seed(0)                                          # the SAME shuffle on every rank ...
-    torch.manual_seed(1 + rank)                                      # ... but per-rank jitter / inverse-CDF / noise streams
+    # ... but per-rank jitter / inverse-CDF / noise streams: the kernels draw them from Philox keyed by the trainer's
+    # seed 0x5EED + 7919 * rank; torch's generator only matters for FusedTrainer(rng="torch")
+    torch.manual_seed(1 + rank)
     t0 = time.time()
     for epoch in range(1, cfg.num_epochs + 1):
         for it, (o, d, near, far, rgb) in enumerate(store.batches(cfg.batch_size, perm_gen)):
@@ -694,7 +720,7 @@ def train_ngp(cfg_in):
     torch.cuda.set_device(dev)
     if dist_on:
         if not torch.distributed.is_initialized():
-            torch.distributed.init_process_group("nccl", device_id=dev)
+            torch.distributed.init_process_group("nccl", device_id=dev, timeout=_PG_TIMEOUT)
         rank, world = torch.distributed.get_rank(), torch.distributed.get_world_size()
     ckpt_dir = str(cfg.checkpoint_dir)
     os.makedirs(ckpt_dir, exist_ok=True)

@@ -35,7 +35,8 @@ int dfn_points_on_rays(const float* rays_o, const float* rays_d, const float* z,
 /* sample_pdf  scripts/train.py:31-75 with the draw u [B,NS] passed in.  bins [B,NB] (or, bins_mid=1, z [B,NB+1]
  * whose mid-points are the bins, train.py:157); weights row r starts at weights + r*w_stride + w_offset and has
  * NB-1 entries (train.py:158 passes weights[...,1:-1]).  inds_out (int64 searchsorted result) and cdf_out
- * [B,NB] are optional. */
+ * [B,NB] are optional.  The cdf prefixes equal a sequential double-precision cumsum bit for bit when the weights are
+ * compositing weights (row sum <= 1); for arbitrary non-negative weights they are within one fp32 ulp of it. */
 int dfn_sample_pdf(const float* bins, int bins_mid, const float* weights, long long w_stride, int w_offset,
                    const float* u, int B, int NB, int NS, float* samples, long long* inds_out, float* cdf_out,
                    void* stream);

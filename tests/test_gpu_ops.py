@@ -131,6 +131,30 @@ def test_sample_pdf_fused(D, golden):
     assert torch.equal(s, s3)
 
 
+def test_sample_pdf_unnormalised_weights(D):
+    """dfn_sample_pdf is a public entry point and takes any non-negative weights, not only compositing weights (row sum
+    <= 1, the case whose cdf prefixes are exact in double).  With rows that sum to ~1e6 and entries spread over 12 decades
+    the warp scan's partial sums round, so the prefixes are no longer guaranteed bit-identical to a sequential double cumsum -
+    they must stay within an fp32 ulp of it, monotone, end at 1, and the inversion on the kernel's own cdf stays bit-exact."""
+    g = torch.Generator().manual_seed(5)
+    B, NB, NS = 300, 63, 128
+    z = torch.sort(torch.rand(B, NB + 1, generator=g) * 4 + 2, dim=1).values
+    mids = 0.5 * (z[:, :-1] + z[:, 1:])
+    w = 10.0 ** (torch.rand(B, NB - 1, generator=g) * 12 - 6)          # 1e-6 .. 1e6
+    w[::7, 5] = 0.0
+    u = torch.rand(B, NS, generator=g)
+    s, inds, cdf = D.ops.sample_pdf(mids.cuda(), w.cuda(), u.cuda(), return_inds=True, return_cdf=True)
+    cdf = cdf.cpu()
+    pdf = (w + 1e-5) / (w + 1e-5).sum(-1, keepdim=True)                # train.py:42-43 in fp32
+    ref = torch.cat([torch.zeros(B, 1), torch.cumsum(pdf.double(), -1).float()], -1)
+    assert float((cdf - ref).abs().max()) <= 6e-7                      # same bar as the normalised case: a few ulp(1)
+    assert bool((cdf[:, 1:] >= cdf[:, :-1]).all()) and bool((cdf[:, 0] == 0).all())
+    assert float((cdf[:, -1] - 1).abs().max()) <= 6e-7
+    s_chk, i_chk = O.invert_cdf(mids, cdf, u)
+    assert torch.equal(inds.cpu(), i_chk) and torch.equal(s.cpu(), s_chk)
+    assert bool(torch.isfinite(s).all())
+
+
 def test_merge_sort_bit_exact(D, golden):
     zz = D.ops.merge_sort_z(T(golden["sampler_z"]).cuda(), T(golden["pdf_samples"]).cuda())
     assert np.array_equal(zz.cpu().numpy(), golden["fine_z"])

@@ -44,10 +44,12 @@ def rel_err(a, b):
     return float((a - b).norm() / b.norm().clamp(min=1e-30))
 
 
-def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35, record=None):
+def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35, record=None, bf16_bar=None):
     """The kernels compute in bf16 like the reference under autocast.  Gradients are therefore judged against the
     fp32 oracle with the error the bf16-autocast oracle itself shows as the yardstick: per parameter tensor
-    rel_L2(cuda, fp32) <= slack * rel_L2(bf16 oracle, fp32) + floor (and an absolute cap)."""
+    rel_L2(cuda, fp32) <= slack * rel_L2(bf16 oracle, fp32) + floor (and an absolute cap).  bf16_bar: in addition
+    rel_L2(cuda, bf16 oracle) <= bf16_bar per tensor - north_star's 2e-2 against the reference's own precision (recorded
+    worst on a B200: 1.1e-2 at 1024 rays, 5.8e-3 at 4096, profiles/r2_grad_errors_B*.json)."""
     got = split_flat(got_flat.cpu(), ref32)
     worst, rows, ok = 0.0, [], True
     for k in param_keys(ref32):
@@ -61,6 +63,10 @@ def check_grads(got_flat, ref32, ref16, label, slack=1.3, floor=0.03, cap=0.35, 
             record[k] = {"cuda_vs_fp32": round(e, 5), "bf16_oracle_vs_fp32": round(e16, 5), "cuda_vs_bf16_oracle": round(rel_err(got[k], g16), 5),
                          "tol": round(tol, 5)}
         ok = ok and e <= tol
+        if bf16_bar is not None:
+            e_lp = rel_err(got[k], g16)
+            rows[-1] += f"  cuda-vs-bf16oracle {e_lp:.4f} (bar {bf16_bar})"
+            ok = ok and e_lp <= bf16_bar
         worst = max(worst, e)
     assert ok, label + "\n" + "\n".join(rows)
     return worst
@@ -230,8 +236,8 @@ def test_fused_step_vs_oracle_at_benchmarked_sizes(D, B):
     rec = {"rays": B, "N_samples": S, "N_importance": I, "losses_cuda": got.tolist(), "losses_fp32_oracle": [lc, lf],
            "losses_bf16_oracle": [lc16, lf16], "metric": "per-tensor relative L2 error of the parameter gradient",
            "coarse": {}, "fine": {}}
-    wc = check_grads(tr.grads[:n], rc, rc16, f"coarse B={B}", record=rec["coarse"])
-    wf = check_grads(tr.grads[n:], rf, rf16, f"fine B={B}", floor=0.06, record=rec["fine"])   # fine samples move with the bf16 coarse weights
+    wc = check_grads(tr.grads[:n], rc, rc16, f"coarse B={B}", record=rec["coarse"], bf16_bar=2e-2)
+    wf = check_grads(tr.grads[n:], rf, rf16, f"fine B={B}", floor=0.06, record=rec["fine"], bf16_bar=2e-2)   # fine samples move with the bf16 coarse weights
     rec["worst"] = {"coarse": wc, "fine": wf}
     out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
     try:
@@ -487,23 +493,32 @@ def test_mapped_weight_pack_equals_direct_pack(D):
 
 
 def test_graph_replay_equals_eager_steps(D):
-    """Steps replayed as CUDA graphs == the same steps run eagerly (same seed => same in-kernel draws).  The weight-gradient
-    flush adds fp32 partial sums with atomics in a different order every run, and AdamW's first steps turn a last-bit difference
-    of a near-zero gradient into a difference of the order of lr, so two EAGER runs of the same steps already differ; the
-    graph run must be no further from an eager run than a second eager run is (x5), and its losses must agree step by step."""
+    """Steps replayed as CUDA graphs == the same steps run eagerly (same seed => same in-kernel draws), ONE optimiser step per
+    step() call (the capture's warm-up run leaves no trace: scripts/train.py:285-323 steps once per batch) and ONE capture per
+    batch size however many distinct input tensors arrive.  The weight-gradient flush adds fp32 partial sums with atomics in a
+    different order every run, and AdamW's first steps turn a last-bit difference of a near-zero gradient into a difference of
+    the order of lr, so two EAGER runs of the same steps already differ; the graph run must be no further from an eager run
+    than a second eager run is (x8), and its losses must agree step by step."""
     B, S, I = 256, 64, 128
     batches = [tuple(t.cuda() if t.shape[-1] != 1 else t.reshape(-1).cuda() for t in make_rays(50 + i, B)) for i in range(2)]
-    seq = [0, 0, 1, 1, 0, 1]                       # what the graph run executes: warm-up(0), replay(0), warm-up(1), replay(1), replay(0), replay(1)
+    short = tuple(t[:100] for t in batches[1])      # the short last batch of an epoch (drop_last=False): a second batch size
+    seq = [0, 1, 0, 1, "short", 0, "short", 1]
 
     def run(use_graph):
         mc, mf = D.get_nerf_models(device="cuda")
         mc.load_state_dict(make_state_dict(31, 256))
         mf.load_state_dict(make_state_dict(32, 256))
         tr = D.FusedTrainer(mc, mf, S, I, total_steps=50, seed=123, use_graph=use_graph)
-        order = [0, 1, 0, 1] if use_graph else seq
-        losses = [tr.step(*batches[b]).clone() for b in order]
+        losses = []
+        for b in seq:
+            batch = short if b == "short" else batches[b]
+            if use_graph:
+                batch = tuple(t.clone() for t in batch)     # fresh tensors every step, as RayStore's gathers are
+            losses.append(tr.step(*batch).clone())
         torch.cuda.synchronize()
-        assert int(tr.step_dev.item()) == len(seq)
+        assert int(tr.step_dev.item()) == len(seq)          # steps taken == step() calls
+        if use_graph:
+            assert tr.graph_captures == 2                   # one per batch size
         return tr.flat.clone(), torch.stack(losses)
 
     e1, l1 = run(False)
@@ -513,10 +528,53 @@ def test_graph_replay_equals_eager_steps(D):
     rel = lambda a, b: float((a - b).norm() / b.norm())  # noqa: E731
     base = max(rel(e2, e1), rel(e3, e1), rel(e3, e2))   # the spread of eager runs among themselves (a handful of sign flips)
     assert rel(g1, e1) <= max(8.0 * base, 1e-4), (rel(g1, e1), base)
-    # the replayed steps are steps 2, 4, 5, 6 of the eager sequence
-    assert torch.allclose(lg, l1[[1, 3, 4, 5]], rtol=2e-3, atol=1e-6), (lg, l1)
+    assert torch.allclose(lg, l1, rtol=2e-3, atol=1e-6), (lg, l1)
     assert bool(torch.isfinite(g1).all())
     print(f"graph replay: rel L2 distance to eager {rel(g1, e1):.2e}; eager to eager {base:.2e}")
+
+
+def test_sm_limit_nests_and_overlap_rejects_fused_backward(D, monkeypatch):
+    """ops.sm_limit restores the budget that was in force on entry; DFN_BWD_FUSED=1 + DFN_OVERLAP is refused at construction."""
+    from deepfields_nerf_b200 import ops
+    with ops.sm_limit(100):
+        with ops.sm_limit(48):
+            assert ops._sm_limit_now.n == 48
+        assert ops._sm_limit_now.n == 100
+    assert ops._sm_limit_now.n == 0
+    monkeypatch.setenv("DFN_BWD_FUSED", "1")
+    monkeypatch.setenv("DFN_OVERLAP", "100,48")
+    mc, mf = D.get_nerf_models(device="cuda")
+    with pytest.raises(RuntimeError, match="cannot be combined"):
+        D.FusedTrainer(mc, mf, 64, 128)
+
+
+def test_overlap_mode_step_equals_sequential_step(D, monkeypatch):
+    """DFN_OVERLAP="100,48" (coarse backward on a side stream beside the fine forward, each on its share of the SMs) computes
+    the same step as the sequential schedule: same losses, gradients within the run-to-run spread of the atomic flushes."""
+    B, S, I = 512, 64, 128
+    batch = tuple(t.cuda() if t.shape[-1] != 1 else t.reshape(-1).cuda() for t in make_rays(77, B))
+
+    def run(overlap):
+        if overlap:
+            monkeypatch.setenv("DFN_OVERLAP", overlap)
+        else:
+            monkeypatch.delenv("DFN_OVERLAP", raising=False)
+        mc, mf = D.get_nerf_models(device="cuda")
+        mc.load_state_dict(make_state_dict(41, 256))
+        mf.load_state_dict(make_state_dict(42, 256))
+        tr = D.FusedTrainer(mc, mf, S, I, total_steps=50, seed=9, use_graph=False)
+        assert (tr.overlap is not None) == bool(overlap)
+        losses = tr.forward_backward(*batch).clone()
+        tr.optimizer_step()
+        torch.cuda.synchronize()
+        return losses, tr.grads.clone()
+
+    l0, g0 = run(None)
+    l1, g1 = run(None)
+    lo, go = run("100,48")
+    rel = lambda a, b: float((a - b).norm() / b.norm())  # noqa: E731
+    assert torch.allclose(lo, l0, rtol=1e-5, atol=1e-7), (lo, l0)
+    assert rel(go, g0) <= max(8.0 * rel(g1, g0), 1e-5), (rel(go, g0), rel(g1, g0))
 
 
 def test_torch_library_ops(D):
