@@ -22,6 +22,7 @@ exist on the GPU box, so the port in oracle/ stands in for it -- kind "port").
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import math
 import os
@@ -91,7 +92,7 @@ class AuxDeadline:
             if self.rank == 0:
                 self.line["aux_timeout"] = {"section": self.section, "seconds": self.seconds}
                 try:
-                    text = json.dumps(self.line)
+                    text = json.dumps(with_summary(self.line))
                 except Exception:          # the main thread was mutating a section's dict: drop the auxiliary sections
                     text = json.dumps({k: v for k, v in self.line.items() if k in HEADLINE_KEYS or k == "aux_timeout"})
                 print(text, flush=True)
@@ -106,6 +107,48 @@ class AuxDeadline:
             self.printed = True
         self.timer.cancel()
         return True
+
+
+def with_summary(line: dict) -> dict:
+    """Puts a compact `summary` object LAST in the line: the second half of BASELINE.json's metric (extract_vol points/s), the
+    inference render, strong scaling and the N > 1 equality flags in < 1 200 characters, so that they survive a reader that
+    keeps only the tail of the line.  Values are copied from the sections above it; absent sections give null."""
+    def g(d, *ks):
+        for k in ks:
+            d = d.get(k) if isinstance(d, dict) else None
+        return d
+
+    def r(x, n=4):
+        return round(x, n) if isinstance(x, float) else x
+
+    ex, mg, rn, ng = line.get("extract_vol"), line.get("multi_gpu_checks"), line.get("render"), line.get("ngp")
+    pmm = g(mg, "param_max_minus_min_over_ranks_after_steps")
+    summ = {
+        "n_gpus": line.get("n_gpus"),
+        "extract_vol_gpts": r(g(ex, "value") / 1e9) if g(ex, "value") else None,
+        "extract_vol_ms": r(g(ex, "ms"), 2),
+        "extract_vol_frac_tensor": r(g(ex, "frac_of_sustained_tensor_peak")),
+        "extract_includes_allgather": bool(ex and line.get("n_gpus", 1) > 1) if ex else None,
+        "extract_cpu_pts_per_s": r(g(ex, "cpu_baseline", "value"), 1),
+        "render_full_ms": r(g(rn, "ms_full"), 2),
+        "render_ert_ms": r(g(rn, "ms_ert"), 2),
+        "strong_ms_per_step": r(g(mg, "strong_scaling", "ms_per_step")),
+        "strong_rays_per_s": r(g(mg, "strong_scaling", "rays_per_s"), 0),
+        "strong_rays_per_gpu": g(mg, "strong_scaling", "rays_per_gpu"),
+        "params_identical": (pmm == 0.0) if pmm is not None else None,
+        "extract_sharded_eq_single": g(mg, "extract_64_sharded_equals_single_gpu"),
+        "render_sharded_eq_single": g(mg, "render_64x48_sharded_equals_single_gpu"),
+        "threshold_identical": g(mg, "extract_threshold_identical_on_all_ranks"),
+        "ngp_train_ms": r(g(ng, "train_step", "ms"), 2),
+        "ngp_train_rays_per_s": r(g(ng, "train_step", "rays_per_s"), 0),
+        "ngp_dp_ms": r(g(ng, "data_parallel", "ms"), 2),
+        "ngp_dp_rays_per_s": r(g(ng, "data_parallel", "rays_per_s"), 0),
+        "ngp_dp_allreduce_mb": r(g(ng, "data_parallel", "allreduce_mb"), 1),
+        "aux_timeout": g(line, "aux_timeout", "section"),
+    }
+    line.pop("summary", None)
+    line["summary"] = summ
+    return line
 
 
 HEADLINE_KEYS = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "repeats", "timed_region_s", "ms_per_step",
@@ -215,6 +258,43 @@ class CpuStep:
         return time.perf_counter() - t0
 
 
+class RefStep:
+    """One training step of the REFERENCE ITSELF on the host cores: the unmodified scripts/train.py `forward_pass` (staged under
+    oracle/_ref by oracle/make_ref.py) with the reference's models, sampler and MSELoss, under torch.autocast("cpu") as
+    train.py:294-295 does on a machine without CUDA, then backward and AdamW (:244-248, :310-321).  The GradScaler of :262 is
+    left out: on CPU it is disabled by torch and only forwards the calls.  Rays are processed in slices of `n` so that a step
+    of 4096 rays can be sampled; weights = the bench's synthetic state dicts."""
+
+    def __init__(self):
+        import torch
+        from types import SimpleNamespace
+        from common import make_state_dict
+        from oracle import make_ref
+        self.torch = torch
+        self.ref_train, ref_model, ref_sampling = make_ref.load()
+        self.ref_train.cfg = SimpleNamespace(N_samples=S_COARSE, N_importance=N_IMPORTANCE, chunk_size=32768)   # cfg/base_cfg.yml:64-67
+        self.dev = torch.device("cpu")
+        self.mc, self.mf = ref_model.get_nerf_models(10, 4, 256, device=self.dev)
+        self.mc.load_state_dict(make_state_dict(31, 256))
+        self.mf.load_state_dict(make_state_dict(32, 256))
+        self.mc.train(); self.mf.train()
+        self.sampler = ref_sampling.StratifiedSampler(S_COARSE, self.dev)
+        self.crit = torch.nn.MSELoss(reduction="mean")
+        self.opt = torch.optim.AdamW(list(self.mc.parameters()) + list(self.mf.parameters()), lr=5e-4, weight_decay=1e-6)
+
+    def __call__(self, seed: int, n_rays: int):
+        from common import make_rays
+        torch = self.torch
+        o, d, near, far, tgt = make_rays(seed, n_rays)
+        t0 = time.perf_counter()
+        self.opt.zero_grad()
+        with torch.amp.autocast("cpu"):
+            total, _, _ = self.ref_train.forward_pass(self.mc, self.mf, o, d, near, far, tgt, self.sampler, self.crit, self.dev, False)
+        total.backward()
+        self.opt.step()
+        return time.perf_counter() - t0
+
+
 def cpu_rate(budget_s: float):
     """rays/s of the CPU port on a bounded sample (>= 1 warm-up, median of >= 5 repetitions), fp32 and
     bf16 CPU-autocast; the fp32 figure is the headline `value` (it is the faster of the two on hosts without bf16 GEMMs)."""
@@ -265,31 +345,44 @@ def run_reference(args):
     if rank != 0:
         return
     cores = use_all_host_threads()
-    # the reference's CPU path is train.py under torch.autocast("cpu") (bf16) or train_no_amp.py (fp32): time the faster
-    probes = {}
-    for tag, ac in (("fp32", False), ("bf16_autocast", True)):
-        pr = CpuStep(64, ac)
-        pr(0, 64)
-        probes[tag] = (pr(1, 64), pr)
-    variant = min(probes, key=lambda k: probes[k][0])
-    t64, probe = probes[variant]
-    # size the per-step sample so that steps+warmup finish in ~150 s
     total = max(args.steps + args.warmup, 1)
-    n = int(max(32, min(1024, (150.0 / total) / max(t64 / 64, 1e-9) // 32 * 32)))
-    step = probe
+    kind, why_port = "port", None
+    try:
+        from oracle import make_ref
+        if not make_ref.available():
+            raise RuntimeError("oracle/_ref not staged (python oracle/make_ref.py where /root/reference exists)")
+        step = RefStep()
+        kind, variant = "reference", "bf16_autocast"
+        step(0, 64)
+        t64 = step(1, 64)
+    except Exception as e:   # the staged reference is missing or does not import here: fall back to the pinned port
+        why_port = f"{type(e).__name__}: {e}"[:200]
+        # the port's CPU path is train.py under torch.autocast("cpu") (bf16) or train_no_amp.py (fp32): time the faster
+        probes = {}
+        for tag, ac in (("fp32", False), ("bf16_autocast", True)):
+            pr = CpuStep(64, ac)
+            pr(0, 64)
+            probes[tag] = (pr(1, 64), pr)
+        variant = min(probes, key=lambda k: probes[k][0])
+        t64, step = probes[variant]
+    # the configuration's 4096-ray step when steps+warmup of it fit ~150 s, else the largest slice of it that does
+    n = int(max(32, min(B_RAYS, (150.0 / total) / max(t64 / 64, 1e-9) // 32 * 32)))
     for i in range(args.warmup):
         step(10 + i, n)
     times = [step(100 + i, n) for i in range(args.steps)]
     elapsed = sum(times)
     value = n * args.steps / elapsed
-    sample = f"{args.steps} steps of {n} rays x (64+192) samples (bounded sample of the 4096-ray batch), torch CPU {variant} (the faster of fp32 / bf16 autocast on this host), {cores} threads"
+    what = ("the reference's own scripts/train.py forward_pass + backward + AdamW under torch.autocast('cpu') (oracle/_ref)"
+            if kind == "reference" else f"CPU port oracle/nerf_oracle.py, {variant} (the faster of fp32 / bf16 autocast on this host)")
+    sample = (f"{args.steps} steps of {n} rays x (64+192) samples ("
+              + ("the whole 4096-ray batch" if n == B_RAYS else "bounded sample of the 4096-ray batch") + f"), {what}, {cores} threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16" if variant != "fp32" else "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "rays_per_step": n, "variant": variant, "note": "CPU port of the reference path (oracle/nerf_oracle.py); "
-                   "the reference itself is Python on torch and /root/reference is absent on the GPU box"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": WORKLOAD, "rays_per_step": n, "variant": variant, "same_config": n == B_RAYS,
+                   "note": what + ("" if why_port is None else "; staged reference unavailable: " + why_port)},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -312,7 +405,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     pk = peaks()
 
     K, W = args.steps, max(args.warmup, 3)
@@ -727,6 +820,51 @@ def run_ours(args):
         line["ngp"] = ngp
         del net, pos_n, dir_n, d_enc, d_tab, enc_holder
 
+    # ---- Instant-NGP data-parallel (scripts/train.py:219-222 under DDP): every rank trains its own 2^16 rays,
+    # ONE all-reduce of the flat fp32 gradient [table | dmlp | cmlp] per step.  Weak scaling; max over ranks on the device.
+    guard.enter("ngp data-parallel")
+    if world > 1 and not args.no_extract:
+        ngp_dp = None
+        try:
+            from common import make_rays
+            torch.manual_seed(7)                          # identical initial parameters on every rank
+            net_dp = D.InstantNGP("large").to(dev)
+            with torch.no_grad():
+                net_dp.pos_encoding.params.uniform_(-1.0, 1.0)
+            Bd = 1 << 16
+            o_n, d_n, near_n, far_n, tgt_n = (t.to(dev) for t in make_rays(90 + rank, Bd))
+            near_n, far_n = near_n.reshape(-1), far_n.reshape(-1)
+            trd = D.NGPTrainer(net_dp, S_COARSE, N_IMPORTANCE, lr=5e-4, total_steps=64)      # default process group
+            for _ in range(2):
+                trd.step(o_n, d_n, near_n, far_n, tgt_n)
+            barrier()
+            trd.profile = True
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            for _ in range(5):
+                trd.step(o_n, d_n, near_n, far_n, tgt_n)
+            b_.record()
+            barrier()
+            ms_d = reduce_max(a_.elapsed_time(b_)) / 5
+            st_d = trd.stage_times_ms()
+            trd.profile = False
+            fmax, fmin = trd.flat.clone(), trd.flat.clone()
+            dist.all_reduce(fmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(fmin, op=dist.ReduceOp.MIN)
+            ngp_dp = {"rays_per_gpu": Bd, "ms": ms_d, "rays_per_s": world * Bd / (ms_d * 1e-3), "scaling": "weak",
+                      "allreduce_mb": trd.grads.numel() * 4 / 1e6,
+                      "stages_ms_rank0": {k: round(sum(v) / len(v), 3) for k, v in st_d.items()},
+                      "note": "stage 'adamw' holds the blocking all-reduce of the whole flat gradient + non-finite guard + AdamW",
+                      "param_max_minus_min_over_ranks": float((fmax - fmin).abs().max()),
+                      "skipped_steps": int(trd.skip.item())}
+            del o_n, d_n, near_n, far_n, tgt_n, trd, net_dp, fmax, fmin
+            torch.cuda.empty_cache()
+        except Exception as e:  # an auxiliary measurement must not take the headline line down with it
+            ngp_dp = {"error": f"{type(e).__name__}: {e}"[:300]}
+        if line.get("ngp") is None:
+            line["ngp"] = {}
+        line["ngp"]["data_parallel"] = ngp_dp
+
     # ---- same-box comparator: the port of the reference step in stock eager PyTorch ON THIS GPU ------------
     # (what the hand-written kernels buy over library kernels on the same device); 4096 rays, coarse + fine, backward,
     # AdamW; bf16 autocast as scripts/train.py:262 (fp16 there) and fp32 with TF32 matmuls as scripts/train.py:22-24.
@@ -781,7 +919,7 @@ def run_ours(args):
     guard.enter("final barrier")
     barrier()                      # rank 0 alone ran the last sections: leave together, so that the teardown is not skewed
     if guard.finish() and rank == 0:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(with_summary(line)), flush=True)
     if world > 1:
         bye = threading.Timer(30.0, lambda: os._exit(0))      # the line is out: a communicator teardown may not hold the job
         bye.daemon = True
