@@ -46,8 +46,11 @@ constexpr int kEpiThreads = kEpiWarps * 32;
 #ifndef DFN_STORE_PIECES
 #define DFN_STORE_PIECES 8
 #endif
+// > 0: pause that long between the pieces of a stash copy; < 0: wait until the previous piece has been read out of shared
+// memory instead.  Round 3 sweep (profiles/r3_store_pacing_sweep.txt): a fixed 75-250 ns pause beats the read wait by 3-4 % on
+// the fine forward (1.243 -> 1.188 ms at 200 ns); 400 ns and more make the store the bottleneck (1.64 ms at 400, 2.79 at 800).
 #ifndef DFN_STORE_GAP_NS
-#define DFN_STORE_GAP_NS -1
+#define DFN_STORE_GAP_NS 200
 #endif
 constexpr bool kUseStoreWarp = DFN_FWD_STORE_WARP != 0;
 constexpr int kStoreWarp = 2 + kEpiWarps;     // TRAIN: ships published activation tiles to the stash (bulk shared -> global)
@@ -242,8 +245,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_fwd
     // ================= TRAIN: stash store (one thread) =================
     // The activation tile a job's epilogue publishes (h1..h8, features) is exactly the stash tile (same chunk layout), so
     // it leaves the SM as bulk copies while the tensor cores read it; the epilogue warps issue no global stores for it.
-    // The copy goes out in 8 KB pieces, each after the previous one has been read out of shared memory: one 64 KB copy
-    // holds up the weight loads queued behind it in the TMA unit (measured: fine pass 1.18 ms vs 1.07 ms in pieces).
+    // The copy goes out in 8 KB pieces a fixed pause apart (DFN_STORE_GAP_NS): one 64 KB copy holds up the weight loads
+    // queued behind it in the TMA unit (measured: fine pass 1.18 ms vs 1.07 ms in pieces).
     // `stored` tells the epilogues the tile may be overwritten; one arrive per (job, slot) keeps the aready phases
     // this thread has to observe in lockstep with them.
     if (TRAIN && lane == 0) {

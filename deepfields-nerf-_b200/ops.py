@@ -354,16 +354,18 @@ def mlp_backward_fused(packed: PackedMLP, rgb: Tensor, sigma: Tensor, d_rgb: Ten
 
 
 def mlp_backward(packed: PackedMLP, rgb: Tensor, sigma: Tensor, d_rgb: Tensor, d_sigma: Tensor, stash: Tensor,
-                 dz: Tensor, grads: Tensor, *, pos=None, view=None, rays=None, grid=None, mark=None) -> None:
+                 dz: Tensor, grads: Tensor, *, pos=None, view=None, rays=None, grid=None, mark=None, dgrad_sms: int = 0) -> None:
     """Accumulates d loss / d params into `grads` (flat fp32, reference parameter order).  Two launches: the
-    data-gradient chain, then the weight-gradient reduction; `mark(name)` (optional) is called between them."""
+    data-gradient chain, then the weight-gradient reduction; `mark(name)` (optional) is called between them.
+    dgrad_sms > 0: the data-gradient launch leaves the other SMs free (a collective running beside it needs somewhere to live)."""
     s, P, keep = _source(pos, view, rays, grid)
     assert grads.numel() == MLP_NUM_PARAMS and grads.dtype == torch.float32 and grads.is_cuda
     assert dz.numel() >= mlp_dz_bytes(P)
-    _lib.call("dfn_mlp_backward_dgrad", P, packed.bwd.data_ptr(), packed.consts.data_ptr(),
-              _f32(rgb.reshape(-1, 3), "rgb").data_ptr(), _f32(sigma.reshape(-1), "sigma").data_ptr(),
-              _f32(d_rgb.reshape(-1, 3), "d_rgb").data_ptr(), _f32(d_sigma.reshape(-1), "d_sigma").data_ptr(),
-              stash.data_ptr(), dz.data_ptr(), _stream())
+    with sm_limit(dgrad_sms if dgrad_sms > 0 else getattr(_sm_limit_now, "n", 0)):
+        _lib.call("dfn_mlp_backward_dgrad", P, packed.bwd.data_ptr(), packed.consts.data_ptr(),
+                  _f32(rgb.reshape(-1, 3), "rgb").data_ptr(), _f32(sigma.reshape(-1), "sigma").data_ptr(),
+                  _f32(d_rgb.reshape(-1, 3), "d_rgb").data_ptr(), _f32(d_sigma.reshape(-1), "d_sigma").data_ptr(),
+                  stash.data_ptr(), dz.data_ptr(), _stream())
     if mark is not None:
         mark("dgrad")
     _lib.call("dfn_mlp_backward_wgrad", C.byref(s), P, stash.data_ptr(), dz.data_ptr(), grads.data_ptr(), _stream())

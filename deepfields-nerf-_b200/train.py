@@ -124,6 +124,7 @@ class FusedTrainer:
         self.pg = process_group = None if self.local else process_group
         self.world = torch.distributed.get_world_size(process_group) if self._dist_on() else 1
         rank = torch.distributed.get_rank(process_group) if self._dist_on() else 0
+        self.pg = self._grad_group(process_group)
         self.rng = rng
         self.seed = int(seed) if seed is not None else 0x5EED + 7919 * rank
         self.use_graph = (os.environ.get("DFN_CUDA_GRAPH", "0") == "1") if use_graph is None else bool(use_graph)
@@ -134,6 +135,9 @@ class FusedTrainer:
         ov = os.environ.get("DFN_OVERLAP", "0")
         self.overlap = tuple(int(x) for x in ov.split(",")) if "," in ov else None
         self._side = torch.cuda.Stream(device=dev) if self.overlap else None
+        # world > 1: SMs the coarse network's data-gradient launch may use while the fine half of the gradient is all-reduced
+        # beside it (0 = all of them; then NCCL's CTAs only become resident when that launch drains)
+        self._dp_dgrad_sms = int(os.environ.get("DFN_DP_DGRAD_SMS", "0"))
         if self.overlap and ops.bwd_fused_default():
             # the one-launch backward sizes itself to the whole device and both networks would share one ring workspace on
             # two streams at once: corrupted gradients or the ring's time-out trap
@@ -195,6 +199,20 @@ class FusedTrainer:
 
     def _dist_on(self):
         return not self.local and torch.distributed.is_available() and torch.distributed.is_initialized()
+
+    def _grad_group(self, parent):
+        """The communicator of the gradient exchange.  The two all-reduces of a step are 2.4 MB each - latency class - and run
+        BESIDE the coarse network's backward kernels, so NCCL should take few SMs for them: DFN_GRAD_NCCL_CTAS=n (> 0) gives the
+        exchange a communicator of its own limited to n CTAs (ncclConfig max_ctas); 0 / unset = the parent group as it is.
+        Collective over the parent group: every rank constructs its trainer at the same point."""
+        n = int(os.environ.get("DFN_GRAD_NCCL_CTAS", "0"))
+        if n <= 0 or self.world == 1 or torch.distributed.get_backend(parent) != "nccl":
+            return parent
+        opts = torch.distributed.ProcessGroupNCCL.Options()
+        opts.config.max_ctas = n
+        opts.config.min_ctas = 1
+        ranks = torch.distributed.get_process_group_ranks(parent if parent is not None else torch.distributed.group.WORLD)
+        return torch.distributed.new_group(ranks=ranks, backend="nccl", pg_options=opts)
 
     def _alloc(self, B):
         if self._B == B:
@@ -288,12 +306,13 @@ class FusedTrainer:
         if done_c is not None:
             torch.cuda.current_stream().wait_event(done_c)
         else:
-            self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, mk_c, self.dz_c)
+            self._bwd(mc, rgb_c, sig_c, d_rgb_c, d_sig_c, self.stash_c, self.grads[:n], rays_c, mk_c, self.dz_c,
+                      dgrad_sms=self._dp_dgrad_sms if self.world > 1 else 0)
         self._reduce_async(self.grads[:n])
         self.aux = {"z": z_c, "z_all": z_all, "weights_coarse": w_c}
         return self.loss_sum / (3.0 * B)  # [loss_coarse, loss_fine] (MSELoss mean)
 
-    def _bwd(self, model, rgb, sig, d_rgb, d_sig, stash, grads, rays, mark, dz):
+    def _bwd(self, model, rgb, sig, d_rgb, d_sig, stash, grads, rays, mark, dz, dgrad_sms=0):
         if ops.bwd_fused_default():
             P = rgb.shape[0]
             if getattr(self, "_ws", None) is None or self._ws.numel() < ops.mlp_bwd_fused_ws_bytes(P):
@@ -301,7 +320,7 @@ class FusedTrainer:
             ops.mlp_backward_fused(model._packed, rgb, sig, d_rgb, d_sig, stash, self._ws, grads, rays=rays)
             mark("bwd_fused")
         else:
-            ops.mlp_backward(model._packed, rgb, sig, d_rgb, d_sig, stash, dz, grads, rays=rays, mark=mark)
+            ops.mlp_backward(model._packed, rgb, sig, d_rgb, d_sig, stash, dz, grads, rays=rays, mark=mark, dgrad_sms=dgrad_sms)
 
     def _reduce_async(self, g):
         """Data-parallel exchange of one network's gradient, started as soon as it is complete (NCCL runs on the process
@@ -584,7 +603,9 @@ class NGPTrainer:
     All parameters (hash table, density MLP, colour MLP) live in ONE flat fp32 buffer in the module's parameter order; the
     nn.Parameters are views of it, so state_dict() keeps the reference keys (pos_encoding.params, dmlp.params, cmlp.params).
     Like the reference, world coordinates and view directions go to the encodings unnormalised (instantngp.py:77,98).
-    tiny-cuda-nn parity is unpinned; loss_scale = tcnn's default 128, steps with a non-finite gradient are
+    tiny-cuda-nn parity is unpinned; loss_scale = tcnn's default 128 (FIXED: the reference additionally runs under GradScaler's dynamic scale, initial 65536, so at
+    small batches its smallest fp16 gradient fragments survive where these flush to zero - pass a larger loss_scale for batches
+    of a few thousand rays; d_rgb is bounded by 2 / (3 B) per sample, the guard below catches an overflow), steps with a non-finite gradient are
     skipped as torch.amp.GradScaler.step does (train.py:262-323)."""
 
     def __init__(self, model, N_samples=64, N_importance=128, lr=5e-4, total_steps=1000, white_bg=False, dist_last=1e10,
@@ -620,6 +641,9 @@ class NGPTrainer:
         self.total_steps = total_steps
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.skip = torch.zeros(1, dtype=torch.int32, device=dev)
+        # counter of the in-kernel draws (jitter, inverse-CDF): advances on EVERY step() call, also on one the non-finite guard
+        # skipped, so that the retry sees fresh samples (step_dev, which indexes the schedule and Adam's bias correction, stays)
+        self.draw_step = torch.zeros(1, dtype=torch.int32, device=dev)
         self.sampler = StratifiedSampler(N_samples, dev)
         self.loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
         self.profile, self._marks = False, []
@@ -647,7 +671,7 @@ class NGPTrainer:
         self.grads.zero_()
         self._mark("zero")
         if t_rand is None:
-            z_c = ops.stratified_sample_rng(near, far, self.sampler.t_vals, self.seed, self.step_dev)
+            z_c = ops.stratified_sample_rng(near, far, self.sampler.t_vals, self.seed, self.draw_step)
         else:
             z_c = ops.stratified_sample(near, far, self.sampler.t_vals, t_rand)
         pts_c = ops.points_on_rays(rays_o, rays_d, z_c, want_dirs=False)
@@ -656,7 +680,7 @@ class NGPTrainer:
         self._mark("query_coarse")
         _, w_c, d_rgb_c, d_sig_c = ops.render_loss(rgb_c, sig_c, z_c, target, self.loss_sum[0:1], self.white_bg, self.dist_last)
         self._mark("render_loss_coarse")
-        z_all = ops.sample_merge(z_c, w_c, u, n_new=I, rng=(self.seed, self.step_dev))
+        z_all = ops.sample_merge(z_c, w_c, u, n_new=I, rng=(self.seed, self.draw_step))
         pts_f = ops.points_on_rays(rays_o, rays_d, z_all, want_dirs=False)
         self._mark("sample_fine")
         rgb_f, sig_f = ops.ngp_forward_f32(pts_f, rays_d, tab, grid, dw, cw, dirs_group=T)
@@ -678,6 +702,7 @@ class NGPTrainer:
         ops.adamw_step_shadow(self.flat, self.grads, self.m, self.v, self.lr_table, self.b1_table, self.step_dev, self.half,
                               skip_flag=self.skip, weight_decay=self.wd, grad_scale=1.0 / self.world)
         self.model._half = None          # the module's cached fp16 copies are stale: the next module call re-derives them
+        self.draw_step.add_(1)
         self._mark("adamw")
 
     def step(self, rays_o, rays_d, near, far, target, **draws):

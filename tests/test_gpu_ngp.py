@@ -305,6 +305,8 @@ def test_ngp_trainer_step_matches_autograd_and_guards_nonfinite(D):
     tr.grads[123] = float("inf")
     tr.optimizer_step()
     assert int(tr.step_dev.item()) == 1 and int(tr.skip.item()) == 1 and torch.equal(tr.flat, p1)
+    # the skipped step did not advance the schedule / Adam counter, but the draw counter moved on: the retry gets fresh samples
+    assert int(tr.draw_step.item()) == 2
     # ... and training goes on afterwards, with in-kernel draws
     l0 = None
     for _ in range(40):
