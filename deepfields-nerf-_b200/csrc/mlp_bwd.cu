@@ -44,6 +44,10 @@ constexpr int kEpiThreads = kEpiWarps * 32;
 #ifndef DFN_DZ_STORE_PIECES
 #define DFN_DZ_STORE_PIECES 1
 #endif
+// > 0: pause between the pieces instead of waiting for the previous piece's shared-memory read (as the forward does)
+#ifndef DFN_DZ_STORE_GAP_NS
+#define DFN_DZ_STORE_GAP_NS -1
+#endif
 constexpr int kStoreWarp = 2 + kEpiWarps;     // ships published dZ tiles to the dz scratch (bulk shared -> global)
 constexpr int kThreads = 64 + kEpiThreads + 32;   // producer, issuer, 8 epilogue warps, dz store warp
 
@@ -193,7 +197,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_dgr
               for (int i = 0; i < DFN_DZ_STORE_PIECES; ++i) {
                 bulk_s2g_hint(dst + i * kPiece, sbase + kOffAct + t * kActBytes + i * kPiece, kPiece, pol);
                 bulk_commit();
-                bulk_wait_read_all();
+                if (DFN_DZ_STORE_GAP_NS > 0 && i + 1 < DFN_DZ_STORE_PIECES) __nanosleep(DFN_DZ_STORE_GAP_NS);
+                else bulk_wait_read_all();
               }
             }
             mbar_arrive(bar_stored(t));
