@@ -9,6 +9,7 @@ train.sample_pdf) call the same ctypes entry points; the registered ops are the 
 """
 from __future__ import annotations
 
+from collections import OrderedDict
 from typing import Tuple
 
 import torch
@@ -70,12 +71,36 @@ def _(bins, weights, u):
 
 
 # ---- OptimizedVanillaNeRF.forward (scripts/model.py:173-187) on the flat parameter vector ----------------------------------------
+# bf16 operand images of a parameter vector, keyed by (storage address, offset, in-place version counter): the forward and the
+# backward of one autograd step - and every further call until the parameters are written again (optimiser step, load) - share
+# one repack instead of two launches + 2.4 MB each.  A few entries suffice (coarse + fine network, a spare).
+_PACKED = OrderedDict()
+_PACKED_MAX = 4
+
+
+def _packed_for(flat_params: Tensor) -> "ops.PackedMLP":
+    key = (flat_params.device, flat_params.untyped_storage().data_ptr(), flat_params.storage_offset(), flat_params._version)
+    pk = _PACKED.get(key)
+    if pk is None:
+        # a new version of the same buffer replaces its stale image (and reuses its memory)
+        stale = [k for k in _PACKED if k[:3] == key[:3]]
+        pk = _PACKED.pop(stale[0]) if stale else ops.PackedMLP(flat_params.device)
+        for k in stale[1:]:
+            _PACKED.pop(k)
+        pk.pack(flat_params)
+        _PACKED[key] = pk
+        while len(_PACKED) > _PACKED_MAX:
+            _PACKED.popitem(last=False)
+    else:
+        _PACKED.move_to_end(key)
+    return pk
+
+
 @torch.library.custom_op("dfn::vanilla_mlp", mutates_args=(), device_types="cuda")
 def vanilla_mlp(flat_params: Tensor, pos: Tensor, view: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
     """(rgb [P,3], sigma [P], activation stash) of the fused tcgen05 forward; flat_params in the reference's named_parameters()
     order (595 844 floats)."""
-    pk = ops.PackedMLP(pos.device)
-    pk.pack(flat_params)
+    pk = _packed_for(flat_params)
     P = pos.shape[0]
     stash = torch.empty(ops.mlp_stash_bytes(P), dtype=torch.uint8, device=pos.device)
     rgb, sigma = ops.mlp_forward(pk, pos=pos.contiguous(), view=view.contiguous(), stash=stash)
@@ -91,8 +116,7 @@ def _(flat_params, pos, view):
 @torch.library.custom_op("dfn::vanilla_mlp_backward", mutates_args=(), device_types="cuda")
 def _vanilla_mlp_backward(flat_params: Tensor, pos: Tensor, view: Tensor, rgb: Tensor, sigma: Tensor, stash: Tensor, d_rgb: Tensor,
                           d_sigma: Tensor) -> Tensor:
-    pk = ops.PackedMLP(pos.device)
-    pk.pack(flat_params)
+    pk = _packed_for(flat_params)
     P = pos.shape[0]
     grads = torch.zeros(ops.MLP_NUM_PARAMS, dtype=torch.float32, device=pos.device)
     dz = torch.empty(ops.mlp_dz_bytes(P), dtype=torch.uint8, device=pos.device)

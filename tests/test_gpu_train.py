@@ -616,6 +616,18 @@ def test_torch_library_ops(D):
     ((rgb_m ** 2).mean() + 1e-2 * sig_m.mean()).backward()
     gm = torch.cat([p.grad.reshape(-1) for p in m._ordered_params()])
     assert rel_err(flat.grad, gm) < 2e-3          # same kernels, fp32 atomics order
+    # the op caches the bf16 operand images per parameter buffer and version: forward + backward above shared one repack, and
+    # an in-place write (an optimiser step) invalidates it
+    from deepfields_nerf_b200 import torch_ops as TO
+    n_img = len(TO._PACKED)
+    assert n_img >= 1
+    with torch.no_grad():
+        flat.mul_(0.5)
+    rgb_h, sig_h, _ = torch.ops.dfn.vanilla_mlp(flat, pos, view)
+    assert len(TO._PACKED) == n_img
+    m.load_state_dict({k: (v if "freq_bands" in k else v * 0.5) for k, v in sd.items()})
+    rgb_m2, sig_m2 = m(pos, view)
+    assert torch.equal(rgb_h, rgb_m2) and torch.equal(sig_h, sig_m2[:, 0]) and not torch.equal(rgb_h, rgb_o)
     # fake tensors: shapes without touching the GPU kernels
     from torch._subclasses.fake_tensor import FakeTensorMode
     with FakeTensorMode():
